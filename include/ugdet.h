@@ -1,0 +1,183 @@
+/*
+ * ugdet.h -- C ABI of the B200-native Haar-cascade face-detection engine (libugdet.so).
+ *
+ * This is the drop-in boundary for ONE hot path of kyukyukyu/ugproj-detector:
+ *     ugproj::FaceDetector::detectFaces            (reference src/tracker/detector.cc:10-43,
+ *                                                   class at src/tracker/detector.h:10-19)
+ * and the slice of OpenCV it drives (cvtColor, inRange, equalizeHist,
+ * CascadeClassifier::load / detectMultiScale, mean).  The reference has no FFI layer; its seam is
+ * that C++ class.  Everything below is plain C (pointers + sizes, no OpenCV / torch types) so the
+ * reference's C++ host code can bind it directly -- see INTEGRATION.md for the 20-line
+ * FaceDetector shim a maintainer adds.
+ *
+ * Conventions (mirror the reference: int return, 0 = OK, non-zero = failure,
+ * src/file_io.cc:7-15, src/tracker/main.cc:19-41):
+ *   - every function returns UGD_OK (0) or a UGD_ERR_* code; nothing throws across the ABI;
+ *   - the caller owns every input and output buffer;
+ *   - a ugd_cascade is immutable after load and may be shared by many detectors;
+ *   - a ugd_detector is single-threaded (one per host thread / CUDA stream);
+ *   - there is NO CPU fallback: without a CUDA device ugd_create fails with UGD_ERR_CUDA.
+ */
+#ifndef UGDET_H
+#define UGDET_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UGD_OK               0
+#define UGD_ERR_ARG          1   /* bad argument (null pointer, size out of range)                  */
+#define UGD_ERR_IO           2   /* file cannot be opened / read                                    */
+#define UGD_ERR_PARSE        3   /* malformed XML / INI                                             */
+#define UGD_ERR_UNSUPPORTED  4   /* cascade uses something the engine does not implement (tilted,
+                                    LBP/HOG, non-integer rect weights, > 255 tree nodes ...)        */
+#define UGD_ERR_CUDA         5   /* CUDA runtime error; text via ugd_last_error()                   */
+#define UGD_ERR_CAPACITY     6   /* frame larger than the detector was created for, or an internal
+                                    per-frame candidate buffer overflowed                           */
+#define UGD_ERR_NOMEM        7
+
+/* == cv::Rect (x, y, width, height as int32) -- detector.h:15 std::vector<cv::Rect>& rects */
+typedef struct { int32_t x, y, width, height; } ugd_rect;
+
+/* Runtime parameters of the path.  Defaults = the reference's literals / cfg defaults. */
+typedef struct {
+    double  scale_factor;     /* detection.scale, default 1.1            (src/structure.cc:83-85)   */
+    int32_t min_neighbors;    /* literal 2                               (src/tracker/detector.cc:29) */
+    int32_t min_w, min_h;     /* literal Size(30,30)                     (detector.cc:31)            */
+    int32_t max_w, max_h;     /* 0,0 = no maxSize (the reference passes none)                        */
+    uint8_t skin_lower[3];    /* Y,Cr,Cb  default 0,133,77               (structure.cc:75-78)        */
+    uint8_t skin_upper[3];    /* Y,Cr,Cb  default 255,173,127            (structure.cc:79-82)        */
+    uint8_t _pad[2];
+    int32_t dense_stages;     /* engine tuning: cascade stages evaluated densely (one lane per grid
+                                 position) before survivors are compacted into the work queue;
+                                 0 = engine default.  Does not change results.                       */
+    int32_t max_raw_per_frame;/* capacity of the per-frame candidate list fed to groupRectangles;
+                                 0 = engine default (8192)                                           */
+} ugd_params;
+
+typedef struct ugd_cascade  ugd_cascade;
+typedef struct ugd_detector ugd_detector;
+
+typedef struct {
+    int32_t win_w, win_h;     /* detection window of the cascade (20x20 / 24x24)                     */
+    int32_t nstages, ntrees, nnodes;
+    int32_t max_tree_nodes;   /* 1 = stump cascade                                                   */
+    int32_t old_format;       /* 1 = type_id "opencv-haar-classifier" (the reference data XMLs)         */
+    int32_t sum_exact;        /* 1 = every stage sum is exactly representable in fp64, so the
+                                 engine's parallel summation order cannot change a decision         */
+} ugd_cascade_info;
+
+/* Work counters of the most recent detect call (summed over its frames). */
+typedef struct {
+    int64_t frames;
+    int64_t levels;             /* pyramid levels per frame                                          */
+    int64_t level_pixels;       /* sum of level pixels per frame                                     */
+    int64_t grid_windows;       /* grid positions (all frames)                                       */
+    int64_t windows_evaluated;  /* grid positions minus x-skipped ones == oracle runAt calls         */
+    int64_t lowvar;             /* windows rejected by the variance test                             */
+    int64_t queued;             /* windows that survived the dense stages and entered the work queue */
+    int64_t raw;                /* accepted windows before grouping                                  */
+    int64_t grouped;            /* rectangles returned                                               */
+    int64_t near_threshold;     /* windows whose stage sum lay within 1e-5 relative of a stage
+                                   threshold (north-star counter; informational)                     */
+    int64_t weak_evals;         /* weak-classifier nodes evaluated at evaluated windows (== the oracle's
+                                   count for stump cascades; the stage-0 pre-pass also touches
+                                   x-skipped positions, which are not counted)                       */
+} ugd_counters;
+
+/* Names of the engine's kernels, in launch order, for ugd_get_kernel_times(). */
+enum { UGD_K_PREPROCESS = 0,    /* BGR -> gray + skin mask + histogram                (a2-a4)        */
+       UGD_K_EQUALIZE,          /* LUT from histogram, apply, AND mask                (a5-a6)        */
+       UGD_K_RESIZE,            /* all pyramid levels, INTER_LINEAR_EXACT             (a7)           */
+       UGD_K_COLSUM,            /* integral phase 1: per-strip column sums            (a8)           */
+       UGD_K_CARRY,             /* integral phase 2: scan of strip sums               (a8)           */
+       UGD_K_INTEGRAL,          /* integral phase 3: S and SQ planes                  (a8)           */
+       UGD_K_STAGE0,            /* variance norm + stage 0 at every grid position     (a9)           */
+       UGD_K_DENSE,             /* x-skip resolve + dense stages + queue compaction   (a9)           */
+       UGD_K_TAIL,              /* queued windows, remaining stages                   (a9)           */
+       UGD_K_GROUP,             /* groupRectangles + clip + skin post-filter          (a10-a12)      */
+       UGD_K_COUNT };
+
+/* ---- parameters / configuration -------------------------------------------------------------- */
+void ugd_params_default(ugd_params* p);
+
+/* Reads the [detection] section (and [scan] frame_size) of a reference conf/<name>.cfg with the
+ * reference's keys and defaults (structure.cc:62-85); a relative cascade path is resolved against
+ * the cfg's directory (structure.cc:199-204).  scan_w/scan_h receive -1,-1 when absent
+ * (structure.cc:64-65).  Replaces Boost.program_options for this section only. */
+int ugd_config_load(const char* cfg_path, ugd_params* p, char* cascade_path, size_t cascade_path_cap,
+                    int32_t* scan_w, int32_t* scan_h);
+
+/* ---- cascade model: replaces cv::CascadeClassifier::load (src/file_io.cc:11) ------------------ */
+int  ugd_cascade_load_xml(const char* path, ugd_cascade** out);
+int  ugd_cascade_get_info(const ugd_cascade* c, ugd_cascade_info* info);
+/* Copies the parsed model out as flat arrays (any pointer may be NULL).  Sizes: stage_* [nstages],
+ * tree_* [ntrees], node_rects [nnodes*12] (3 x (x,y,w,h)), node_weights [nnodes*3], others [nnodes].
+ * stage_thr already holds f32(xml) - 1e-5f.  Used by the loader parity tests. */
+int  ugd_cascade_dump(const ugd_cascade* c, int32_t* stage_first_tree, int32_t* stage_ntrees, float* stage_thr,
+                      int32_t* tree_first_node, int32_t* tree_nnodes, int32_t* node_rects, float* node_weights,
+                      float* node_thr, int32_t* node_left, int32_t* node_right, float* node_left_val,
+                      float* node_right_val);
+void ugd_cascade_free(ugd_cascade* c);
+
+/* ---- detector: replaces ugproj::FaceDetector (detector.h:10-19) ------------------------------- */
+/* max_w/max_h: largest frame that will be passed; max_batch: frames processed per launch group. */
+int  ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int max_w, int max_h, int max_batch,
+                ugd_detector** out);
+void ugd_destroy(ugd_detector* d);
+/* Run on a caller-provided cudaStream_t (e.g. torch's current stream); NULL = the detector's own. */
+int  ugd_set_stream(ugd_detector* d, void* cuda_stream);
+
+/* == FaceDetector::detectFaces(frame, rects): BGR 8UC3 host frame -> rect list.  Writes at most
+ * `cap` rects to out and the true count to *n (the C++ shim appends them to the caller's vector,
+ * as detector.cc:41 does). */
+int  ugd_detect_bgr(ugd_detector* d, const uint8_t* bgr, int w, int h, size_t stride_bytes, ugd_rect* out,
+                    int cap, int* n);
+/* == cascade.detectMultiScale(gray, ...) on a ready 8UC1 image (no equalizeHist, no skin logic). */
+int  ugd_detect_gray(ugd_detector* d, const uint8_t* gray, int w, int h, size_t stride_bytes, ugd_rect* out,
+                     int cap, int* n);
+/* Many frames per call.  frames: nframes tightly packed frames (w*h*(3 if is_bgr else 1) bytes each),
+ * in host memory (is_device=0; copied inside the call) or device memory (is_device=1).
+ * out: nframes*cap rects (host); counts: nframes (host).  Frames beyond max_batch are processed in
+ * successive groups of max_batch. */
+int  ugd_detect_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h,
+                      ugd_rect* out, int cap, int* counts);
+
+/* ---- observability / parity hooks ------------------------------------------------------------- */
+int  ugd_get_counters(const ugd_detector* d, ugd_counters* c);
+/* Per-kernel device time (ms, CUDA events on the detector's stream) of the most recent detect call;
+ * recorded only after ugd_set_profiling(d, 1).  times_ms: UGD_K_COUNT entries. */
+int  ugd_set_profiling(ugd_detector* d, int on);
+int  ugd_get_kernel_times(const ugd_detector* d, float* times_ms, int64_t* launches);
+const char* ugd_kernel_name(int k);
+
+/* Pyramid geometry for a frame size: number of levels, and per level the float32 scale, level
+ * width/height and grid step.  Arrays may be NULL; cap = their length. */
+int  ugd_plan_info(ugd_detector* d, int w, int h, int* nlevels, float* scales, int32_t* lw, int32_t* lh,
+                   int32_t* step, int cap);
+/* Raw view of the most recent single-frame gray/bgr detect (frame 0 of a batch): every accepted
+ * window before grouping (unclipped) and its final-stage sum -- the same observables as cv2's
+ * detectMultiScale(minNeighbors=0) / detectMultiScale3(outputRejectLevels). */
+int  ugd_get_raw(ugd_detector* d, ugd_rect* out, double* sums, int cap, int* n);
+/* When enabled, the next detect calls also record, for frame 0, the fate of every grid position in
+ * scan order (level, row, column): -2 x-skipped, -1 low variance, k = rejected at stage k,
+ * nstages = accepted.  ugd_get_stage_map copies it out (cap entries; *n = grid positions). */
+int  ugd_set_stage_map(ugd_detector* d, int on);
+int  ugd_get_stage_map(ugd_detector* d, int16_t* map, size_t cap, size_t* n);
+/* Intermediate images of frame 0 of the most recent call, for per-subsystem parity tests:
+ *   ugd_get_preprocessed: equalised+masked gray (w*h) and skin mask (w*h) after a BGR call;
+ *   ugd_get_level: level image (lw*lh, tight) and integral planes S, SQ ((lh+1)*(lw+1), tight). */
+int  ugd_get_preprocessed(ugd_detector* d, uint8_t* gray_eq, uint8_t* mask);
+int  ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t* SQ);
+
+const char* ugd_strerror(int code);
+const char* ugd_last_error(const ugd_detector* d);   /* detail of the detector's last failure */
+const char* ugd_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UGDET_H */

@@ -1,0 +1,133 @@
+"""GPU parity tests proper: every kernel of the path against the CPU oracle (and live cv2 4.13),
+called through the C ABI (ctypes -> libugdet.so).  Bit-exact: integers, bytes, decisions, rects."""
+import numpy as np
+import pytest
+
+from conftest import CASCADES, rectset
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dets(ug, cv2ref):
+    out = {}
+    for name in CASCADES:
+        c = ug.Cascade(cv2ref.cascade_path(name))
+        out[name] = (c, ug.Detector(c, ug.default_params(), max_size=(1280, 720), max_batch=4))
+    yield out
+    for _, d in out.values():
+        d.close()
+
+
+def test_pyramid_and_integrals_bit_exact(dets, synth, orc):
+    import cv2
+    _, det = dets["alt"]
+    g = synth.gray_frame(640, 360, 6, 5)
+    det.detect_gray(g)
+    sc, lw, lh, st = det.plan_info(640, 360)
+    want_sc = orc.scale_list(640, 360, 20, 20)
+    assert np.array_equal(sc, want_sc)
+    for i in range(len(sc)):
+        assert (lw[i], lh[i]) == orc.level_size(640, 360, float(sc[i]))
+        img, S, SQ = det.level(i, int(lw[i]), int(lh[i]))
+        ref = cv2.resize(g, (int(lw[i]), int(lh[i])), interpolation=cv2.INTER_LINEAR_EXACT)
+        assert np.array_equal(img, ref), f"level {i} image"
+        assert np.array_equal(img, orc.resize_exact(g, int(lw[i]), int(lh[i])))
+        s2, q2 = cv2.integral2(ref, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
+        assert np.array_equal(S, s2), f"level {i} S"
+        assert np.array_equal(SQ, q2), f"level {i} SQ"
+
+
+def test_integral_wraps_like_cv2_at_720p(dets, synth):
+    import cv2
+    _, det = dets["alt"]
+    g = np.full((720, 1280), 255, np.uint8)
+    g[::7, ::5] = 3
+    det.detect_gray(g)
+    sc, lw, lh, _ = det.plan_info(1280, 720)
+    img, S, SQ = det.level(0, int(lw[0]), int(lh[0]))
+    s2, q2 = cv2.integral2(img, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
+    assert (q2 < 0).any()                      # the squared integral really wraps here
+    assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+
+
+def test_preprocess_bit_exact(dets, synth, orc):
+    import cv2
+    _, det = dets["alt2"]
+    rng = np.random.default_rng(1)
+    for bgr in (synth.bgr_frame(640, 360, 6, 2), rng.integers(0, 256, (123, 157, 3), dtype=np.uint8)):
+        h, w = bgr.shape[:2]
+        det.detect_bgr(bgr)
+        geq, mask = det.preprocessed(w, h)
+        ycc = cv2.cvtColor(bgr, cv2.COLOR_BGR2YCrCb)
+        m = cv2.inRange(ycc, (0, 133, 77), (255, 173, 127))
+        want = cv2.bitwise_and(cv2.equalizeHist(cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY)), m)
+        assert np.array_equal(mask, m)
+        assert np.array_equal(geq, want)
+        assert np.array_equal(mask, orc.inrange3(orc.bgr2ycrcb(bgr), (0, 133, 77), (255, 173, 127)))
+
+
+@pytest.mark.parametrize("name", CASCADES)
+def test_window_decisions_raw_and_grouped(dets, synth, orc, cv2ref, name):
+    casc, det = dets[name]
+    oc = orc.OracleCascade.load(cv2ref.cascade_path(name))
+    det.set_stage_map(True)
+    for seed in (0, 1):
+        g = synth.gray_frame(640, 360, 6, seed)
+        got = det.detect_gray(g)
+        raw, sums = det.raw()
+        smap = det.stage_map()
+        ctr = det.counters()
+        oraw, osums, octr, omap = orc.detect_raw(oc, g, want_map=True)
+        # per-window accept/reject decisions, every grid position, bit-exact
+        assert len(smap) == len(omap)
+        bad = np.nonzero(smap != omap)[0]
+        assert len(bad) == 0, f"{len(bad)} window decisions differ, first at {bad[:5]}: {smap[bad[:5]]} vs {omap[bad[:5]]}"
+        assert ctr["windows_evaluated"] == octr["windows_evaluated"]
+        assert ctr["grid_windows"] == octr["grid_windows"]
+        assert ctr["lowvar"] == octr["lowvar"]
+        # accepted windows + final-stage sums (bitwise)
+        a = sorted(zip(map(tuple, raw.tolist()), sums.tolist()))
+        b = sorted(zip(map(tuple, oraw.tolist()), osums.tolist()))
+        assert a == b
+        # grouped rectangles vs oracle and live cv2
+        want, _ = orc.detect_multiscale(oc, g)
+        assert rectset(got) == rectset(want)
+        cc = cv2ref.load(cv2ref.cascade_path(name))
+        assert rectset(got) == rectset(cv2ref.detect_multiscale_cv2(cc, g))
+    det.set_stage_map(False)
+
+
+def test_detect_faces_bgr_end_to_end(dets, synth, orc, cv2ref):
+    casc, det = dets["alt2"]
+    oc = orc.OracleCascade.load(cv2ref.cascade_path("alt2"))
+    cc = cv2ref.load(cv2ref.cascade_path("alt2"))
+    nonempty = 0
+    for seed in range(4):
+        bgr = synth.bgr_frame(640, 360, 6, seed)
+        got = det.detect_bgr(bgr)
+        want, _ = orc.detect_faces(oc, bgr)
+        assert rectset(got) == rectset(want)
+        assert rectset(got) == rectset(cv2ref.detect_faces_cv2(cc, bgr))
+        nonempty += len(got) > 0
+    assert nonempty > 0
+
+
+def test_batch_equals_single_and_720p(dets, synth, orc, cv2ref):
+    casc, det = dets["alt"]
+    cc = cv2ref.load(cv2ref.cascade_path("alt"))
+    frames = synth.gray_batch(1280, 720, 6, seed0=10)       # 6 frames > max_batch 4: two groups
+    got = det.detect_batch(frames)
+    for f in range(len(frames)):
+        assert rectset(got[f]) == rectset(det.detect_gray(frames[f]))
+        assert rectset(got[f]) == rectset(cv2ref.detect_multiscale_cv2(cc, frames[f]))
+
+
+def test_edge_cases(dets, synth, ug):
+    casc, det = dets["alt"]
+    assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance
+    assert len(det.detect_gray(np.zeros((25, 25), np.uint8))) == 0            # smaller than minSize: no level
+    g = synth.gray_frame(333, 217, 3, 4)                                      # ragged sizes
+    det.detect_gray(g)
+    with pytest.raises(ug.UgdError):
+        det.detect_gray(np.zeros((721, 1280), np.uint8))                       # larger than created for

@@ -1,0 +1,285 @@
+"""ugproj-detector_b200 -- host-side mirror of the reference's detector interface over libugdet.so.
+
+The product is the CUDA library (csrc/, C ABI in include/ugdet.h).  This module is the thin
+Python face of it used by tests and bench.py; `FaceDetector` mirrors ugproj::FaceDetector
+(reference src/tracker/detector.h:10-19): constructed from a loaded cascade + the [detection]
+config section, `detectFaces(frame, rects)` APPENDS to the caller's list (detector.cc:41).
+
+There is no CPU path here: importing works without a GPU (the library only needs libcudart's
+static stub), but creating a detector without a CUDA device raises UgdError(UGD_ERR_CUDA).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM = range(8)
+K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_stage0",
+           "k_dense", "k_tail", "k_group")
+
+
+class Rect(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
+
+
+class Params(C.Structure):
+    _fields_ = [("scale_factor", C.c_double), ("min_neighbors", C.c_int32), ("min_w", C.c_int32),
+                ("min_h", C.c_int32), ("max_w", C.c_int32), ("max_h", C.c_int32),
+                ("skin_lower", C.c_uint8 * 3), ("skin_upper", C.c_uint8 * 3), ("_pad", C.c_uint8 * 2),
+                ("dense_stages", C.c_int32), ("max_raw_per_frame", C.c_int32)]
+
+
+class CascadeInfo(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("win_w", "win_h", "nstages", "ntrees", "nnodes", "max_tree_nodes",
+                                         "old_format", "sum_exact")]
+
+
+class Counters(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("frames", "levels", "level_pixels", "grid_windows", "windows_evaluated",
+                                         "lowvar", "queued", "raw", "grouped", "near_threshold",
+                                         "weak_evals")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+class UgdError(RuntimeError):
+    def __init__(self, code, detail=""):
+        self.code = code
+        msg = lib().ugd_strerror(code).decode()
+        super().__init__(f"ugdet error {code} ({msg})" + (f": {detail}" if detail else ""))
+
+
+def lib_path() -> str:
+    return _build.LIB
+
+
+def lib():
+    """Loads libugdet.so (building it in-tree with nvcc if it is missing or stale)."""
+    global _LIB
+    if _LIB is None:
+        path = _build.build()
+        L = C.CDLL(path)
+        L.ugd_strerror.restype = C.c_char_p
+        L.ugd_last_error.restype = C.c_char_p
+        L.ugd_version.restype = C.c_char_p
+        L.ugd_kernel_name.restype = C.c_char_p
+        L.ugd_cascade_free.restype = None
+        L.ugd_destroy.restype = None
+        L.ugd_params_default.restype = None
+        L.ugd_last_error.argtypes = [C.c_void_p]
+        L.ugd_destroy.argtypes = [C.c_void_p]
+        L.ugd_cascade_free.argtypes = [C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def default_params(**kw) -> Params:
+    p = Params()
+    lib().ugd_params_default(C.byref(p))
+    for k, v in kw.items():
+        if k in ("skin_lower", "skin_upper"):
+            setattr(p, k, (C.c_uint8 * 3)(*v))
+        elif k == "min_size":
+            p.min_w, p.min_h = v
+        elif k == "max_size":
+            p.max_w, p.max_h = v
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def load_config(cfg_path: str):
+    """[detection] section of a reference cfg -> (Params, cascade_path, (scan_w, scan_h))."""
+    p = Params()
+    buf = C.create_string_buffer(4096)
+    sw, sh = C.c_int32(), C.c_int32()
+    rc = lib().ugd_config_load(cfg_path.encode(), C.byref(p), buf, C.c_size_t(4096), C.byref(sw), C.byref(sh))
+    if rc:
+        raise UgdError(rc, cfg_path)
+    return p, buf.value.decode(), (sw.value, sh.value)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Cascade:
+    """== cv::CascadeClassifier after load() (reference src/file_io.cc:11)."""
+
+    def __init__(self, path: str):
+        self._h = C.c_void_p()
+        rc = lib().ugd_cascade_load_xml(path.encode(), C.byref(self._h))
+        if rc:
+            raise UgdError(rc, path)
+        self.path = path
+        self.info = CascadeInfo()
+        lib().ugd_cascade_get_info(self._h, C.byref(self.info))
+
+    def dump(self):
+        i = self.info
+        d = dict(stage_first_tree=np.zeros(i.nstages, np.int32), stage_ntrees=np.zeros(i.nstages, np.int32),
+                 stage_thr=np.zeros(i.nstages, np.float32), tree_first_node=np.zeros(i.ntrees, np.int32),
+                 tree_nnodes=np.zeros(i.ntrees, np.int32), node_rects=np.zeros((i.nnodes, 3, 4), np.int32),
+                 node_weights=np.zeros((i.nnodes, 3), np.float32), node_thr=np.zeros(i.nnodes, np.float32),
+                 node_left=np.zeros(i.nnodes, np.int32), node_right=np.zeros(i.nnodes, np.int32),
+                 node_left_val=np.zeros(i.nnodes, np.float32), node_right_val=np.zeros(i.nnodes, np.float32))
+        rc = lib().ugd_cascade_dump(self._h, *[_p(v) for v in d.values()])
+        if rc:
+            raise UgdError(rc)
+        return d
+
+    def __del__(self):
+        if getattr(self, "_h", None) and _LIB is not None:
+            _LIB.ugd_cascade_free(self._h)
+            self._h = None
+
+
+class Detector:
+    """Owns one ugd_detector.  All frames are numpy uint8 arrays (or raw device pointers)."""
+
+    def __init__(self, cascade: Cascade, params: Params | None = None, device: int = 0, max_size=(1280, 720),
+                 max_batch: int = 1):
+        self.cascade = cascade
+        self.params = params if params is not None else default_params()
+        self._h = C.c_void_p()
+        rc = lib().ugd_create(cascade._h, C.byref(self.params), device, max_size[0], max_size[1], max_batch,
+                              C.byref(self._h))
+        if rc:
+            raise UgdError(rc, "ugd_create")
+        self.max_batch = max_batch
+
+    def _ck(self, rc):
+        if rc:
+            raise UgdError(rc, lib().ugd_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None) and _LIB is not None:
+            _LIB.ugd_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_stream(self, cuda_stream: int):
+        self._ck(lib().ugd_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    # -- single frame -----------------------------------------------------------------------------
+    def detect_bgr(self, bgr: np.ndarray, cap: int = 1024) -> np.ndarray:
+        assert bgr.dtype == np.uint8 and bgr.ndim == 3 and bgr.shape[2] == 3
+        bgr = np.ascontiguousarray(bgr)
+        h, w = bgr.shape[:2]
+        out = (Rect * cap)()
+        n = C.c_int()
+        self._ck(lib().ugd_detect_bgr(self._h, _p(bgr), w, h, C.c_size_t(w * 3), out, cap, C.byref(n)))
+        return _rects_np(out, min(n.value, cap))
+
+    def detect_gray(self, gray: np.ndarray, cap: int = 1024) -> np.ndarray:
+        assert gray.dtype == np.uint8 and gray.ndim == 2
+        gray = np.ascontiguousarray(gray)
+        h, w = gray.shape
+        out = (Rect * cap)()
+        n = C.c_int()
+        self._ck(lib().ugd_detect_gray(self._h, _p(gray), w, h, C.c_size_t(w), out, cap, C.byref(n)))
+        return _rects_np(out, min(n.value, cap))
+
+    # -- batch ------------------------------------------------------------------------------------
+    def detect_batch(self, frames: np.ndarray, cap: int = 256):
+        """frames: [N,H,W] gray or [N,H,W,3] BGR host array -> list of [n_i,4] int32 arrays."""
+        assert frames.dtype == np.uint8 and frames.ndim in (3, 4)
+        frames = np.ascontiguousarray(frames)
+        n, h, w = frames.shape[:3]
+        return self._batch(_p(frames), 0, frames.ndim == 4, n, w, h, cap)
+
+    def detect_batch_device(self, dev_ptr: int, is_bgr: bool, n: int, w: int, h: int, cap: int = 256):
+        return self._batch(C.c_void_p(dev_ptr), 1, is_bgr, n, w, h, cap)
+
+    def _batch(self, ptr, is_device, is_bgr, n, w, h, cap):
+        key = (n, cap)
+        if getattr(self, "_bkey", None) != key:
+            self._bout = np.zeros((n, cap, 4), np.int32)
+            self._bcnt = np.zeros(n, np.int32)
+            self._bkey = key
+        self._ck(lib().ugd_detect_batch(self._h, ptr, is_device, int(is_bgr), n, w, h, _p(self._bout), cap,
+                                        _p(self._bcnt)))
+        return [self._bout[i, :min(int(self._bcnt[i]), cap)].copy() for i in range(n)]
+
+    # -- observability ----------------------------------------------------------------------------
+    def counters(self) -> dict:
+        c = Counters()
+        self._ck(lib().ugd_get_counters(self._h, C.byref(c)))
+        return c.as_dict()
+
+    def set_profiling(self, on: bool):
+        self._ck(lib().ugd_set_profiling(self._h, int(on)))
+
+    def kernel_times(self):
+        t = (C.c_float * len(K_NAMES))()
+        l = (C.c_int64 * len(K_NAMES))()
+        self._ck(lib().ugd_get_kernel_times(self._h, t, l))
+        return {K_NAMES[i]: (float(t[i]), int(l[i])) for i in range(len(K_NAMES))}
+
+    def plan_info(self, w, h):
+        n = C.c_int()
+        self._ck(lib().ugd_plan_info(self._h, w, h, C.byref(n), None, None, None, None, 0))
+        sc = np.zeros(n.value, np.float32)
+        lw = np.zeros(n.value, np.int32); lh = np.zeros(n.value, np.int32); st = np.zeros(n.value, np.int32)
+        self._ck(lib().ugd_plan_info(self._h, w, h, C.byref(n), _p(sc), _p(lw), _p(lh), _p(st), n.value))
+        return sc, lw, lh, st
+
+    def raw(self, cap: int = 1 << 16):
+        out = (Rect * cap)()
+        sums = np.zeros(cap, np.float64)
+        n = C.c_int()
+        self._ck(lib().ugd_get_raw(self._h, out, _p(sums), cap, C.byref(n)))
+        m = min(n.value, cap)
+        return _rects_np(out, m), sums[:m].copy()
+
+    def set_stage_map(self, on: bool):
+        self._ck(lib().ugd_set_stage_map(self._h, int(on)))
+
+    def stage_map(self):
+        n = C.c_size_t()
+        self._ck(lib().ugd_get_stage_map(self._h, None, C.c_size_t(0), C.byref(n)))
+        m = np.zeros(n.value, np.int16)
+        self._ck(lib().ugd_get_stage_map(self._h, _p(m), C.c_size_t(n.value), C.byref(n)))
+        return m
+
+    def preprocessed(self, w, h):
+        g = np.zeros((h, w), np.uint8); m = np.zeros((h, w), np.uint8)
+        self._ck(lib().ugd_get_preprocessed(self._h, _p(g), _p(m)))
+        return g, m
+
+    def level(self, idx, lw, lh):
+        img = np.zeros((lh, lw), np.uint8)
+        S = np.zeros((lh + 1, lw + 1), np.int32); SQ = np.zeros((lh + 1, lw + 1), np.int32)
+        self._ck(lib().ugd_get_level(self._h, idx, _p(img), _p(S), _p(SQ)))
+        return img, S, SQ
+
+
+def _rects_np(buf, n):
+    if n == 0:
+        return np.zeros((0, 4), np.int32)
+    return np.frombuffer(buf, dtype=np.int32, count=4 * n).reshape(n, 4).copy()
+
+
+class FaceDetector:
+    """Mirror of ugproj::FaceDetector (reference src/tracker/detector.h:10-19).
+
+    FaceDetector(cascade, cfg) holds references to a loaded cascade and the detection config;
+    detectFaces(frame, rects) appends (x, y, w, h) tuples to `rects` (detector.cc:41)."""
+
+    def __init__(self, cascade: Cascade, cfg: Params | None = None, max_size=(1920, 1080), device: int = 0):
+        self.cascade = cascade
+        self.cfg_ = cfg if cfg is not None else default_params()
+        self._det = Detector(cascade, self.cfg_, device=device, max_size=max_size, max_batch=1)
+
+    def detectFaces(self, frame: np.ndarray, rects: list) -> None:
+        for r in self._det.detect_bgr(frame):
+            rects.append(tuple(int(v) for v in r))

@@ -1,0 +1,573 @@
+// C ABI of libugdet.so (include/ugdet.h): detector object, device buffers, launch sequence.
+// Host orchestration only -- all arithmetic of the path happens in the kernels of k_*.cu.
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace ugd;
+
+namespace {
+
+struct DevPtr {                       // grow-only device allocation
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct DevPlan {                      // a Plan plus its device copies
+    Plan host;
+    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_pos;
+    void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release(); wk_colsum.release();
+                     wk_carry.release(); wk_integral.release(); wk_pos.release(); }
+};
+
+std::mutex g_const_mu;
+const void* g_const_owner = nullptr;  // which detector's dense nodes currently sit in __constant__
+
+inline size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+
+}  // namespace
+
+struct ugd_detector {
+    const Cascade* casc = nullptr;
+    ugd_params prm{};
+    int device = 0, max_w = 0, max_h = 0, max_batch = 1;
+    int dense_stages = 1, dense_nodes = 0, rawcap = 8192;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
+    // cascade on device
+    DevPtr nodeA, nodeB, nodeC, st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
+    // frame buffers
+    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, posv, queue, qcount, raw, rawsum,
+        rawcount, grp, out, outcount, counters, stage_map, gray_in;
+    // host staging (pinned)
+    ugd_rect* h_out = nullptr; int* h_counts = nullptr; unsigned long long* h_ctr = nullptr;
+    size_t h_out_cap = 0; int h_outcap_rects = 0;
+    // state of the last call
+    DevBufs last{};
+    const DevPlan* last_plan = nullptr;
+    bool last_was_bgr = false;
+    ugd_counters ctr{};
+    bool profiling = false, want_map = false;
+    float ktime[UGD_K_COUNT] = {0}; int64_t klaunch[UGD_K_COUNT] = {0};
+    cudaEvent_t ev[UGD_K_COUNT + 1] = {nullptr};
+    std::string err;
+    int sm_count = 148;
+};
+
+namespace {
+
+int fail_cuda(ugd_detector* d, cudaError_t e, const char* what) {
+    d->err = std::string(what) + ": " + cudaGetErrorString(e);
+    return UGD_ERR_CUDA;
+}
+#define CK(call)                                                        \
+    do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(d, e_, #call); } while (0)
+
+template <class T>
+int upload(ugd_detector* d, DevPtr& dst, const std::vector<T>& v) {
+    CK(dst.reserve(std::max<size_t>(v.size() * sizeof(T), 16)));
+    if (!v.empty()) CK(cudaMemcpyAsync(dst.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, d->stream));
+    return UGD_OK;
+}
+
+int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
+    auto key = std::make_pair(w, h);
+    auto it = d->plans.find(key);
+    if (it != d->plans.end()) { *out = it->second.get(); return UGD_OK; }
+    std::unique_ptr<DevPlan> dp(new DevPlan);
+    const Cascade& c = *d->casc;
+    build_plan(w, h, c.win_w, c.win_h, d->prm.scale_factor, d->prm.min_w, d->prm.min_h, d->prm.max_w, d->prm.max_h, dp->host);
+    int rc;
+    if ((rc = upload(d, dp->levels, dp->host.levels))) return rc;
+    if ((rc = upload(d, dp->xtab, dp->host.xtab))) return rc;
+    if ((rc = upload(d, dp->ytab, dp->host.ytab))) return rc;
+    if ((rc = upload(d, dp->wk_resize, dp->host.wk_resize))) return rc;
+    if ((rc = upload(d, dp->wk_colsum, dp->host.wk_colsum))) return rc;
+    if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
+    if ((rc = upload(d, dp->wk_integral, dp->host.wk_integral))) return rc;
+    if ((rc = upload(d, dp->wk_pos, dp->host.wk_pos))) return rc;
+    CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
+    *out = dp.get();
+    d->plans[key] = std::move(dp);
+    return UGD_OK;
+}
+
+int upload_cascade(ugd_detector* d) {
+    const Cascade& c = *d->casc;
+    std::vector<uint4> A(c.nnodes()), B(c.nnodes());
+    std::vector<uint2> C(c.nnodes());
+    for (int i = 0; i < c.nnodes(); ++i) {
+        const PackedNode& p = c.packed[i];
+        A[i] = make_uint4(p.r0, p.r1, p.r2, p.thr_bits);
+        memcpy(&B[i], &p.lval, 16);
+        C[i] = make_uint2(p.meta, p.meta2);
+    }
+    int rc;
+    if ((rc = upload(d, d->nodeA, A))) return rc;
+    if ((rc = upload(d, d->nodeB, B))) return rc;
+    if ((rc = upload(d, d->nodeC, C))) return rc;
+    if ((rc = upload(d, d->st_first_tree, c.stage_first_tree))) return rc;
+    if ((rc = upload(d, d->st_ntrees, c.stage_ntrees))) return rc;
+    if ((rc = upload(d, d->st_thr, c.stage_thr))) return rc;
+    if ((rc = upload(d, d->tree_first_node, c.tree_first_node))) return rc;
+    if ((rc = upload(d, d->st_first_node, c.stage_first_node))) return rc;
+    CK(cudaStreamSynchronize(d->stream));
+    return UGD_OK;
+}
+
+// The dense-stage nodes live in one __constant__ array shared by all detectors of the process.
+int bind_constants(ugd_detector* d) {
+    std::lock_guard<std::mutex> lk(g_const_mu);
+    if (g_const_owner == d) return UGD_OK;
+    const Cascade& c = *d->casc;
+    CK(upload_dense_nodes(c.packed.data(), d->dense_nodes, d->stream));
+    CK(upload_dense_stage_table(c.stage_first_node.data(), c.stage_thr.data(), d->dense_stages + 1, d->stream));
+    CK(cudaStreamSynchronize(d->stream));
+    g_const_owner = d;
+    return UGD_OK;
+}
+
+int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, int outcap) {
+    const size_t F = (size_t)nframes;
+    const size_t px = round_up((size_t)p.w * p.h, 256);
+    if (need_bgr) {
+        CK(d->bgr.reserve(F * round_up((size_t)p.w * p.h * 3, 256) + 256));
+        CK(d->gray_raw.reserve(F * px + 256));
+        CK(d->gray_eq.reserve(F * px + 256));
+        CK(d->hist.reserve(F * 256 * sizeof(uint32_t)));
+    }
+    CK(d->mask.reserve(F * px + 256));
+    CK(d->gray_in.reserve(F * px + 256));
+    CK(d->pyr.reserve(F * p.pyr_bytes + 256));
+    CK(d->S.reserve(F * p.int_ints * 4 + 256));
+    CK(d->SQ.reserve(F * p.int_ints * 4 + 256));
+    CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
+    CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
+    CK(d->posv.reserve(F * p.pos_entries * 4 + 256));
+    CK(d->queue.reserve(F * p.pos_entries * 8 + 256));
+    CK(d->qcount.reserve(F * 4));
+    CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
+    CK(d->rawsum.reserve(F * d->rawcap * sizeof(double)));
+    CK(d->rawcount.reserve(F * 4));
+    CK(d->grp.reserve(F * 10 * (size_t)d->rawcap * 4));
+    CK(d->out.reserve(F * (size_t)outcap * sizeof(ugd_rect)));
+    CK(d->outcount.reserve(F * 4));
+    CK(d->counters.reserve(F * kCtrPerFrame * 8));
+    if (d->want_map) CK(d->stage_map.reserve(p.pos_entries * 2 + 256));
+    size_t need = F * (size_t)outcap;
+    if (need > d->h_out_cap || !d->h_out) {
+        if (d->h_out) cudaFreeHost(d->h_out);
+        if (d->h_counts) cudaFreeHost(d->h_counts);
+        if (d->h_ctr) cudaFreeHost(d->h_ctr);
+        d->h_out = nullptr; d->h_counts = nullptr; d->h_ctr = nullptr;
+        CK(cudaMallocHost((void**)&d->h_out, std::max<size_t>(need, 1) * sizeof(ugd_rect)));
+        CK(cudaMallocHost((void**)&d->h_counts, (size_t)d->max_batch * sizeof(int)));
+        CK(cudaMallocHost((void**)&d->h_ctr, (size_t)d->max_batch * kCtrPerFrame * 8));
+        d->h_out_cap = need;
+    }
+    return UGD_OK;
+}
+
+void mark(ugd_detector* d, int k) { if (d->profiling) cudaEventRecord(d->ev[k], d->stream); }
+
+// One group of <= max_batch frames already resident on the device.
+int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t frame_stride, bool is_bgr, int nframes,
+              ugd_rect* out, int cap, int* counts) {
+    const Plan& p = dp->host;
+    const Cascade& c = *d->casc;
+    int rc;
+    if ((rc = bind_constants(d))) return rc;
+    DevBufs b{};
+    b.w = p.w; b.h = p.h; b.nlevels = (int)p.levels.size(); b.nframes = nframes;
+    b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
+    b.stumps_only = c.max_tree_nodes == 1;
+    b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
+    b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint2>();
+    b.stage_first_tree = d->st_first_tree.as<int32_t>(); b.stage_ntrees = d->st_ntrees.as<int32_t>();
+    b.stage_thr = d->st_thr.as<float>(); b.tree_first_node = d->tree_first_node.as<int32_t>();
+    b.stage_first_node = d->st_first_node.as<int32_t>();
+    b.px_stride = round_up((size_t)p.w * p.h, 256);
+    b.gray_raw = d->gray_raw.as<uint8_t>(); b.gray_eq = d->gray_eq.as<uint8_t>(); b.mask = d->mask.as<uint8_t>();
+    b.hist = d->hist.as<uint32_t>();
+    memcpy(b.skin_lo, d->prm.skin_lower, 3); memcpy(b.skin_hi, d->prm.skin_upper, 3);
+    b.use_skin = is_bgr ? 1 : 0;
+    if (is_bgr) {
+        b.bgr = dev_frames; b.bgr_stride = frame_stride;
+        b.src_gray = b.gray_eq; b.src_stride = b.px_stride; b.src_pitch = p.w;
+    } else {
+        b.src_gray = dev_frames; b.src_stride = frame_stride; b.src_pitch = p.w;
+    }
+    b.pyr = d->pyr.as<uint8_t>(); b.pyr_stride = p.pyr_bytes;
+    b.S = d->S.as<int32_t>(); b.SQ = d->SQ.as<int32_t>(); b.int_stride = p.int_ints;
+    b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
+    b.posv = d->posv.as<float>(); b.pos_stride = p.pos_entries;
+    b.queue = d->queue.as<uint2>(); b.qcount = d->qcount.as<int>();
+    b.raw = d->raw.as<ugd_rect>(); b.rawsum = d->rawsum.as<double>(); b.rawcap = d->rawcap; b.rawcount = d->rawcount.as<int>();
+    b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
+    b.grp_scratch = d->grp.as<int>(); b.grp_stride = 10 * (size_t)d->rawcap;
+    b.out = d->out.as<ugd_rect>(); b.outcap = cap; b.outcount = d->outcount.as<int>();
+    b.min_neighbors = d->prm.min_neighbors;
+    b.counters = d->counters.as<unsigned long long>();
+    cudaStream_t st = d->stream;
+
+    CK(cudaMemsetAsync(b.qcount, 0, (size_t)nframes * 4, st));
+    CK(cudaMemsetAsync(b.rawcount, 0, (size_t)nframes * 4, st));
+    CK(cudaMemsetAsync(b.counters, 0, (size_t)nframes * kCtrPerFrame * 8, st));
+    if (b.stage_map) CK(cudaMemsetAsync(b.stage_map, 0x80, p.pos_entries * 2, st));
+    mark(d, 0);
+    if (is_bgr) {
+        CK(cudaMemsetAsync(b.hist, 0, (size_t)nframes * 256 * 4, st));
+        launch_preprocess(b, st);
+    }
+    mark(d, 1);
+    if (is_bgr) launch_equalize(b, st);
+    mark(d, 2);
+    launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), st);
+    mark(d, 3);
+    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
+    mark(d, 4);
+    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
+    mark(d, 5);
+    launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
+    mark(d, 6);
+    launch_stage0(b, dp->wk_pos.as<WorkItem>(), (int)p.wk_pos.size(), st);
+    mark(d, 7);
+    launch_dense(b, dp->wk_pos.as<WorkItem>(), (int)p.wk_pos.size(), st);
+    mark(d, 8);
+    int tail_blocks = 0;
+    if (d->dense_stages < c.nstages() && !p.levels.empty()) {
+        tail_blocks = std::max(1, (d->sm_count * 8 + nframes - 1) / nframes);
+        launch_tail(b, tail_blocks, st);
+    }
+    mark(d, 9);
+    launch_group(b, st);
+    mark(d, 10);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(d->h_out, b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->h_counts, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->h_ctr, b.counters, (size_t)nframes * kCtrPerFrame * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    bool overflow = false;
+    for (int f = 0; f < nframes; ++f) {
+        int n = d->h_counts[f];
+        counts[f] = n;
+        memcpy(out + (size_t)f * cap, d->h_out + (size_t)f * cap, (size_t)std::min(n, cap) * sizeof(ugd_rect));
+        const unsigned long long* k = d->h_ctr + (size_t)f * kCtrPerFrame;
+        d->ctr.windows_evaluated += (int64_t)k[CTR_EVALUATED];
+        d->ctr.lowvar += (int64_t)k[CTR_LOWVAR];
+        d->ctr.raw += (int64_t)k[CTR_RAW];
+        d->ctr.grouped += (int64_t)k[CTR_GROUPED];
+        d->ctr.near_threshold += (int64_t)k[CTR_NEAR];
+        d->ctr.weak_evals += (int64_t)k[CTR_WEAK];
+        if (k[CTR_RAW_OVERFLOW]) overflow = true;
+    }
+    {
+        std::vector<int> qc(nframes);
+        CK(cudaMemcpy(qc.data(), b.qcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost));
+        for (int v : qc) d->ctr.queued += v;
+    }
+    d->ctr.frames += nframes;
+    d->ctr.grid_windows += p.grid_windows * nframes;
+    d->ctr.levels = (int64_t)p.levels.size();
+    d->ctr.level_pixels = p.level_pixels;
+    if (d->profiling) {
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 1, tail_blocks ? 1 : 0, 1};
+        for (int k = 0; k < UGD_K_COUNT; ++k) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
+            d->ktime[k] += ms; d->klaunch[k] += launches[k];
+        }
+    }
+    d->last = b; d->last_plan = dp; d->last_was_bgr = is_bgr;
+    if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
+    return UGD_OK;
+}
+
+int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
+                  size_t host_row_stride, ugd_rect* out, int cap, int* counts) {
+    if (!d || !frames || !out || !counts || nframes < 0 || cap <= 0 || w <= 0 || h <= 0) return UGD_ERR_ARG;
+    if (w > d->max_w || h > d->max_h) { d->err = "frame larger than the detector was created for"; return UGD_ERR_CAPACITY; }
+    CK(cudaSetDevice(d->device));
+    DevPlan* dp = nullptr;
+    int rc;
+    if ((rc = get_plan(d, w, h, &dp))) return rc;
+    d->ctr = ugd_counters{};
+    memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
+    const size_t ch = is_bgr ? 3 : 1;
+    const size_t tight = (size_t)w * h * ch;
+    for (int f0 = 0; f0 < nframes; f0 += d->max_batch) {
+        const int nf = std::min(d->max_batch, nframes - f0);
+        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap))) return rc;
+        const uint8_t* dev; size_t stride;
+        uint8_t* staging = is_bgr ? d->bgr.as<uint8_t>() : d->gray_in.as<uint8_t>();
+        const size_t st_stride = is_bgr ? round_up(tight, 256) : round_up(tight, 256);
+        if (is_device) {
+            const uint8_t* src = static_cast<const uint8_t*>(frames) + (size_t)f0 * tight;
+            if (is_bgr && (((uintptr_t)src & 3) || (tight & 3))) {   // K1 reads 32-bit words: realign
+                CK(cudaMemcpy2DAsync(staging, st_stride, src, tight, tight, nf, cudaMemcpyDeviceToDevice, d->stream));
+                dev = staging; stride = st_stride;
+            } else { dev = src; stride = tight; }
+        } else {
+            const uint8_t* src = static_cast<const uint8_t*>(frames);
+            if (host_row_stride == (size_t)w * ch) {
+                CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->stream));
+            } else {                                                   // single strided frame (cv::Mat with step)
+                CK(cudaMemcpy2DAsync(staging, (size_t)w * ch, src, host_row_stride, (size_t)w * ch, h, cudaMemcpyHostToDevice, d->stream));
+            }
+            dev = staging; stride = st_stride;
+        }
+        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, out + (size_t)f0 * cap, cap, counts + f0))) return rc;
+    }
+    return UGD_OK;
+}
+
+}  // namespace
+
+// ---- C ABI ---------------------------------------------------------------------------------------
+extern "C" {
+
+int ugd_cascade_load_xml(const char* path, ugd_cascade** out) {
+    if (!path || !out) return UGD_ERR_ARG;
+    *out = nullptr;
+    std::unique_ptr<ugd_cascade> c(new ugd_cascade);
+    std::string err;
+    int rc = load_cascade_xml(path, c->c, err);
+    if (rc != UGD_OK) { fprintf(stderr, "ugdet: %s: %s\n", path, err.c_str()); return rc; }
+    *out = c.release();
+    return UGD_OK;
+}
+
+int ugd_cascade_get_info(const ugd_cascade* c, ugd_cascade_info* i) {
+    if (!c || !i) return UGD_ERR_ARG;
+    i->win_w = c->c.win_w; i->win_h = c->c.win_h; i->nstages = c->c.nstages(); i->ntrees = c->c.ntrees();
+    i->nnodes = c->c.nnodes(); i->max_tree_nodes = c->c.max_tree_nodes; i->old_format = c->c.old_format;
+    i->sum_exact = c->c.sum_exact;
+    return UGD_OK;
+}
+
+int ugd_cascade_dump(const ugd_cascade* cc, int32_t* sft, int32_t* snt, float* sthr, int32_t* tfn, int32_t* tnn,
+                     int32_t* nrects, float* nw, float* nthr, int32_t* nl, int32_t* nr, float* nlv, float* nrv) {
+    if (!cc) return UGD_ERR_ARG;
+    const Cascade& c = cc->c;
+    for (int s = 0; s < c.nstages(); ++s) {
+        if (sft) sft[s] = c.stage_first_tree[s];
+        if (snt) snt[s] = c.stage_ntrees[s];
+        if (sthr) sthr[s] = c.stage_thr[s];
+    }
+    for (int t = 0; t < c.ntrees(); ++t) { if (tfn) tfn[t] = c.tree_first_node[t]; if (tnn) tnn[t] = c.tree_nnodes[t]; }
+    for (int n = 0; n < c.nnodes(); ++n) {
+        const HostNode& h = c.nodes[n];
+        if (nrects) memcpy(nrects + 12 * n, h.rect, 48);
+        if (nw) memcpy(nw + 3 * n, h.weight, 12);
+        if (nthr) nthr[n] = h.thr;
+        if (nl) nl[n] = h.left;
+        if (nr) nr[n] = h.right;
+        if (nlv) nlv[n] = h.left_val;
+        if (nrv) nrv[n] = h.right_val;
+    }
+    return UGD_OK;
+}
+
+void ugd_cascade_free(ugd_cascade* c) { delete c; }
+
+int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int max_w, int max_h, int max_batch,
+               ugd_detector** out) {
+    if (!c || !out || max_w <= 0 || max_h <= 0 || max_batch <= 0) return UGD_ERR_ARG;
+    *out = nullptr;
+    if (max_w > 4095 + c->c.win_w || max_h > 4095 + c->c.win_h) return UGD_ERR_CAPACITY;   // queue packs x,y in 12 bits
+    std::unique_ptr<ugd_detector> up(new ugd_detector);
+    ugd_detector* d = up.get();
+    d->casc = &c->c;
+    if (p) d->prm = *p; else ugd_params_default(&d->prm);
+    if (!(d->prm.scale_factor > 1.0)) return UGD_ERR_ARG;
+    d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
+    d->rawcap = d->prm.max_raw_per_frame > 0 ? (int)round_up((size_t)d->prm.max_raw_per_frame, 4) : 8192;
+    // dense stages: default 2 (stage 0 in k_stage0, stage 1 in k_dense), bounded by the __constant__ budget
+    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 3;
+    D = std::min(D, std::min(d->casc->nstages(), 63));
+    while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;
+    if (d->casc->stage_first_node[D] > kMaxDenseNodes) return UGD_ERR_UNSUPPORTED;
+    d->dense_stages = D; d->dense_nodes = d->casc->stage_first_node[D];
+    cudaError_t e = cudaSetDevice(cuda_device);
+    if (e != cudaSuccess) { fprintf(stderr, "ugdet: cudaSetDevice(%d): %s\n", cuda_device, cudaGetErrorString(e)); return UGD_ERR_CUDA; }
+    if ((e = cudaStreamCreateWithFlags(&d->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        fprintf(stderr, "ugdet: cudaStreamCreate: %s\n", cudaGetErrorString(e)); return UGD_ERR_CUDA;
+    }
+    d->stream = d->own_stream;
+    cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
+    for (auto& ev : d->ev) cudaEventCreate(&ev);
+    if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h)) != cudaSuccess) {
+        fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
+    }
+    int rc = upload_cascade(d);
+    if (rc != UGD_OK) { fprintf(stderr, "ugdet: %s\n", d->err.c_str()); ugd_destroy(up.release()); return rc; }
+    *out = up.release();
+    return UGD_OK;
+}
+
+void ugd_destroy(ugd_detector* d) {
+    if (!d) return;
+    cudaSetDevice(d->device);
+    if (d->stream) cudaStreamSynchronize(d->stream);
+    { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
+    for (auto& kv : d->plans) kv.second->release();
+    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+                     &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
+                     &d->carryS, &d->carryQ, &d->posv, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
+                     &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};
+    for (DevPtr* p : all) p->release();
+    if (d->h_out) cudaFreeHost(d->h_out);
+    if (d->h_counts) cudaFreeHost(d->h_counts);
+    if (d->h_ctr) cudaFreeHost(d->h_ctr);
+    for (auto& ev : d->ev) if (ev) cudaEventDestroy(ev);
+    if (d->own_stream) cudaStreamDestroy(d->own_stream);
+    delete d;
+}
+
+int ugd_set_stream(ugd_detector* d, void* s) {
+    if (!d) return UGD_ERR_ARG;
+    if (d->stream) cudaStreamSynchronize(d->stream);
+    d->stream = s ? static_cast<cudaStream_t>(s) : d->own_stream;
+    { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
+    return UGD_OK;
+}
+
+int ugd_detect_bgr(ugd_detector* d, const uint8_t* bgr, int w, int h, size_t stride, ugd_rect* out, int cap, int* n) {
+    if (!n) return UGD_ERR_ARG;
+    if (stride == 0) stride = (size_t)w * 3;
+    if (stride < (size_t)w * 3) return UGD_ERR_ARG;
+    return detect_common(d, bgr, false, true, 1, w, h, stride, out, cap, n);
+}
+
+int ugd_detect_gray(ugd_detector* d, const uint8_t* gray, int w, int h, size_t stride, ugd_rect* out, int cap, int* n) {
+    if (!n) return UGD_ERR_ARG;
+    if (stride == 0) stride = (size_t)w;
+    if (stride < (size_t)w) return UGD_ERR_ARG;
+    return detect_common(d, gray, false, false, 1, w, h, stride, out, cap, n);
+}
+
+int ugd_detect_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h,
+                     ugd_rect* out, int cap, int* counts) {
+    return detect_common(d, frames, is_device != 0, is_bgr != 0, nframes, w, h, (size_t)w * (is_bgr ? 3 : 1), out, cap, counts);
+}
+
+int ugd_get_counters(const ugd_detector* d, ugd_counters* c) {
+    if (!d || !c) return UGD_ERR_ARG;
+    *c = d->ctr;
+    return UGD_OK;
+}
+
+int ugd_set_profiling(ugd_detector* d, int on) { if (!d) return UGD_ERR_ARG; d->profiling = on != 0; return UGD_OK; }
+
+int ugd_get_kernel_times(const ugd_detector* d, float* t, int64_t* l) {
+    if (!d) return UGD_ERR_ARG;
+    for (int k = 0; k < UGD_K_COUNT; ++k) { if (t) t[k] = d->ktime[k]; if (l) l[k] = d->klaunch[k]; }
+    return UGD_OK;
+}
+
+const char* ugd_kernel_name(int k) {
+    static const char* names[UGD_K_COUNT] = {"k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry",
+                                             "k_integral", "k_stage0", "k_dense", "k_tail", "k_group"};
+    return k >= 0 && k < UGD_K_COUNT ? names[k] : "?";
+}
+
+int ugd_plan_info(ugd_detector* d, int w, int h, int* nlevels, float* scales, int32_t* lw, int32_t* lh, int32_t* step, int cap) {
+    if (!d || w <= 0 || h <= 0) return UGD_ERR_ARG;
+    Plan p;
+    const Cascade& c = *d->casc;
+    build_plan(w, h, c.win_w, c.win_h, d->prm.scale_factor, d->prm.min_w, d->prm.min_h, d->prm.max_w, d->prm.max_h, p);
+    if (nlevels) *nlevels = (int)p.levels.size();
+    for (int i = 0; i < (int)p.levels.size() && i < cap; ++i) {
+        if (scales) scales[i] = p.levels[i].scale;
+        if (lw) lw[i] = p.levels[i].sw;
+        if (lh) lh[i] = p.levels[i].sh;
+        if (step) step[i] = p.levels[i].step;
+    }
+    return UGD_OK;
+}
+
+int ugd_get_raw(ugd_detector* d, ugd_rect* out, double* sums, int cap, int* n) {
+    if (!d || !n || !d->last_plan) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    int cnt = 0;
+    CK(cudaMemcpy(&cnt, d->last.rawcount, 4, cudaMemcpyDeviceToHost));
+    *n = cnt;
+    int m = std::min(std::min(cnt, cap), d->last.rawcap);
+    if (out && m > 0) CK(cudaMemcpy(out, d->last.raw, (size_t)m * sizeof(ugd_rect), cudaMemcpyDeviceToHost));
+    if (sums && m > 0) CK(cudaMemcpy(sums, d->last.rawsum, (size_t)m * 8, cudaMemcpyDeviceToHost));
+    return UGD_OK;
+}
+
+int ugd_set_stage_map(ugd_detector* d, int on) { if (!d) return UGD_ERR_ARG; d->want_map = on != 0; return UGD_OK; }
+
+int ugd_get_stage_map(ugd_detector* d, int16_t* map, size_t cap, size_t* n) {
+    if (!d || !n || !d->last_plan || !d->last.stage_map) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    const Plan& p = d->last_plan->host;
+    *n = p.map_entries;
+    if (!map) return UGD_OK;
+    std::vector<int16_t> padded(p.pos_entries);
+    CK(cudaMemcpy(padded.data(), d->last.stage_map, p.pos_entries * 2, cudaMemcpyDeviceToHost));
+    for (const LevelInfo& L : p.levels)
+        for (int r = 0; r < L.nyg; ++r)
+            for (int x = 0; x < L.nxg; ++x) {
+                size_t o = (size_t)L.map_off + (size_t)r * L.nxg + x;
+                if (o < cap) map[o] = padded[(size_t)L.pos_off + (size_t)r * L.nxg_pad + x];
+            }
+    return UGD_OK;
+}
+
+int ugd_get_preprocessed(ugd_detector* d, uint8_t* gray_eq, uint8_t* mask) {
+    if (!d || !d->last_plan || !d->last_was_bgr) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    size_t n = (size_t)d->last.w * d->last.h;
+    if (gray_eq) CK(cudaMemcpy(gray_eq, d->last.gray_eq, n, cudaMemcpyDeviceToHost));
+    if (mask) CK(cudaMemcpy(mask, d->last.mask, n, cudaMemcpyDeviceToHost));
+    return UGD_OK;
+}
+
+int ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t* SQ) {
+    if (!d || !d->last_plan) return UGD_ERR_ARG;
+    const Plan& p = d->last_plan->host;
+    if (level < 0 || level >= (int)p.levels.size()) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    const LevelInfo& L = p.levels[level];
+    if (img) CK(cudaMemcpy2D(img, L.sw, d->last.pyr + L.img_off, L.img_pitch, L.sw, L.sh, cudaMemcpyDeviceToHost));
+    size_t wbytes = (size_t)(L.sw + 1) * 4;
+    if (S) CK(cudaMemcpy2D(S, wbytes, d->last.S + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
+    if (SQ) CK(cudaMemcpy2D(SQ, wbytes, d->last.SQ + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
+    return UGD_OK;
+}
+
+const char* ugd_strerror(int code) {
+    switch (code) {
+        case UGD_OK: return "ok";
+        case UGD_ERR_ARG: return "bad argument";
+        case UGD_ERR_IO: return "cannot read file";
+        case UGD_ERR_PARSE: return "malformed cascade or config file";
+        case UGD_ERR_UNSUPPORTED: return "unsupported cascade feature";
+        case UGD_ERR_CUDA: return "CUDA error";
+        case UGD_ERR_CAPACITY: return "capacity exceeded";
+        case UGD_ERR_NOMEM: return "out of memory";
+        default: return "unknown error";
+    }
+}
+
+const char* ugd_last_error(const ugd_detector* d) { return d ? d->err.c_str() : ""; }
+const char* ugd_version(void) { return "ugdet-b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,51 @@
+// Host-side cascade model (immutable after load) and the packed device layout derived from it.
+// Replaces the cv::CascadeClassifier object the reference loads at src/file_io.cc:11.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace ugd {
+
+struct HostNode {
+    int32_t rect[3][4];     // x, y, w, h ; unused rect = zeros
+    float   weight[3];      // 0 = rect absent
+    float   thr;
+    int32_t left, right;    // > 0: child node index inside the tree, 0: leaf
+    float   left_val, right_val;
+};
+
+// Packed node, 48 bytes, the unit both evaluators read.
+//   q0 = { rect0, rect1, rect2, thr_bits }         rect = x | y<<8 | w<<16 | h<<24
+//   q1 = { left_val (f64), right_val (f64) }       leaves pre-widened: stage sums are fp64
+//   q2 = { meta, 0, 0, 0 }  meta = left | right<<8 | (w0&0xff)<<16 | (w1&0xff)<<24 ; q2.y = w2 | last<<8
+struct alignas(16) PackedNode {
+    uint32_t r0, r1, r2, thr_bits;
+    double   lval, rval;
+    uint32_t meta, meta2, pad0, pad1;
+};
+static_assert(sizeof(PackedNode) == 48, "PackedNode layout");
+
+struct Cascade {
+    int win_w = 0, win_h = 0;
+    bool old_format = false;
+    bool sum_exact = false;
+    int max_tree_nodes = 0;
+    std::vector<int32_t> stage_first_tree, stage_ntrees;
+    std::vector<float>   stage_thr;              // f32(xml) - 1e-5f
+    std::vector<int32_t> tree_first_node, tree_nnodes;
+    std::vector<HostNode> nodes;
+    // derived
+    std::vector<PackedNode> packed;              // one per node, same order
+    std::vector<int32_t> stage_first_node;       // [nstages+1]
+    int nstages() const { return (int)stage_thr.size(); }
+    int ntrees() const { return (int)tree_first_node.size(); }
+    int nnodes() const { return (int)nodes.size(); }
+};
+
+// Returns UGD_OK or an error code; err receives a one-line reason.
+int load_cascade_xml(const std::string& path, Cascade& out, std::string& err);
+
+}  // namespace ugd
+
+struct ugd_cascade { ugd::Cascade c; };

@@ -1,0 +1,170 @@
+// groupRectangles + clip + skin post-filter on the device,
+// one CTA per frame, so a batch never round-trips to the host between the cascade and the result.
+// Candidates per frame are few (10^2..10^3); this kernel is latency-, not bandwidth-bound.
+#include "kernels.cuh"
+
+namespace ugd {
+
+__device__ __forceinline__ bool similar_rects(const ugd_rect& a, const ugd_rect& b) {
+    const double eps = 0.2;
+    const double d = __dmul_rn(__dmul_rn(eps, (double)(min(a.width, b.width) + min(a.height, b.height))), 0.5);
+    return (double)abs(a.x - b.x) <= d && (double)abs(a.y - b.y) <= d &&
+           (double)abs(a.x + a.width - b.x - b.width) <= d && (double)abs(a.y + a.height - b.y - b.height) <= d;
+}
+
+__device__ __forceinline__ bool rect_less(const ugd_rect& a, const ugd_rect& b) {   // canonical output order
+    if (a.y != b.y) return a.y < b.y;
+    if (a.x != b.x) return a.x < b.x;
+    if (a.height != b.height) return a.height < b.height;
+    return a.width < b.width;
+}
+
+__global__ void __launch_bounds__(256) k_group(DevBufs b) {
+    __shared__ int s_changed, s_nkept, s_nfinal;
+    __shared__ unsigned long long s_red[8];
+    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int total = b.rawcount[frame];
+    const int n = min(total, b.rawcap);
+    unsigned long long* ctr = b.counters + (size_t)frame * kCtrPerFrame;
+    const ugd_rect* raw = b.raw + (size_t)frame * b.rawcap;
+    int* scratch = b.grp_scratch + (size_t)frame * b.grp_stride;
+    int* label = scratch;                    // [rawcap]
+    int* acc = scratch + b.rawcap;           // [rawcap][4] class sums -> class mean rect
+    int* cnt = scratch + 5 * b.rawcap;       // [rawcap]
+    ugd_rect* kept = reinterpret_cast<ugd_rect*>(scratch + 6 * b.rawcap);   // [rawcap]
+    const int g = b.min_neighbors;
+    if (tid == 0) {
+        s_nkept = 0; s_nfinal = 0;
+        ctr[CTR_RAW] = (unsigned long long)total;
+        if (total > b.rawcap) ctr[CTR_RAW_OVERFLOW] = 1ull;
+    }
+    __syncthreads();
+
+    if (g <= 0) {                                            // groupRectangles leaves the list unchanged
+        for (int i = tid; i < n; i += 256) kept[i] = raw[i];
+        if (tid == 0) s_nkept = n;
+        __syncthreads();
+    } else {
+        // ---- connected components of the similarity graph: min-label propagation + pointer jumping ----
+        for (int i = tid; i < n; i += 256) label[i] = i;
+        __syncthreads();
+        for (;;) {
+            if (tid == 0) s_changed = 0;
+            __syncthreads();
+            for (int i = tid; i < n; i += 256) {
+                const ugd_rect ri = raw[i];
+                const int li = label[i];
+                int m = li;
+                for (int j = 0; j < n; ++j) {
+                    const int lj = ((volatile int*)label)[j];
+                    if (lj < m && similar_rects(ri, raw[j])) m = lj;
+                }
+                if (m < li) { atomicMin(&label[i], m); s_changed = 1; }
+            }
+            __syncthreads();
+            for (int i = tid; i < n; i += 256) {             // pointer jumping (labels only ever point inside the class)
+                int l = ((volatile int*)label)[i];
+                int r = ((volatile int*)label)[l];
+                while (r != l) { l = r; r = ((volatile int*)label)[l]; }
+                label[i] = l;
+            }
+            __syncthreads();
+            if (!s_changed) break;
+            __syncthreads();
+        }
+        // ---- per-class integer sums -> rounded means ----
+        for (int i = tid; i < n; i += 256) { acc[4 * i] = acc[4 * i + 1] = acc[4 * i + 2] = acc[4 * i + 3] = 0; cnt[i] = 0; }
+        __syncthreads();
+        for (int i = tid; i < n; i += 256) {
+            const int l = label[i];
+            const ugd_rect r = raw[i];
+            atomicAdd(&acc[4 * l], r.x); atomicAdd(&acc[4 * l + 1], r.y);
+            atomicAdd(&acc[4 * l + 2], r.width); atomicAdd(&acc[4 * l + 3], r.height);
+            atomicAdd(&cnt[l], 1);
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += 256) {
+            if (label[i] != i) continue;
+            const float s = __fdiv_rn(1.f, (float)cnt[i]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[4 * i + k] = __float2int_rn(__fmul_rn((float)acc[4 * i + k], s));
+        }
+        __syncthreads();
+        // ---- keep classes with more than g members that are not nested in a stronger class ----
+        for (int i = tid; i < n; i += 256) {
+            if (label[i] != i) continue;
+            const int n1 = cnt[i];
+            if (n1 <= g) continue;
+            const int x1 = acc[4 * i], y1 = acc[4 * i + 1], w1 = acc[4 * i + 2], h1 = acc[4 * i + 3];
+            bool drop = false;
+            for (int j = 0; j < n && !drop; ++j) {
+                if (j == i || label[j] != j) continue;
+                const int n2 = cnt[j];
+                if (n2 <= g) continue;
+                const int x2 = acc[4 * j], y2 = acc[4 * j + 1], w2 = acc[4 * j + 2], h2 = acc[4 * j + 3];
+                const int dx = __double2int_rn(__dmul_rn((double)w2, 0.2)), dy = __double2int_rn(__dmul_rn((double)h2, 0.2));
+                if (x1 >= x2 - dx && y1 >= y2 - dy && x1 + w1 <= x2 + w2 + dx && y1 + h1 <= y2 + h2 + dy &&
+                    (n2 > max(3, n1) || n1 < 3))
+                    drop = true;
+            }
+            if (!drop) {
+                const int slot = atomicAdd(&s_nkept, 1);
+                ugd_rect r; r.x = x1; r.y = y1; r.width = w1; r.height = h1;
+                kept[slot] = r;
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- clip to the image (A.5 last line), drop empties; then the skin-coverage test (detector.cc:33-42) ----
+    const int nk = s_nkept;
+    const uint8_t* mask = b.mask + (size_t)frame * b.px_stride;
+    for (int k = 0; k < nk; ++k) {
+        ugd_rect r = kept[k];
+        const int x0 = max(r.x, 0), y0 = max(r.y, 0), x1 = min(r.x + r.width, b.w), y1 = min(r.y + r.height, b.h);
+        bool ok = x1 > x0 && y1 > y0;
+        r.x = x0; r.y = y0; r.width = x1 - x0; r.height = y1 - y0;
+        if (ok && b.use_skin) {
+            unsigned long long sum = 0;
+            for (int yy = warp; yy < r.height; yy += 8) {
+                const uint8_t* row = mask + (size_t)(y0 + yy) * b.w + x0;
+                for (int xx = lane; xx < r.width; xx += 32) sum += row[xx];
+            }
+#pragma unroll
+            for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+            __syncthreads();
+            if (lane == 0) s_red[warp] = sum;
+            __syncthreads();
+            sum = 0;
+#pragma unroll
+            for (int wv = 0; wv < 8; ++wv) sum += s_red[wv];
+            // cv::mean = sum * (1/N); norm of a 1-channel mean is the mean itself
+            const double mean = __dmul_rn((double)sum, __ddiv_rn(1.0, __dmul_rn((double)r.width, (double)r.height)));
+            ok = !(__ddiv_rn(mean, 256.0) < 0.8);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (ok) { kept[s_nfinal] = r; ++s_nfinal; }
+        }
+        __syncthreads();
+    }
+    // ---- canonical order (rank sort; cv2's own order depends on thread timing) ----
+    const int nf = s_nfinal;
+    ugd_rect* out = b.out + (size_t)frame * b.outcap;
+    for (int i = tid; i < nf; i += 256) {
+        const ugd_rect ri = kept[i];
+        int rank = 0;
+        for (int j = 0; j < nf; ++j) {
+            const ugd_rect rj = kept[j];
+            if (rect_less(rj, ri) || (!rect_less(ri, rj) && j < i)) ++rank;
+        }
+        if (rank < b.outcap) out[rank] = ri;
+    }
+    if (tid == 0) { b.outcount[frame] = nf; ctr[CTR_GROUPED] = (unsigned long long)nf; }
+}
+
+void launch_group(const DevBufs& b, cudaStream_t st) {
+    k_group<<<b.nframes, 256, 0, st>>>(b);
+}
+
+}  // namespace ugd

@@ -1,0 +1,317 @@
+// Image-side kernels of the detection path (sm_100a): colour conversion + skin mask + histogram,
+// equalizeHist, pyramid resize, integral / squared-integral images.  All integer, bit-exact with
+// the oracle.  These passes are HBM-bound: every kernel
+// moves 16-byte vectors per thread, consecutive threads touch consecutive addresses.
+#include "kernels.cuh"
+
+namespace ugd {
+
+__device__ __forceinline__ uint32_t sat8(int v) { return (uint32_t)min(max(v, 0), 255); }
+
+// ------------------------------------------------------------------------------------------------
+// K1  BGR -> gray (a4) + YCrCb skin mask (a2,a3) + 256-bin histogram of gray (first half of a5).
+// 4 pixels per thread per iteration: 12 B in, 4 B + 4 B out.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPreIters = 8;   // quads per thread -> 8192 pixels per CTA, 256 global atomics per CTA
+
+__global__ void __launch_bounds__(256) k_preprocess(DevBufs b) {
+    __shared__ uint32_t sh[8][256];                         // per-warp private histograms
+    const int frame = blockIdx.y, tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < 8 * 256; i += 256) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    const int n = b.w * b.h;
+    const uint8_t* src = b.bgr + (size_t)frame * b.bgr_stride;
+    uint8_t* gray = b.gray_raw + (size_t)frame * b.px_stride;
+    uint8_t* mask = b.mask + (size_t)frame * b.px_stride;
+    const int lo0 = b.skin_lo[0], lo1 = b.skin_lo[1], lo2 = b.skin_lo[2];
+    const int hi0 = b.skin_hi[0], hi1 = b.skin_hi[1], hi2 = b.skin_hi[2];
+    for (int it = 0; it < kPreIters; ++it) {
+        int q = (blockIdx.x * kPreIters + it) * 256 + tid;  // quad index
+        int p0 = q * 4;
+        if (p0 >= n) break;
+        uint8_t px[12];
+        if (p0 + 4 <= n) {
+            const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src) + (size_t)q * 3;
+            uint32_t a = s32[0], c = s32[1], d = s32[2];
+            *reinterpret_cast<uint32_t*>(px) = a;
+            *reinterpret_cast<uint32_t*>(px + 4) = c;
+            *reinterpret_cast<uint32_t*>(px + 8) = d;
+        } else {
+            for (int k = 0; k < 12; ++k) px[k] = (p0 * 3 + k < n * 3) ? src[(size_t)p0 * 3 + k] : 0;
+        }
+        uint32_t g4 = 0, m4 = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int B = px[3 * k], G = px[3 * k + 1], R = px[3 * k + 2];
+            int g = (3735 * B + 19235 * G + 9798 * R + 16384) >> 15;
+            int Y = (1868 * B + 9617 * G + 4899 * R + 8192) >> 14;
+            int Cr = (int)sat8(((R - Y) * 11682 + 128 * 16384 + 8192) >> 14);
+            int Cb = (int)sat8(((B - Y) * 9241 + 128 * 16384 + 8192) >> 14);
+            Y = (int)sat8(Y);
+            bool ok = Y >= lo0 && Y <= hi0 && Cr >= lo1 && Cr <= hi1 && Cb >= lo2 && Cb <= hi2;
+            g4 |= (uint32_t)g << (8 * k);
+            m4 |= (ok ? 255u : 0u) << (8 * k);
+            if (p0 + k < n) atomicAdd(&sh[warp][g], 1u);
+        }
+        if (p0 + 4 <= n) {
+            *reinterpret_cast<uint32_t*>(gray + p0) = g4;
+            *reinterpret_cast<uint32_t*>(mask + p0) = m4;
+        } else {
+            for (int k = 0; p0 + k < n; ++k) { gray[p0 + k] = (uint8_t)(g4 >> (8 * k)); mask[p0 + k] = (uint8_t)(m4 >> (8 * k)); }
+        }
+    }
+    __syncthreads();
+    uint32_t t = 0;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) t += sh[wv][tid];
+    if (t) atomicAdd(&b.hist[(size_t)frame * 256 + tid], t);
+}
+
+void launch_preprocess(const DevBufs& b, cudaStream_t st) {
+    int n = b.w * b.h;
+    int per_cta = 256 * 4 * kPreIters;
+    dim3 grid((n + per_cta - 1) / per_cta, b.nframes);
+    k_preprocess<<<grid, 256, 0, st>>>(b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2  equalizeHist LUT (a5) + apply + AND with the skin mask (a6).  16 pixels per thread.
+// Every CTA rebuilds the 256-entry LUT from the frame histogram (256 threads, one bin each).
+// ------------------------------------------------------------------------------------------------
+constexpr int kEqIters = 4;
+
+__global__ void __launch_bounds__(256) k_equalize(DevBufs b) {
+    __shared__ uint32_t cum[256];
+    __shared__ uint8_t lut[256];
+    __shared__ int s_i0;
+    const int frame = blockIdx.y, tid = threadIdx.x;
+    const int n = b.w * b.h;
+    uint32_t hv = b.hist[(size_t)frame * 256 + tid];
+    if (tid == 0) s_i0 = 256;
+    __syncthreads();
+    if (hv) atomicMin(&s_i0, tid);
+    cum[tid] = hv;
+    __syncthreads();
+    const int i0 = s_i0;
+    // inclusive scan over bins (Hillis-Steele, 8 steps)
+    for (int d = 1; d < 256; d <<= 1) {
+        uint32_t v = tid >= d ? cum[tid - d] : 0;
+        __syncthreads();
+        cum[tid] += v;
+        __syncthreads();
+    }
+    {
+        uint32_t h0 = i0 < 256 ? cum[i0] - (i0 ? cum[i0 - 1] : 0) : 0;
+        if (i0 == 256 || h0 == (uint32_t)n) lut[tid] = (uint8_t)tid;          // constant image: unchanged
+        else if (tid <= i0) lut[tid] = 0;
+        else {
+            float scale = 255.f / (float)(n - (int)h0);                       // IEEE division
+            uint32_t s = cum[tid] - cum[i0];
+            lut[tid] = (uint8_t)sat8(__float2int_rn(__fmul_rn((float)s, scale)));
+        }
+    }
+    __syncthreads();
+    const uint8_t* src = b.gray_raw + (size_t)frame * b.px_stride;
+    const uint8_t* mk = b.mask + (size_t)frame * b.px_stride;
+    uint8_t* dst = b.gray_eq + (size_t)frame * b.px_stride;
+    for (int it = 0; it < kEqIters; ++it) {
+        int p0 = ((blockIdx.x * kEqIters + it) * 256 + tid) * 16;
+        if (p0 >= n) break;
+        // planes are padded to a multiple of 256 bytes, so the vector access is always in bounds
+        uint4 g = *reinterpret_cast<const uint4*>(src + p0);
+        uint4 m = *reinterpret_cast<const uint4*>(mk + p0);
+        uint32_t gi[4] = {g.x, g.y, g.z, g.w}, mi[4] = {m.x, m.y, m.z, m.w}, o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t v = gi[k];
+            uint32_t r = (uint32_t)lut[v & 255] | (uint32_t)lut[(v >> 8) & 255] << 8 |
+                         (uint32_t)lut[(v >> 16) & 255] << 16 | (uint32_t)lut[v >> 24] << 24;
+            o[k] = b.use_skin ? (r & mi[k]) : r;
+        }
+        *reinterpret_cast<uint4*>(dst + p0) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+void launch_equalize(const DevBufs& b, cudaStream_t st) {
+    int n = b.w * b.h;
+    int per_cta = 256 * 16 * kEqIters;
+    dim3 grid((n + per_cta - 1) / per_cta, b.nframes);
+    k_equalize<<<grid, 256, 0, st>>>(b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3  pyramid resize, every level of every frame in one launch (a7; INTER_LINEAR_EXACT, A.2).
+// One thread = 4 consecutive output pixels; coefficient tables come from the plan.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_resize(DevBufs b, const WorkItem* __restrict__ wk) {
+    const WorkItem it = wk[blockIdx.x];
+    const LevelInfo& L = b.levels[it.level];
+    const int quads = L.img_pitch >> 2;
+    const int q = it.first + threadIdx.x;
+    if (q >= quads * L.sh) return;
+    const int y = q / quads, qx = q - y * quads;
+    const int frame = blockIdx.y;
+    const uint8_t* src = b.src_gray + (size_t)frame * b.src_stride;
+    const uint32_t ye = __ldg(b.ytab + L.ytab_off + y);
+    const int y0 = ye & 0xffff, cy1 = ye >> 16, cy0 = 256 - cy1;
+    const int y1 = min(y0 + 1, b.h - 1);
+    const uint8_t* r0 = src + (size_t)y0 * b.src_pitch;
+    const uint8_t* r1 = src + (size_t)y1 * b.src_pitch;
+    const uint4 xe4 = __ldg(reinterpret_cast<const uint4*>(b.xtab + L.xtab_off) + qx);
+    const uint32_t xe[4] = {xe4.x, xe4.y, xe4.z, xe4.w};
+    uint32_t outv = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int x = qx * 4 + k;
+        if (x < L.sw) {
+            int x0 = xe[k] & 0xffff, cx1 = xe[k] >> 16, cx0 = 256 - cx1;
+            int x1 = min(x0 + 1, b.w - 1);
+            int t0 = (int)__ldg(r0 + x0) * cx0 + (int)__ldg(r0 + x1) * cx1;
+            int t1 = (int)__ldg(r1 + x0) * cx0 + (int)__ldg(r1 + x1) * cx1;
+            uint32_t v = (uint32_t)(t0 * cy0 + t1 * cy1 + 32768) >> 16;
+            outv |= v << (8 * k);
+        }
+    }
+    uint8_t* dst = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
+    *reinterpret_cast<uint32_t*>(dst + (size_t)y * L.img_pitch + qx * 4) = outv;
+}
+
+void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_resize<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4  integral images S and SQ (a8), three phases so that every output element is written once
+// and every level pixel is read twice (second read is an L2 hit):
+//   colsum   : per 32-row strip, column sums of pixel and pixel^2            (1 B/px read)
+//   carry    : exclusive scan of those sums down the strips (tiny)
+//   integral : per strip, 128-column chunks: warp-shuffle row scans into shared memory, then a
+//              column pass that adds the strip carry and stores coalesced rows (8 B/px written)
+// Arithmetic is uint32 modular, which reproduces cv2's wrapping int32 SQ plane bit for bit.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_colsum(DevBufs b, const WorkItem* __restrict__ wk) {
+    const WorkItem it = wk[blockIdx.x];
+    const LevelInfo& L = b.levels[it.level];
+    const int quads = L.img_pitch >> 2;
+    const int i = it.first + threadIdx.x;
+    if (i >= quads * L.nstrips) return;
+    const int strip = i / quads, qx = i - strip * quads;
+    const int frame = blockIdx.y;
+    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + qx * 4;
+    const int v0 = strip * kStripRows, v1 = min(v0 + kStripRows, L.sh);
+    uint32_t s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+#pragma unroll 8
+    for (int v = v0; v < v1; ++v) {
+        uint32_t p = *reinterpret_cast<const uint32_t*>(img + (size_t)v * L.img_pitch);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { uint32_t c = (p >> (8 * k)) & 255u; s[k] += c; q[k] += c * c; }
+    }
+    size_t o = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * L.img_pitch + qx * 4;
+    *reinterpret_cast<uint4*>(b.carryS + o) = make_uint4(s[0], s[1], s[2], s[3]);
+    *reinterpret_cast<uint4*>(b.carryQ + o) = make_uint4(q[0], q[1], q[2], q[3]);
+}
+
+__global__ void __launch_bounds__(256) k_carry(DevBufs b, const WorkItem* __restrict__ wk) {
+    const WorkItem it = wk[blockIdx.x];
+    const LevelInfo& L = b.levels[it.level];
+    const int quads = L.img_pitch >> 2;
+    const int qx = it.first + threadIdx.x;
+    if (qx >= quads) return;
+    const int frame = blockIdx.y;
+    size_t o = (size_t)frame * b.carry_stride + L.carry_off + qx * 4;
+    uint4 as = make_uint4(0, 0, 0, 0), aq = as;
+    for (int t = 0; t < L.nstrips; ++t, o += L.img_pitch) {
+        uint4 vs = *reinterpret_cast<uint4*>(b.carryS + o), vq = *reinterpret_cast<uint4*>(b.carryQ + o);
+        *reinterpret_cast<uint4*>(b.carryS + o) = as;
+        *reinterpret_cast<uint4*>(b.carryQ + o) = aq;
+        as.x += vs.x; as.y += vs.y; as.z += vs.z; as.w += vs.w;
+        aq.x += vq.x; aq.y += vq.y; aq.z += vq.z; aq.w += vq.w;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_integral(DevBufs b, const WorkItem* __restrict__ wk) {
+    __shared__ __align__(16) uint32_t ES[kStripRows][kChunkCols];
+    __shared__ __align__(16) uint32_t EQ[kStripRows][kChunkCols];
+    __shared__ uint32_t leftS[kStripRows], leftQ[kStripRows];
+    const WorkItem it = wk[blockIdx.x];
+    const LevelInfo& L = b.levels[it.level];
+    const int strip = it.first, frame = blockIdx.y;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
+    const size_t co = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * L.img_pitch;
+    const uint32_t* cS = b.carryS + co;
+    const uint32_t* cQ = b.carryQ + co;
+    uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off);
+    uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off);
+    if (tid < kStripRows) { leftS[tid] = 0; leftQ[tid] = 0; }
+    __syncthreads();
+    const int nchunks = (L.sw + 1 + kChunkCols - 1) / kChunkCols;
+    const int Y0 = strip * kStripRows;
+    for (int c = 0; c < nchunks; ++c) {
+        // ---- row pass: exclusive prefix along x of (carry row, then 31 pixel rows) ----
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int k = warp * 4 + r;
+            const int u = c * kChunkCols + lane * 4;
+            uint32_t v[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+            if (u < L.img_pitch) {
+                if (k == 0) {
+                    uint4 a = *reinterpret_cast<const uint4*>(cS + u), d = *reinterpret_cast<const uint4*>(cQ + u);
+                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+                    q[0] = d.x; q[1] = d.y; q[2] = d.z; q[3] = d.w;
+                } else {
+                    const int row = Y0 + k - 1;
+                    if (row < L.sh) {
+                        uint32_t p = *reinterpret_cast<const uint32_t*>(img + (size_t)row * L.img_pitch + u);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { uint32_t t = (p >> (8 * j)) & 255u; v[j] = t; q[j] = t * t; }
+                    }
+                }
+            }
+            uint32_t ts = v[0] + v[1] + v[2] + v[3], tq = q[0] + q[1] + q[2] + q[3];
+            uint32_t is = ts, iq = tq;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                uint32_t a = __shfl_up_sync(0xffffffffu, is, d), e = __shfl_up_sync(0xffffffffu, iq, d);
+                if (lane >= d) { is += a; iq += e; }
+            }
+            uint32_t es = is - ts + leftS[k], eq = iq - tq + leftQ[k];
+            *reinterpret_cast<uint4*>(&ES[k][lane * 4]) = make_uint4(es, es + v[0], es + v[0] + v[1], es + v[0] + v[1] + v[2]);
+            *reinterpret_cast<uint4*>(&EQ[k][lane * 4]) = make_uint4(eq, eq + q[0], eq + q[0] + q[1], eq + q[0] + q[1] + q[2]);
+            uint32_t tots = __shfl_sync(0xffffffffu, is, 31), totq = __shfl_sync(0xffffffffu, iq, 31);
+            __syncwarp();
+            if (lane == 0) { leftS[k] += tots; leftQ[k] += totq; }
+        }
+        __syncthreads();
+        // ---- column pass: running sum down the strip, coalesced stores ----
+        {
+            const int col = tid & (kChunkCols - 1);
+            const int X = c * kChunkCols + col;
+            const uint32_t(*E)[kChunkCols] = (tid >> 7) ? EQ : ES;
+            uint32_t* out = (tid >> 7) ? outQ : outS;
+            if (X <= L.sw) {
+                uint32_t acc = E[0][col];
+                const int kmax = min(kStripRows, L.sh + 1 - Y0);
+                uint32_t* o = out + (size_t)Y0 * L.P + X;
+#pragma unroll 8
+                for (int k = 0; k < kmax; ++k) {
+                    o[(size_t)k * L.P] = acc;
+                    if (k + 1 < kStripRows) acc += E[k + 1][col];
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_colsum<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
+}
+void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_carry<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
+}
+void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_integral<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
+}
+
+}  // namespace ugd
