@@ -273,11 +273,11 @@ def main():
             "k_resize": src_px + level_px,                         # 1 B/source px read once + 1 B/level px written
             "k_colsum": level_px,                                  # 1 B/level px read (carry rows are noise)
             "k_integral": level_px + 8 * int_entries,              # 1 B read + two int32 planes written
-            "k_stage0": 8 * 4 * ctr["grid_windows"] / max(ctr["frames"], 1) + 4 * ctr["grid_windows"] / max(ctr["frames"], 1),
-            # cascade: 4-byte gathers, 8 per 2-rect / 12 per 3-rect weak classifier (avg 8.7 for alt) + 8 for the norm
-            "k_dense": 0.0, "k_tail": 0.0,
+            "k_scan": 0.0, "k_tail": 0.0,                          # L1/shared-bound, see roofline below
         }
-        gather_bytes = weak_per_frame * 4 * 8.67 + win_per_frame * 4 * 8
+        # cascade: 4-byte gathers; merged corner lists need 7.5 per weak classifier on average for alt
+        # (6/8/9 distinct corners instead of 8/12), + 8 for the variance norm of every window
+        gather_bytes = weak_per_frame * 4 * 7.5 + win_per_frame * 4 * 8
         kern = {}
         for k, (t, l) in ktimes.items():
             if l == 0:
@@ -290,16 +290,16 @@ def main():
             if alg.get(k):
                 gbs = alg[k] * GROUP / (v["ms_per_launch"] * 1e-3) / 1e9
                 v.update({"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak})
-        casc_ms = sum(kern[k]["ms_per_launch"] for k in ("k_stage0", "k_dense", "k_tail") if k in kern)
+        casc_ms = sum(kern[k]["ms_per_launch"] for k in ("k_scan", "k_tail") if k in kern)
         l1_peak = 148 * 128 * sm_max * 1e6 / 1e9               # GB/s: 148 SMs x 128 B/clk x max SM clock
         casc_gbs = gather_bytes * GROUP / (casc_ms * 1e-3) / 1e9 if casc_ms else 0.0
         dominant = max(kern, key=lambda k: kern[k]["ms_per_launch"]) if kern else None
-        if dominant in ("k_stage0", "k_dense", "k_tail"):
-            roof = {"kernel": "cascade (k_stage0+k_dense+k_tail)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
+        if dominant in ("k_scan", "k_tail"):
+            roof = {"kernel": "cascade (k_scan+k_tail)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
                     "unit": "GB/s", "frac": casc_gbs / l1_peak, "traffic": None,
                     "note": "gather/threshold work: bounded by L1/shared-memory throughput (148 SM x 128 B/clk x "
                             f"{sm_max:.0f} MHz), not HBM; algorithmic bytes = 4 B x (8 norm corners per window + "
-                            "8.67 corners per weak classifier)"}
+                            "7.5 corners per weak classifier)"}
         else:
             v = kern.get(dominant, {})
             roof = {"kernel": dominant, "bound": v.get("bound", "hbm"), "achieved": v.get("achieved"), "peak": hbm_peak,
@@ -315,7 +315,7 @@ def main():
                    "sample": f"{cn} of the step's {nF} frames in {cdt:.1f} s, cv2 detectMultiScale, "
                              f"{os.cpu_count()} host cpus"}
         groups = (nF + GROUP - 1) // GROUP
-        launches_per_step = groups * 8                          # resize, colsum, carry, integral, stage0, dense, tail, group
+        launches_per_step = groups * 7                          # resize, colsum, carry, integral, scan, tail, group
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,

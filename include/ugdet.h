@@ -51,9 +51,9 @@ typedef struct {
     uint8_t skin_lower[3];    /* Y,Cr,Cb  default 0,133,77               (structure.cc:75-78)        */
     uint8_t skin_upper[3];    /* Y,Cr,Cb  default 255,173,127            (structure.cc:79-82)        */
     uint8_t _pad[2];
-    int32_t dense_stages;     /* engine tuning: cascade stages evaluated densely (one lane per grid
-                                 position) before survivors are compacted into the work queue;
-                                 0 = engine default.  Does not change results.                       */
+    int32_t dense_stages;     /* engine tuning: cascade stages evaluated inside the scan tiles before
+                                 survivors move to the global work queue; 0 = engine default.
+                                 Does not change results.                                            */
     int32_t max_raw_per_frame;/* capacity of the per-frame candidate list fed to groupRectangles;
                                  0 = engine default (8192)                                           */
 } ugd_params;
@@ -95,8 +95,8 @@ enum { UGD_K_PREPROCESS = 0,    /* BGR -> gray + skin mask + histogram          
        UGD_K_COLSUM,            /* integral phase 1: per-strip column sums            (a8)           */
        UGD_K_CARRY,             /* integral phase 2: scan of strip sums               (a8)           */
        UGD_K_INTEGRAL,          /* integral phase 3: S and SQ planes                  (a8)           */
-       UGD_K_STAGE0,            /* variance norm + stage 0 at every grid position     (a9)           */
-       UGD_K_DENSE,             /* x-skip resolve + dense stages + queue compaction   (a9)           */
+       UGD_K_SCAN,              /* tiled window scan: variance norm, x-skip, in-tile
+                                   stages with block-wide compaction                  (a9)           */
        UGD_K_TAIL,              /* queued windows, remaining stages                   (a9)           */
        UGD_K_GROUP,             /* groupRectangles + clip + skin post-filter          (a10-a12)      */
        UGD_K_COUNT };

@@ -1,6 +1,7 @@
 // C ABI of libugdet.so (include/ugdet.h): detector object, device buffers, launch sequence.
 // Host orchestration only -- all arithmetic of the path happens in the kernels of k_*.cu.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -29,9 +30,9 @@ struct DevPtr {                       // grow-only device allocation
 
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
-    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_pos;
+    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_scan;
     void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release(); wk_colsum.release();
-                     wk_carry.release(); wk_integral.release(); wk_pos.release(); }
+                     wk_carry.release(); wk_integral.release(); wk_scan.release(); }
 };
 
 std::mutex g_const_mu;
@@ -45,13 +46,13 @@ struct ugd_detector {
     const Cascade* casc = nullptr;
     ugd_params prm{};
     int device = 0, max_w = 0, max_h = 0, max_batch = 1;
-    int dense_stages = 1, dense_nodes = 0, rawcap = 8192;
+    int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 12;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
     DevPtr nodeA, nodeB, nodeC, st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
-    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, posv, queue, qcount, raw, rawsum,
+    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, queue, qcount, raw, rawsum,
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
     // host staging (pinned)
     ugd_rect* h_out = nullptr; int* h_counts = nullptr; unsigned long long* h_ctr = nullptr;
@@ -99,7 +100,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_colsum, dp->host.wk_colsum))) return rc;
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_integral, dp->host.wk_integral))) return rc;
-    if ((rc = upload(d, dp->wk_pos, dp->host.wk_pos))) return rc;
+    if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
     *out = dp.get();
     d->plans[key] = std::move(dp);
@@ -134,9 +135,7 @@ int bind_constants(ugd_detector* d) {
     std::lock_guard<std::mutex> lk(g_const_mu);
     if (g_const_owner == d) return UGD_OK;
     const Cascade& c = *d->casc;
-    CK(upload_dense_nodes(c.packed.data(), d->dense_nodes, d->stream));
-    CK(upload_dense_stage_table(c.stage_first_node.data(), c.stage_thr.data(), d->dense_stages + 1, d->stream));
-    CK(cudaStreamSynchronize(d->stream));
+    CK(upload_scan_constants(c, d->dense_stages, d->stream));
     g_const_owner = d;
     return UGD_OK;
 }
@@ -157,8 +156,7 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->SQ.reserve(F * p.int_ints * 4 + 256));
     CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
     CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
-    CK(d->posv.reserve(F * p.pos_entries * 4 + 256));
-    CK(d->queue.reserve(F * p.pos_entries * 8 + 256));
+    CK(d->queue.reserve(F * p.pos_entries * 16 + 256));
     CK(d->qcount.reserve(F * 4));
     CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
     CK(d->rawsum.reserve(F * d->rawcap * sizeof(double)));
@@ -214,8 +212,9 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.pyr = d->pyr.as<uint8_t>(); b.pyr_stride = p.pyr_bytes;
     b.S = d->S.as<int32_t>(); b.SQ = d->SQ.as<int32_t>(); b.int_stride = p.int_ints;
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
-    b.posv = d->posv.as<float>(); b.pos_stride = p.pos_entries;
-    b.queue = d->queue.as<uint2>(); b.qcount = d->qcount.as<int>();
+    b.pos_stride = p.pos_entries;
+    b.queue = d->queue.as<uint4>(); b.qcount = d->qcount.as<int>();
+    b.tile_min = d->tile_min;
     b.raw = d->raw.as<ugd_rect>(); b.rawsum = d->rawsum.as<double>(); b.rawcap = d->rawcap; b.rawcount = d->rawcount.as<int>();
     b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
     b.grp_scratch = d->grp.as<int>(); b.grp_stride = 10 * (size_t)d->rawcap;
@@ -244,18 +243,16 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 5);
     launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
     mark(d, 6);
-    launch_stage0(b, dp->wk_pos.as<WorkItem>(), (int)p.wk_pos.size(), st);
+    launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), st);
     mark(d, 7);
-    launch_dense(b, dp->wk_pos.as<WorkItem>(), (int)p.wk_pos.size(), st);
-    mark(d, 8);
     int tail_blocks = 0;
     if (d->dense_stages < c.nstages() && !p.levels.empty()) {
         tail_blocks = std::max(1, (d->sm_count * 8 + nframes - 1) / nframes);
         launch_tail(b, tail_blocks, st);
     }
-    mark(d, 9);
+    mark(d, 8);
     launch_group(b, st);
-    mark(d, 10);
+    mark(d, 9);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(d->h_out, b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(d->h_counts, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
@@ -285,7 +282,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     d->ctr.levels = (int64_t)p.levels.size();
     d->ctr.level_pixels = p.level_pixels;
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 1, tail_blocks ? 1 : 0, 1};
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, tail_blocks ? 1 : 0, 1};
         for (int k = 0; k < UGD_K_COUNT; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
@@ -396,8 +393,9 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     if (!(d->prm.scale_factor > 1.0)) return UGD_ERR_ARG;
     d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
     d->rawcap = d->prm.max_raw_per_frame > 0 ? (int)round_up((size_t)d->prm.max_raw_per_frame, 4) : 8192;
-    // dense stages: default 2 (stage 0 in k_stage0, stage 1 in k_dense), bounded by the __constant__ budget
-    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 3;
+    // in-tile stages: default 8, bounded by the __constant__ node budget
+    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 8;
+    if (const char* e = getenv("UGD_TILE_MIN")) d->tile_min = atoi(e);
     D = std::min(D, std::min(d->casc->nstages(), 63));
     while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;
     if (d->casc->stage_first_node[D] > kMaxDenseNodes) return UGD_ERR_UNSUPPORTED;
@@ -427,7 +425,7 @@ void ugd_destroy(ugd_detector* d) {
     for (auto& kv : d->plans) kv.second->release();
     DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
-                     &d->carryS, &d->carryQ, &d->posv, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
+                     &d->carryS, &d->carryQ, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};
     for (DevPtr* p : all) p->release();
     if (d->h_out) cudaFreeHost(d->h_out);
@@ -481,7 +479,7 @@ int ugd_get_kernel_times(const ugd_detector* d, float* t, int64_t* l) {
 
 const char* ugd_kernel_name(int k) {
     static const char* names[UGD_K_COUNT] = {"k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry",
-                                             "k_integral", "k_stage0", "k_dense", "k_tail", "k_group"};
+                                             "k_integral", "k_scan", "k_tail", "k_group"};
     return k >= 0 && k < UGD_K_COUNT ? names[k] : "?";
 }
 

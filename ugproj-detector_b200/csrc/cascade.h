@@ -26,6 +26,14 @@ struct alignas(16) PackedNode {
 };
 static_assert(sizeof(PackedNode) == 48, "PackedNode layout");
 
+// Corner-list form of a node: feature = sum_j coef[j] * S[corner j], duplicates merged
+// (6, 8 or 9 distinct corners for the shipped cascades instead of 8 / 12).  Exact in int32.
+struct CornerNode {
+    int nc;                 // corners used, padded with coef 0 up to 6, 8, 9 or 12
+    int8_t cx[12], cy[12];  // corner position inside the window
+    int8_t coef[12];
+};
+
 struct Cascade {
     int win_w = 0, win_h = 0;
     bool old_format = false;
@@ -37,6 +45,7 @@ struct Cascade {
     std::vector<HostNode> nodes;
     // derived
     std::vector<PackedNode> packed;              // one per node, same order
+    std::vector<CornerNode> corners;             // one per node, same order
     std::vector<int32_t> stage_first_node;       // [nstages+1]
     int nstages() const { return (int)stage_thr.size(); }
     int ntrees() const { return (int)tree_first_node.size(); }

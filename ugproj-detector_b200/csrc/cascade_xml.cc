@@ -240,6 +240,7 @@ int validate_and_pack(Cascade& c, std::string& err) {
     int min_lsb = 1000; double max_bound = 0;
     c.stage_first_node.assign(c.nstages() + 1, 0);
     c.packed.resize(c.nodes.size());
+    c.corners.resize(c.nodes.size());
     for (int s = 0; s < c.nstages(); ++s) {
         double bound = 0;
         if (c.stage_ntrees[s] <= 0) { err = "stage without weak classifiers"; return UGD_ERR_PARSE; }
@@ -276,6 +277,32 @@ int validate_and_pack(Cascade& c, std::string& err) {
                 p.meta = (uint32_t)n.left | (uint32_t)n.right << 8 | ((uint32_t)(int)n.weight[0] & 0xffu) << 16 | ((uint32_t)(int)n.weight[1] & 0xffu) << 24;
                 p.meta2 = ((uint32_t)(int)n.weight[2] & 0xffu) | (k == nn - 1 ? 0x100u : 0u);
                 p.pad0 = p.pad1 = 0;
+                {   // corner list: merge duplicate corners, drop zero coefficients
+                    CornerNode cn{};
+                    int m = 0;
+                    int tx[12], ty[12], tc[12];
+                    for (int r = 0; r < 3; ++r) {
+                        int w = (int)n.weight[r];
+                        if (!w) continue;
+                        const int32_t* q = n.rect[r];
+                        const int px[4] = {q[0], q[0] + q[2], q[0], q[0] + q[2]};
+                        const int py[4] = {q[1], q[1], q[1] + q[3], q[1] + q[3]};
+                        const int sg[4] = {w, -w, -w, w};
+                        for (int e = 0; e < 4; ++e) {
+                            int f = 0;
+                            for (; f < m; ++f) if (tx[f] == px[e] && ty[f] == py[e]) break;
+                            if (f == m) { tx[m] = px[e]; ty[m] = py[e]; tc[m] = 0; ++m; }
+                            tc[f] += sg[e];
+                        }
+                    }
+                    int o = 0;
+                    for (int f = 0; f < m; ++f) {
+                        if (!tc[f]) continue;
+                        cn.cx[o] = (int8_t)tx[f]; cn.cy[o] = (int8_t)ty[f]; cn.coef[o] = (int8_t)tc[f]; ++o;
+                    }
+                    cn.nc = o <= 6 ? 6 : (o <= 8 ? 8 : (o <= 9 ? 9 : 12));   // padding entries: corner (0,0), coef 0
+                    c.corners[base + k] = cn;
+                }
                 for (int side = 0; side < 2; ++side) {
                     if ((side ? n.right : n.left) != 0) continue;
                     float lf = side ? n.right_val : n.left_val;

@@ -1,36 +1,324 @@
 // Window scan and cascade stage evaluation for sm_100a.
 //
-//   k_stage0 : one lane per grid position: variance normalisation + stage 0.  Lanes of a warp are
-//              x-adjacent windows, so every corner gather is one coalesced 128/256-byte request.
-//   k_dense  : resolves the oracle's sequential x-skip rule in closed form with ballots, runs the
-//              next few stages densely (cascade nodes broadcast from __constant__), then ballot/popc
-//              compacts the survivors into the per-frame work queue.
-//   k_tail   : persistent warps pull queued windows; the window's (win+1)^2 patch of S is staged in
-//              shared memory once, then the 32 lanes evaluate 32 weak classifiers of a stage in
-//              parallel (no divergence, conflict-light shared-memory gathers) and a warp reduction
-//              forms the stage sum.  Rejected windows free the whole warp at the next stage boundary.
+//   k_scan : one block = 8 grid rows of one level of one frame (one warp per row), walking the rows
+//            left to right in tiles of 32 x 8 windows.  Per tile:
+//              1. the (8*step+win) x (32*step+win) patch of the integral image S is staged in shared
+//                 memory (coalesced loads; for grid step 2 even/odd columns are de-interleaved so
+//                 that the 32 lanes of a warp always hit 32 consecutive banks);
+//              2. every lane computes the variance normalisation and stage 0 of its own window;
+//              3. the oracle's sequential x-skip rule is resolved in closed form with one ballot and
+//                 a run-parity carried along the row in a register;
+//              4. surviving windows are ballot/popc-compacted ACROSS the block into a dense list, and
+//                 stage by stage the list is re-evaluated and re-compacted, so every warp that works
+//                 has (almost) all lanes on live windows.  Node data is broadcast from __constant__
+//                 as merged corner lists (6/8/9 LDS + IMAD per weak classifier);
+//              5. when fewer than `tile_min` windows are left (or the in-tile stages are exhausted)
+//                 the survivors go to the frame's global work queue.
+//   k_tail : persistent warps pull queued windows; the window's (win+1)^2 patch of S is staged in
+//            shared memory once, then the 32 lanes evaluate 32 weak classifiers of a stage in
+//            parallel and a warp reduction forms the stage sum.
 //
-// Exactness: feature sums are int32 (exact because weights are small integers), the one rounding
-// step is val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, which are exact for
-// the shipped cascades (ugd_cascade_info.sum_exact), hence independent of summation order.
+// Exactness: feature sums are int32 (exact: weights are small integers), the one rounding step is
+// val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, exact for the shipped cascades
+// (ugd_cascade_info.sum_exact), hence independent of summation order.
 #include "kernels.cuh"
 
 namespace ugd {
 
-__constant__ PackedNode c_nodes[kMaxDenseNodes];
-__constant__ int c_stage_first_node[64];   // first node of dense stage s, s <= dense_stages
+__constant__ DNode c_dn[kMaxDenseNodes];
+__constant__ int c_stage_first_node[65];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[64];
+__constant__ ScanGeom c_geom;
 
-cudaError_t upload_dense_nodes(const PackedNode* nodes, int n, cudaStream_t st) {
-    if (n > kMaxDenseNodes) return cudaErrorInvalidValue;
-    return cudaMemcpyToSymbolAsync(c_nodes, nodes, sizeof(PackedNode) * (size_t)n, 0, cudaMemcpyHostToDevice, st);
-}
-cudaError_t upload_dense_stage_table(const int* first_node, const float* thr, int n, cudaStream_t st) {
-    cudaError_t e = cudaMemcpyToSymbolAsync(c_stage_first_node, first_node, sizeof(int) * (size_t)n, 0, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyToSymbolAsync(c_stage_thr, thr, sizeof(float) * (size_t)(n - 1), 0, cudaMemcpyHostToDevice, st);
+ScanGeom make_scan_geom(int win_w, int win_h) {
+    ScanGeom g{};
+    for (int si = 0; si < 2; ++si) {
+        const int step = si + 1;
+        g.TC[si] = 31 * step + win_w + 1;
+        g.TR[si] = (kScanRows - 1) * step + win_h + 1;
+        g.TCH[si] = si ? (g.TC[si] + 1) / 2 : 0;
+        g.TP[si] = si ? 2 * g.TCH[si] : g.TC[si];
+    }
+    g.tile_ints = std::max(g.TR[0] * g.TP[0], g.TR[1] * g.TP[1]);
+    return g;
 }
 
+static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     // byte offset
+    return 4 * (si ? y * g.TP[1] + (x & 1) * g.TCH[1] + (x >> 1) : y * g.TP[0] + x);
+}
+
+cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
+    const int nn = c.stage_first_node[dense_stages];
+    if (nn > kMaxDenseNodes || dense_stages > 64) return cudaErrorInvalidValue;
+    ScanGeom g = make_scan_geom(c.win_w, c.win_h);
+    for (int si = 0; si < 2; ++si) {
+        g.norm_off[si][0] = tile_off(g, si, 1, 1);
+        g.norm_off[si][1] = tile_off(g, si, c.win_w - 1, 1);
+        g.norm_off[si][2] = tile_off(g, si, 1, c.win_h - 1);
+        g.norm_off[si][3] = tile_off(g, si, c.win_w - 1, c.win_h - 1);
+    }
+    std::vector<DNode> dn((size_t)std::max(nn, 1));
+    for (int t = 0; t < c.ntrees(); ++t) {
+        const int base = c.tree_first_node[t];
+        for (int k = 0; k < c.tree_nnodes[t]; ++k) {
+            const int n = base + k;
+            if (n >= nn) continue;
+            const CornerNode& cn = c.corners[n];
+            const HostNode& h = c.nodes[n];
+            DNode& d = dn[n];
+            memset(&d, 0, sizeof d);
+            for (int j = 0; j < 12; ++j) {
+                d.coef[j] = cn.coef[j];
+                for (int si = 0; si < 2; ++si) d.off[si][j] = tile_off(g, si, cn.cx[j], cn.cy[j]);
+            }
+            d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
+                     (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
+            d.thr = h.thr; d.lval = h.left_val; d.rval = h.right_val;
+        }
+    }
+    cudaError_t e;
+    if ((e = cudaMemcpyToSymbolAsync(c_dn, dn.data(), sizeof(DNode) * dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, c.stage_first_node.data(), sizeof(int) * (size_t)(dense_stages + 1), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, c.stage_thr.data(), sizeof(float) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_geom, &g, sizeof g, 0, cudaMemcpyHostToDevice, st))) return e;
+    return cudaStreamSynchronize(st);      // dn is a local: the copy must finish before it goes away
+}
+
+__device__ __forceinline__ int near_thr(double sum, float thr) {
+    return fabs(sum - (double)thr) <= 1e-5 * fabs((double)thr);
+}
+
+// One in-tile stage for one window.  `t` points at the window's origin inside the shared tile; the
+// loop and every node field are warp-uniform, so node data is broadcast from the constant bank.
+#define TILE_AT(j) (d.coef[j] * *reinterpret_cast<const int*>(t + o[j]))
+template <bool STUMPS>
+__device__ __forceinline__ double tile_stage(int n0, int n1, int si, const char* __restrict__ t, float vnf) {
+    double sum = 0.0;
+    float leaf = 0.f;
+    int at = 0, k = 0;
+    for (int n = n0; n < n1; ++n) {
+        const DNode& d = c_dn[n];
+        const int32_t* o = d.off[si];
+        int r = TILE_AT(0) + TILE_AT(1) + TILE_AT(2) + TILE_AT(3) + TILE_AT(4) + TILE_AT(5);
+        const uint32_t meta = d.meta;
+        const int nc = meta & 255u;
+        if (nc > 6) {
+            r += TILE_AT(6) + TILE_AT(7);
+            if (nc > 8) {
+                r += TILE_AT(8);
+                if (nc > 9) r += TILE_AT(9) + TILE_AT(10) + TILE_AT(11);
+            }
+        }
+        const bool lt = __fmul_rn(__int2float_rn(r), vnf) < d.thr;
+        if (STUMPS) {
+            sum += (double)(lt ? d.lval : d.rval);
+        } else {
+            if (at == k) {
+                const int go = lt ? ((meta >> 8) & 255u) : ((meta >> 16) & 255u);
+                leaf = lt ? d.lval : d.rval;
+                at = go ? go : 255;
+            }
+            if (meta >> 24) { sum += (double)leaf; at = 0; k = 0; } else ++k;
+        }
+    }
+    return sum;
+}
+#undef TILE_AT
+
+__device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scale, int rw, int rh, int x, int y, double sum) {
+    int slot = atomicAdd(&b.rawcount[frame], 1);
+    if (slot < b.rawcap) {
+        ugd_rect r;
+        r.x = __float2int_rn(__fmul_rn((float)x, scale));
+        r.y = __float2int_rn(__fmul_rn((float)y, scale));
+        r.width = rw; r.height = rh;
+        b.raw[(size_t)frame * b.rawcap + slot] = r;
+        b.rawsum[(size_t)frame * b.rawcap + slot] = sum;
+    }
+}
+
+template <bool STUMPS>
+__global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
+    constexpr int NW = kScanRows, NT = NW * 32;
+    extern __shared__ int s_tile[];
+    __shared__ float s_vnf[NT];
+    __shared__ uint16_t s_id[2][NT];
+    __shared__ int s_cnt[NW];
+    __shared__ int s_qbase;
+    __shared__ unsigned int s_ctr[4];                  // evaluated, lowvar, near, weak
+
+    const WorkItem it = wk[blockIdx.x];
+    const int frame = blockIdx.y, tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const LevelInfo& Lg = b.levels[it.level];
+    const int sw = Lg.sw, sh = Lg.sh, P = Lg.P, step = Lg.step, nxg = Lg.nxg, nyg = Lg.nyg, nxg_pad = Lg.nxg_pad;
+    const float scale = Lg.scale;
+    const int rect_w = Lg.rect_w, rect_h = Lg.rect_h;
+    const uint32_t pos_off = Lg.pos_off;
+    const int si = step - 1;
+    const int TP = c_geom.TP[si], TCH = c_geom.TCH[si], TC = c_geom.TC[si], TR = c_geom.TR[si];
+    const int r0 = it.first;
+    const int row = r0 + w;
+    const bool row_valid = row < nyg;
+    const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
+    const int32_t* Q = b.SQ + (size_t)frame * b.int_stride + Lg.int_off;
+    const int ow = b.win_w, oh = b.win_h, D = b.dense_stages, nstages = b.nstages;
+    const double area = (double)((ow - 2) * (oh - 2));
+    const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
+    int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
+    if (tid < 4) s_ctr[tid] = 0;
+    int run_in = 0;                                    // stage-0 failure run ending just before this segment
+    unsigned weak = 0;                                 // lane 0 of each warp tallies weak classifiers
+
+    for (int xi0 = 0; xi0 < nxg; xi0 += 32) {
+        __syncthreads();                               // previous tile fully consumed
+        // ---- 1. stage the S tile ----
+        {
+            const int X0 = xi0 * step, Y0 = r0 * step;
+            for (int r = w; r < TR; r += NW) {
+                const int32_t* src = S + (size_t)min(Y0 + r, sh) * P;
+                int* dst = s_tile + r * TP;
+                for (int c = lane; c < TC; c += 32) {
+                    const int v = src[min(X0 + c, sw)];
+                    dst[si ? (c & 1) * TCH + (c >> 1) : c] = v;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- 2. variance normalisation + stage 0, every lane ----
+        const int xi = xi0 + lane;
+        const bool valid = row_valid && xi < nxg;
+        const int x = valid ? xi * step : 0, y = valid ? row * step : 0;
+        const char* t = reinterpret_cast<const char*>(s_tile + (w * step) * TP + lane);
+        float vnf = 1.f;
+        bool ok = false;
+        {
+            const int32_t* no = c_geom.norm_off[si];
+            const int vs = *reinterpret_cast<const int*>(t + no[0]) - *reinterpret_cast<const int*>(t + no[1]) -
+                           *reinterpret_cast<const int*>(t + no[2]) + *reinterpret_cast<const int*>(t + no[3]);
+            const int32_t* q = Q + (size_t)y * P + x;
+            const uint32_t vq = (uint32_t)q[P + 1] - (uint32_t)q[P + ow - 1] - (uint32_t)q[(oh - 1) * P + 1] + (uint32_t)q[(oh - 1) * P + ow - 1];
+            double nf = area * (double)vq - (double)vs * (double)vs;
+            if (nf > 0.0) {
+                nf = sqrt(nf);
+                vnf = (float)(1.0 / nf);
+                ok = area * (double)vnf < 1e-1;
+            }
+            if (!ok) vnf = 1.f;
+        }
+        double sum = tile_stage<STUMPS>(c_stage_first_node[0], c_stage_first_node[1], si, t, vnf);
+        const float thr0 = c_stage_thr[0];
+        const bool pass0 = !(sum < (double)thr0);
+        // ---- 3. x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
+        //         ending at i-1 has even length (a failure is only seen at evaluated positions) ----
+        const bool f0 = valid && ok && !pass0;
+        const unsigned F = __ballot_sync(0xffffffffu, f0);
+        const unsigned inv = ~F & below;
+        const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
+        run_in = (F == 0xffffffffu) ? run_in + 32 : __clz((int)~F);
+        const bool evaluated = valid && !(run & 1);
+        bool alive = evaluated && ok && pass0;
+        {
+            const unsigned em = __ballot_sync(0xffffffffu, evaluated);
+            const unsigned lm = __ballot_sync(0xffffffffu, evaluated && !ok);
+            const unsigned s0 = __ballot_sync(0xffffffffu, evaluated && ok);
+            const unsigned nm = __ballot_sync(0xffffffffu, evaluated && ok && near_thr(sum, thr0));
+            if (lane == 0) {
+                atomicAdd(&s_ctr[0], __popc(em));
+                if (lm) atomicAdd(&s_ctr[1], __popc(lm));
+                if (nm) atomicAdd(&s_ctr[2], __popc(nm));
+                weak += __popc(s0) * (unsigned)(c_stage_first_node[1] - c_stage_first_node[0]);
+            }
+        }
+        if (map && valid) {
+            if (!evaluated) map[row * nxg_pad + xi] = kMapSkip;
+            else if (!ok) map[row * nxg_pad + xi] = kMapLowVar;
+            else if (!pass0) map[row * nxg_pad + xi] = 0;
+        }
+        s_vnf[tid] = vnf;
+        // ---- 4. block-wide compaction, then stage by stage on the dense list ----
+        int cur = 0, n, s = 1;
+        {
+            const unsigned am = __ballot_sync(0xffffffffu, alive);
+            if (lane == 0) s_cnt[w] = __popc(am);
+            __syncthreads();
+            int base = 0, tot = 0;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) { const int cj = s_cnt[j]; if (j < w) base += cj; tot += cj; }
+            if (alive) s_id[0][base + __popc(am & below)] = (uint16_t)tid;
+            n = tot;
+            __syncthreads();
+        }
+        if (nstages == 1 && alive) {                   // one-stage cascade: accepted right here
+            emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
+            if (map) map[row * nxg_pad + xi] = 1;
+        }
+        while (s < D && n > 0 && !(n < b.tile_min && s >= 2)) {
+            const int i = tid;
+            const bool act = i < n;
+            bool pass = false;
+            int my = 0;
+            if (w * 32 < n) {                           // warp-uniform: this warp has list entries
+                my = act ? s_id[cur][i] : s_id[cur][0];
+                const char* tw = reinterpret_cast<const char*>(s_tile + ((my >> 5) * step) * TP + (my & 31));
+                const float v = s_vnf[my];
+                sum = tile_stage<STUMPS>(c_stage_first_node[s], c_stage_first_node[s + 1], si, tw, v);
+                const float thr = c_stage_thr[s];
+                pass = act && !(sum < (double)thr);
+                const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));
+                if (lane == 0) {
+                    if (nm) atomicAdd(&s_ctr[2], __popc(nm));
+                    weak += (unsigned)min(32, n - w * 32) * (unsigned)(c_stage_first_node[s + 1] - c_stage_first_node[s]);
+                }
+                if (act && !pass && map) map[(r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31)] = (int16_t)s;
+                if (pass && s + 1 == nstages) {
+                    emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + (my & 31)) * step, (r0 + (my >> 5)) * step, sum);
+                    if (map) map[(r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31)] = (int16_t)nstages;
+                    pass = false;                       // accepted: nothing left to do for it
+                }
+            }
+            const unsigned pm = __ballot_sync(0xffffffffu, pass);
+            __syncthreads();                            // everyone has read s_cnt / s_id[cur] of this round
+            if (lane == 0) s_cnt[w] = __popc(pm);
+            __syncthreads();
+            int base = 0, tot = 0;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) { const int cj = s_cnt[j]; if (j < w) base += cj; tot += cj; }
+            if (pass) s_id[cur ^ 1][base + __popc(pm & below)] = (uint16_t)my;
+            cur ^= 1; n = tot; ++s;
+            __syncthreads();
+        }
+        // ---- 5. survivors -> the frame's work queue (they resume at stage s) ----
+        if (n > 0 && s < nstages) {
+            if (tid == 0) s_qbase = atomicAdd(&b.qcount[frame], n);
+            __syncthreads();
+            if (tid < n) {
+                const int my = s_id[cur][tid];
+                const int qx = (xi0 + (my & 31)) * step, qy = (r0 + (my >> 5)) * step;
+                b.queue[(size_t)frame * b.pos_stride + s_qbase + tid] =
+                    make_uint4((uint32_t)qx | (uint32_t)qy << 12 | (uint32_t)it.level << 24, __float_as_uint(s_vnf[my]), (uint32_t)s, 0u);
+            }
+        }
+    }
+    if (lane == 0 && weak) atomicAdd(&s_ctr[3], weak);
+    __syncthreads();
+    if (tid < 4 && s_ctr[tid]) {
+        const int slot[4] = {CTR_EVALUATED, CTR_LOWVAR, CTR_NEAR, CTR_WEAK};
+        atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + slot[tid]], (unsigned long long)s_ctr[tid]);
+    }
+}
+
+static int g_scan_smem = 0;
+
+void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (!nblocks) return;
+    const size_t smem = (size_t)make_scan_geom(b.win_w, b.win_h).tile_ints * sizeof(int);
+    if (b.stumps_only) k_scan<true><<<dim3(nblocks, b.nframes), kScanRows * 32, smem, st>>>(b, wk);
+    else k_scan<false><<<dim3(nblocks, b.nframes), kScanRows * 32, smem, st>>>(b, wk);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tail: one warp per queued window, lanes over the weak classifiers of a stage.
+// ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ int rect_sum(const int32_t* __restrict__ p, uint32_t r, int pitch) {
     const int x = r & 255u, y = (r >> 8) & 255u, w = (r >> 16) & 255u, h = r >> 24;
     const int32_t* a = p + y * pitch + x;
@@ -40,7 +328,6 @@ __device__ __forceinline__ int rect_sum(const int32_t* __restrict__ p, uint32_t 
 
 __device__ __forceinline__ int sext8(uint32_t v) { return (int)(int8_t)(v & 255u); }
 
-// Feature response of one node at the window whose integral origin is `p` (pitch in ints).
 __device__ __forceinline__ float node_val(const int32_t* __restrict__ p, int pitch, uint32_t r0, uint32_t r1, uint32_t r2,
                                           uint32_t meta, uint32_t meta2, float vnf) {
     int r = sext8(meta >> 16) * rect_sum(p, r0, pitch) + sext8(meta >> 24) * rect_sum(p, r1, pitch);
@@ -48,183 +335,6 @@ __device__ __forceinline__ float node_val(const int32_t* __restrict__ p, int pit
     return __fmul_rn(__int2float_rn(r), vnf);
 }
 
-// One densely evaluated stage: nodes [n0, n1) from __constant__ (uniform addresses -> broadcast).
-// Trees are walked with a uniform loop over their nodes; a lane only "takes" the node it is at.
-__device__ __forceinline__ double dense_stage(int n0, int n1, const int32_t* __restrict__ p, int pitch, float vnf) {
-    double sum = 0.0, leaf = 0.0;
-    int at = 0, k = 0;                       // lane's current node within the tree; uniform position
-    for (int n = n0; n < n1; ++n) {
-        const PackedNode& nd = c_nodes[n];
-        const uint32_t meta = nd.meta, meta2 = nd.meta2;
-        const float val = node_val(p, pitch, nd.r0, nd.r1, nd.r2, meta, meta2, vnf);
-        const bool lt = val < __uint_as_float(nd.thr_bits);
-        if (at == k) {
-            const int go = lt ? (meta & 255u) : ((meta >> 8) & 255u);
-            leaf = lt ? nd.lval : nd.rval;
-            at = go ? go : 255;
-        }
-        if (meta2 & 0x100u) { sum += leaf; at = 0; k = 0; } else ++k;
-    }
-    return sum;
-}
-
-struct PosInfo { int level, row, xi; bool valid; };
-
-__device__ __forceinline__ int near_thr(double sum, float thr) {
-    return fabs(sum - (double)thr) <= 1e-5 * fabs((double)thr);
-}
-
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_stage0(DevBufs b, const WorkItem* __restrict__ wk) {
-    const WorkItem it = wk[blockIdx.x];
-    const LevelInfo& L = b.levels[it.level];
-    const int frame = blockIdx.y;
-    const int pos = it.first + threadIdx.x;
-    const int nxg_pad = L.nxg_pad;
-    const int row = pos / nxg_pad, xi = pos - row * nxg_pad;
-    float* outp = b.posv + (size_t)frame * b.pos_stride + L.pos_off + pos;
-    if (row >= L.nyg) return;                       // tail of the last block (rounded up to 256)
-    if (xi >= L.nxg) { *outp = 0.f; return; }
-    const int step = L.step, P = L.P;
-    const int x = xi * step, y = row * step;
-    const size_t o = (size_t)frame * b.int_stride + L.int_off + (size_t)y * P + x;
-    const int32_t* S = b.S + o;
-    const int32_t* Q = b.SQ + o;
-    const int ow = b.win_w, oh = b.win_h;
-    // A.3: variance normalisation on the inner (ow-2)x(oh-2) rectangle
-    const int a0 = P + 1, a1 = P + ow - 1, a2 = (oh - 1) * P + 1, a3 = (oh - 1) * P + ow - 1;
-    const int vs = S[a0] - S[a1] - S[a2] + S[a3];
-    const uint32_t vq = (uint32_t)Q[a0] - (uint32_t)Q[a1] - (uint32_t)Q[a2] + (uint32_t)Q[a3];
-    const double area = (double)((ow - 2) * (oh - 2));
-    double nf = area * (double)vq - (double)vs * (double)vs;
-    float res = 0.f;                                // 0 = low variance
-    if (nf > 0.0) {
-        nf = sqrt(nf);
-        const float vnf = (float)(1.0 / nf);
-        if (area * (double)vnf < 1e-1) {
-            const double sum = dense_stage(c_stage_first_node[0], c_stage_first_node[1], S, P, vnf);
-            const float thr = c_stage_thr[0];
-            res = sum < (double)thr ? -1.f : vnf;
-            if (near_thr(sum, thr)) atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + CTR_NEAR], 1ull);
-        }
-    }
-    *outp = res;
-}
-
-void launch_stage0(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
-    if (nblocks) k_stage0<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
-}
-
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, const LevelInfo& L, int x, int y, double sum) {
-    int slot = atomicAdd(&b.rawcount[frame], 1);
-    if (slot < b.rawcap) {
-        const float s = L.scale;
-        ugd_rect r;
-        r.x = __float2int_rn(__fmul_rn((float)x, s));
-        r.y = __float2int_rn(__fmul_rn((float)y, s));
-        r.width = L.rect_w; r.height = L.rect_h;
-        b.raw[(size_t)frame * b.rawcap + slot] = r;
-        b.rawsum[(size_t)frame * b.rawcap + slot] = sum;
-    }
-}
-
-__global__ void __launch_bounds__(256) k_dense(DevBufs b, const WorkItem* __restrict__ wk) {
-    __shared__ unsigned int s_eval, s_lowvar, s_near, s_weak;
-    const WorkItem it = wk[blockIdx.x];
-    const LevelInfo& L = b.levels[it.level];
-    const int frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
-    if (tid == 0) { s_eval = 0; s_lowvar = 0; s_near = 0; s_weak = 0; }
-    __syncthreads();
-    const int pos = it.first + tid;
-    const int nxg_pad = L.nxg_pad;
-    const int row = pos / nxg_pad, xi = pos - row * nxg_pad;     // row is warp-uniform (nxg_pad % 32 == 0)
-    const float* pv = b.posv + (size_t)frame * b.pos_stride + L.pos_off;
-    const bool valid = row < L.nyg && xi < L.nxg;
-    const float v = valid ? pv[pos] : 0.f;
-    if (row < L.nyg) {
-        // ---- x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
-        //      that ends at i-1 has even length (A.3; a failure is only seen at evaluated positions,
-        //      and the position after a non-failure is always evaluated) ----
-        const unsigned F = __ballot_sync(0xffffffffu, v < 0.f);
-        int run_in = 0;                                          // length of the failure run ending just before this segment
-        for (int back = xi - lane - 32; back >= 0; back -= 32) {
-            const float pvb = pv[row * nxg_pad + back + lane];
-            const unsigned m = __ballot_sync(0xffffffffu, pvb < 0.f);
-            const int t = __clz((int)~m);                       // consecutive failures at the top of the word
-            run_in += t;
-            if (t < 32) break;
-        }
-        const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
-        const unsigned inv = ~F & below;
-        const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
-        const bool evaluated = valid && !(run & 1);
-        bool alive = evaluated && v > 0.f;
-        int16_t code = !evaluated ? kMapSkip : (v == 0.f ? kMapLowVar : (v < 0.f ? (int16_t)0 : (int16_t)-100));
-        const unsigned em = __ballot_sync(0xffffffffu, evaluated);
-        const unsigned lm = __ballot_sync(0xffffffffu, evaluated && v == 0.f);
-        unsigned weak = 0;                                       // weak classifiers evaluated by this warp (lane 0's tally)
-        {   // stage 0 ran in k_stage0 for every evaluated, non-low-variance window
-            const unsigned s0 = __ballot_sync(0xffffffffu, evaluated && v != 0.f);
-            weak = __popc(s0) * (unsigned)(c_stage_first_node[1] - c_stage_first_node[0]);
-        }
-        if (lane == 0) { atomicAdd(&s_eval, __popc(em)); if (lm) atomicAdd(&s_lowvar, __popc(lm)); }
-        // ---- dense stages 1 .. D-1 ----
-        const int step = L.step, P = L.P;
-        const int x = xi * step, y = row * step;
-        const int32_t* S = b.S + (size_t)frame * b.int_stride + L.int_off + (size_t)y * P + x;
-        const int D = b.dense_stages;
-        double sum = 0.0;
-        for (int s = 1; s < D; ++s) {
-            const unsigned al = __ballot_sync(0xffffffffu, alive);
-            if (!al) break;
-            weak += __popc(al) * (unsigned)(c_stage_first_node[s + 1] - c_stage_first_node[s]);
-            if (alive) {
-                sum = dense_stage(c_stage_first_node[s], c_stage_first_node[s + 1], S, P, v);
-                const float thr = c_stage_thr[s];
-                if (near_thr(sum, thr)) atomicAdd(&s_near, 1u);
-                if (sum < (double)thr) { alive = false; code = (int16_t)s; }
-            }
-        }
-        if (D >= b.nstages) {
-            if (alive) {
-                if (D == 1) sum = dense_stage(c_stage_first_node[0], c_stage_first_node[1], S, P, v);   // one-stage cascade
-                emit_raw(b, frame, L, x, y, sum); code = (int16_t)b.nstages;
-            }
-        } else {
-            // ---- ballot/popc compaction into the frame's work queue ----
-            const unsigned am = __ballot_sync(0xffffffffu, alive);
-            if (am) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&b.qcount[frame], __popc(am));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (alive) {
-                    const int slot = base + __popc(am & below);
-                    b.queue[(size_t)frame * b.pos_stride + slot] =
-                        make_uint2((uint32_t)x | (uint32_t)y << 12 | (uint32_t)it.level << 24, __float_as_uint(v));
-                }
-            }
-        }
-        if (lane == 0 && weak) atomicAdd(&s_weak, weak);
-        if (b.stage_map && frame == 0 && valid && code != -100) b.stage_map[L.pos_off + pos] = code;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long* c = b.counters + (size_t)frame * kCtrPerFrame;
-        if (s_eval) atomicAdd(&c[CTR_EVALUATED], (unsigned long long)s_eval);
-        if (s_lowvar) atomicAdd(&c[CTR_LOWVAR], (unsigned long long)s_lowvar);
-        if (s_near) atomicAdd(&c[CTR_NEAR], (unsigned long long)s_near);
-        if (s_weak) atomicAdd(&c[CTR_WEAK], (unsigned long long)s_weak);
-    }
-}
-
-void launch_dense(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
-    if (nblocks) k_dense<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
-}
-
-// ------------------------------------------------------------------------------------------------
-// Tail: one warp per queued window, lanes over the weak classifiers of a stage.
-// ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
@@ -237,24 +347,29 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
     const int PW = b.win_w + 1, PH = b.win_h + 1, PN = PW * PH;
     int32_t* patch = s_patch + warp * PN;
     const int qn = min(b.qcount[frame], (int)b.pos_stride);
-    const uint2* queue = b.queue + (size_t)frame * b.pos_stride;
-    const int nstages = b.nstages, D = b.dense_stages;
+    const uint4* queue = b.queue + (size_t)frame * b.pos_stride;
+    const int nstages = b.nstages;
     unsigned near_cnt = 0;
     unsigned long long weak_cnt = 0;                          // per-lane tally of evaluated nodes
     for (int i = blockIdx.x * 8 + warp; i < qn; i += gridDim.x * 8) {
-        const uint2 e = queue[i];
+        const uint4 e = queue[i];
         const int x = e.x & 4095u, y = (e.x >> 12) & 4095u, level = e.x >> 24;
         const float vnf = __uint_as_float(e.y);
         const LevelInfo& L = b.levels[level];
         const int P = L.P;
         const int32_t* S = b.S + (size_t)frame * b.int_stride + L.int_off + (size_t)y * P + x;
         __syncwarp();
-        for (int idx = lane; idx < PN; idx += 32) {
-            const int r = idx / PW, c = idx - r * PW;
-            patch[idx] = S[r * P + c];
+        {
+            int r = 0, c = lane;                               // flattened patch index -> (row, col), incrementally
+            while (c >= PW) { c -= PW; ++r; }
+            for (int idx = lane; idx < PN; idx += 32) {
+                patch[idx] = S[r * P + c];
+                c += 32;
+                while (c >= PW) { c -= PW; ++r; }
+            }
         }
         __syncwarp();
-        int s = D;
+        int s = (int)e.z;
         double sum = 0.0;
         for (; s < nstages; ++s) {
             const int t0 = b.stage_first_tree[s], nt = b.stage_ntrees[s];
@@ -283,7 +398,7 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
             if (sum < (double)thr) break;
         }
         if (lane == 0) {
-            if (s == nstages) emit_raw(b, frame, L, x, y, sum);
+            if (s == nstages) emit_raw(b, frame, L.scale, L.rect_w, L.rect_h, x, y, sum);
             if (b.stage_map && frame == 0) {
                 const int step = L.step;
                 b.stage_map[L.pos_off + (y / step) * L.nxg_pad + x / step] = (int16_t)s;
@@ -304,6 +419,13 @@ cudaError_t init_kernel_attributes(int win_w, int win_h) {
         cudaError_t e = cudaFuncSetAttribute(k_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         g_tail_smem = smem;
+    }
+    const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int);
+    if (scan_smem > g_scan_smem) {
+        cudaError_t e = cudaFuncSetAttribute(k_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+        if (e != cudaSuccess) return e;
+        g_scan_smem = scan_smem;
     }
     return cudaSuccess;
 }

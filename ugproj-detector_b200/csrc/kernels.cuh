@@ -11,7 +11,26 @@
 
 namespace ugd {
 
-constexpr int kMaxDenseNodes = 1024;      // nodes of the densely evaluated stages, held in __constant__
+constexpr int kMaxDenseNodes = 384;       // nodes of the in-tile stages, held in __constant__ (160 B each)
+constexpr int kScanRows = 8;              // grid rows (= warps) per scan block; a tile is 32 x kScanRows windows
+
+// In-tile node: merged corner list.  BYTE offsets into the shared-memory tile are precomputed for the
+// two tile layouts (index 0: grid step 1; index 1: grid step 2, even/odd columns de-interleaved).
+// Every field is a full 32-bit word so the uniform datapath can fetch it with LDCU.128 and use it
+// without unpacking.
+struct alignas(16) DNode {
+    int32_t off[2][12];
+    int32_t coef[12];
+    float   thr, lval, rval;
+    uint32_t meta;                        // nc | lnode << 8 | rnode << 16 | last << 24
+};
+static_assert(sizeof(DNode) == 160, "DNode layout");
+
+struct ScanGeom {                          // per layout (step 1 / step 2)
+    int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
+    int32_t norm_off[2][4];                // tile BYTE offsets of the 4 variance-normalisation corners
+    int tile_ints;                         // ints of shared memory for the tile
+};
 constexpr int kCtrPerFrame = 8;           // per-frame device counters (see enum below)
 enum { CTR_EVALUATED = 0, CTR_LOWVAR, CTR_QUEUED, CTR_RAW, CTR_GROUPED, CTR_NEAR, CTR_RAW_OVERFLOW, CTR_WEAK };
 
@@ -40,8 +59,9 @@ struct DevBufs {
     int32_t* S; int32_t* SQ; size_t int_stride;
     uint32_t* carryS; uint32_t* carryQ; size_t carry_stride;
     // window scan
-    float* posv; size_t pos_stride;                   // >0 vnf (alive after stage 0), 0 low variance, -1 failed stage 0
-    uint2* queue; int* qcount;                        // per frame: pos_stride entries, count
+    size_t pos_stride;                                // padded grid positions per frame
+    uint4* queue; int* qcount;                        // per frame: pos_stride entries {x|y<<12|level<<24, vnf, stage, -}, count
+    int tile_min;                                     // hand a tile's survivors to the queue once fewer than this remain
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
     int16_t* stage_map;                               // frame 0 only, padded layout; may be null
     // grouping / output
@@ -51,11 +71,10 @@ struct DevBufs {
     unsigned long long* counters;                     // [nframes][kCtrPerFrame]
 };
 
-// dense-stage nodes -> __constant__ (call before launching stage0/dense with a new cascade)
-cudaError_t upload_dense_nodes(const PackedNode* nodes, int n, cudaStream_t st);
-
-// first_node: n entries (stage s covers nodes [first_node[s], first_node[s+1])), thr: n-1 entries
-cudaError_t upload_dense_stage_table(const int* first_node, const float* thr, int n, cudaStream_t st);
+// Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
+// to __constant__ (call before launching k_scan with a new cascade).
+ScanGeom make_scan_geom(int win_w, int win_h);
+cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
 void launch_equalize(const DevBufs& b, cudaStream_t st);
@@ -63,8 +82,7 @@ void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
-void launch_stage0(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
-void launch_dense(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
+void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_tail(const DevBufs& b, int blocks_per_frame, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);
 cudaError_t init_kernel_attributes(int win_w, int win_h);

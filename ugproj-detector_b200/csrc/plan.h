@@ -39,7 +39,7 @@ struct Plan {
     int w = 0, h = 0;
     std::vector<LevelInfo> levels;
     std::vector<uint32_t> xtab, ytab;           // entry = i0 | c1 << 16  (c1 in 0..256)
-    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_integral, wk_pos;
+    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_integral, wk_scan;
     // per-frame sizes
     size_t pyr_bytes = 0, int_ints = 0, pos_entries = 0, carry_ints = 0, map_entries = 0;
     int64_t level_pixels = 0, grid_windows = 0;
