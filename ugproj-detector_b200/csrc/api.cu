@@ -396,7 +396,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     // in-tile stages: default 8, bounded by the __constant__ node budget
     int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 8;
     if (const char* e = getenv("UGD_TILE_MIN")) d->tile_min = atoi(e);
-    D = std::min(D, std::min(d->casc->nstages(), 63));
+    D = std::min(D, std::min(d->casc->nstages(), kMaxDenseStages));
     while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;
     if (d->casc->stage_first_node[D] > kMaxDenseNodes) return UGD_ERR_UNSUPPORTED;
     d->dense_stages = D; d->dense_nodes = d->casc->stage_first_node[D];

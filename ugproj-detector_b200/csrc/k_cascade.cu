@@ -26,8 +26,8 @@
 namespace ugd {
 
 __constant__ DNode c_dn[kMaxDenseNodes];
-__constant__ int c_stage_first_node[65];   // first in-tile node of stage s (s <= dense_stages)
-__constant__ float c_stage_thr[64];
+__constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
+__constant__ float c_stage_thr[kMaxDenseStages];
 __constant__ ScanGeom c_geom;
 
 ScanGeom make_scan_geom(int win_w, int win_h) {
@@ -49,7 +49,7 @@ static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     //
 
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
     const int nn = c.stage_first_node[dense_stages];
-    if (nn > kMaxDenseNodes || dense_stages > 64) return cudaErrorInvalidValue;
+    if (nn > kMaxDenseNodes || dense_stages > kMaxDenseStages) return cudaErrorInvalidValue;
     ScanGeom g = make_scan_geom(c.win_w, c.win_h);
     for (int si = 0; si < 2; ++si) {
         g.norm_off[si][0] = tile_off(g, si, 1, 1);
@@ -90,36 +90,58 @@ __device__ __forceinline__ int near_thr(double sum, float thr) {
 
 // One in-tile stage for one window.  `t` points at the window's origin inside the shared tile; the
 // loop and every node field are warp-uniform, so node data is broadcast from the constant bank.
-#define TILE_AT(j) (d.coef[j] * *reinterpret_cast<const int*>(t + o[j]))
+#define TILE_AT(d, o, j) ((d).coef[j] * *reinterpret_cast<const int*>(t + (o)[j]))
+// feature response r of one node: two independent IMAD chains, extra corners behind uniform branches
+__device__ __forceinline__ int node_resp(const DNode& d, int si, const char* __restrict__ t) {
+    const int32_t* o = d.off[si];
+    int a = TILE_AT(d, o, 0) + TILE_AT(d, o, 1) + TILE_AT(d, o, 2);
+    int c = TILE_AT(d, o, 3) + TILE_AT(d, o, 4) + TILE_AT(d, o, 5);
+    const int nc = d.meta & 255u;
+    if (nc > 6) {
+        a += TILE_AT(d, o, 6); c += TILE_AT(d, o, 7);
+        if (nc > 8) {
+            a += TILE_AT(d, o, 8);
+            if (nc > 9) { c += TILE_AT(d, o, 9); a += TILE_AT(d, o, 10); c += TILE_AT(d, o, 11); }
+        }
+    }
+    return a + c;
+}
+
 template <bool STUMPS>
 __device__ __forceinline__ double tile_stage(int n0, int n1, int si, const char* __restrict__ t, float vnf) {
+    if (STUMPS) {
+        // two nodes per trip, separate accumulators: twice the independent work in flight per warp
+        double s0 = 0.0, s1 = 0.0;
+        int n = n0;
+        for (; n + 1 < n1; n += 2) {
+            const DNode& d0 = c_dn[n];
+            const DNode& d1 = c_dn[n + 1];
+            const int r0 = node_resp(d0, si, t), r1 = node_resp(d1, si, t);
+            const bool l0 = __fmul_rn(__int2float_rn(r0), vnf) < d0.thr;
+            const bool l1 = __fmul_rn(__int2float_rn(r1), vnf) < d1.thr;
+            s0 += (double)(l0 ? d0.lval : d0.rval);
+            s1 += (double)(l1 ? d1.lval : d1.rval);
+        }
+        if (n < n1) {
+            const DNode& d0 = c_dn[n];
+            const bool l0 = __fmul_rn(__int2float_rn(node_resp(d0, si, t)), vnf) < d0.thr;
+            s0 += (double)(l0 ? d0.lval : d0.rval);
+        }
+        return s0 + s1;
+    }
     double sum = 0.0;
     float leaf = 0.f;
     int at = 0, k = 0;
     for (int n = n0; n < n1; ++n) {
         const DNode& d = c_dn[n];
-        const int32_t* o = d.off[si];
-        int r = TILE_AT(0) + TILE_AT(1) + TILE_AT(2) + TILE_AT(3) + TILE_AT(4) + TILE_AT(5);
         const uint32_t meta = d.meta;
-        const int nc = meta & 255u;
-        if (nc > 6) {
-            r += TILE_AT(6) + TILE_AT(7);
-            if (nc > 8) {
-                r += TILE_AT(8);
-                if (nc > 9) r += TILE_AT(9) + TILE_AT(10) + TILE_AT(11);
-            }
+        const bool lt = __fmul_rn(__int2float_rn(node_resp(d, si, t)), vnf) < d.thr;
+        if (at == k) {
+            const int go = lt ? ((meta >> 8) & 255u) : ((meta >> 16) & 255u);
+            leaf = lt ? d.lval : d.rval;
+            at = go ? go : 255;
         }
-        const bool lt = __fmul_rn(__int2float_rn(r), vnf) < d.thr;
-        if (STUMPS) {
-            sum += (double)(lt ? d.lval : d.rval);
-        } else {
-            if (at == k) {
-                const int go = lt ? ((meta >> 8) & 255u) : ((meta >> 16) & 255u);
-                leaf = lt ? d.lval : d.rval;
-                at = go ? go : 255;
-            }
-            if (meta >> 24) { sum += (double)leaf; at = 0; k = 0; } else ++k;
-        }
+        if (meta >> 24) { sum += (double)leaf; at = 0; k = 0; } else ++k;
     }
     return sum;
 }
@@ -143,7 +165,7 @@ __global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkIt
     extern __shared__ int s_tile[];
     __shared__ float s_vnf[NT];
     __shared__ uint16_t s_id[2][NT];
-    __shared__ int s_cnt[NW];
+    __shared__ int s_n[3];                             // rotating list counters
     __shared__ int s_qbase;
     __shared__ unsigned int s_ctr[4];                  // evaluated, lowvar, near, weak
 
@@ -171,6 +193,7 @@ __global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkIt
 
     for (int xi0 = 0; xi0 < nxg; xi0 += 32) {
         __syncthreads();                               // previous tile fully consumed
+        if (tid == 0) s_n[0] = 0;
         // ---- 1. stage the S tile ----
         {
             const int X0 = xi0 * step, Y0 = r0 * step;
@@ -236,56 +259,57 @@ __global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkIt
         }
         s_vnf[tid] = vnf;
         // ---- 4. block-wide compaction, then stage by stage on the dense list ----
-        int cur = 0, n, s = 1;
+        // The list of n live windows is cut into k = ceil(n/32) chunks, one warp each; list slots are
+        // handed out with one shared-memory atomic per warp, so a stage costs a single barrier.
+        int cur = 0, n, s = 1, rot = 0;                // rot: which of the three list counters is being filled
         {
             const unsigned am = __ballot_sync(0xffffffffu, alive);
-            if (lane == 0) s_cnt[w] = __popc(am);
-            __syncthreads();
-            int base = 0, tot = 0;
-#pragma unroll
-            for (int j = 0; j < NW; ++j) { const int cj = s_cnt[j]; if (j < w) base += cj; tot += cj; }
+            int base = 0;
+            if (lane == 0 && am) base = atomicAdd(&s_n[0], __popc(am));
+            base = __shfl_sync(0xffffffffu, base, 0);
             if (alive) s_id[0][base + __popc(am & below)] = (uint16_t)tid;
-            n = tot;
+            if (tid == 0) { s_n[1] = 0; }
             __syncthreads();
+            n = s_n[0];
         }
         if (nstages == 1 && alive) {                   // one-stage cascade: accepted right here
             emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
             if (map) map[row * nxg_pad + xi] = 1;
         }
         while (s < D && n > 0 && !(n < b.tile_min && s >= 2)) {
-            const int i = tid;
-            const bool act = i < n;
+            const int k = (n + 31) >> 5;
+            const int nxt = rot == 2 ? 0 : rot + 1, nxt2 = nxt == 2 ? 0 : nxt + 1;
+            if (tid == 0) s_n[nxt2] = 0;               // counter of the round after next: nobody reads it any more
             bool pass = false;
             int my = 0;
-            if (w * 32 < n) {                           // warp-uniform: this warp has list entries
-                my = act ? s_id[cur][i] : s_id[cur][0];
+            if (w < k) {                               // warp-uniform: this warp owns a chunk of the list
+                const int i = w * 32 + lane;
+                const bool act = i < n;
+                my = s_id[cur][act ? i : 0];
                 const char* tw = reinterpret_cast<const char*>(s_tile + ((my >> 5) * step) * TP + (my & 31));
-                const float v = s_vnf[my];
-                sum = tile_stage<STUMPS>(c_stage_first_node[s], c_stage_first_node[s + 1], si, tw, v);
+                const int b0 = c_stage_first_node[s], b1 = c_stage_first_node[s + 1];
+                sum = tile_stage<STUMPS>(b0, b1, si, tw, s_vnf[my]);
+                if (lane == 0) weak += (unsigned)min(32, n - w * 32) * (unsigned)(b1 - b0);
                 const float thr = c_stage_thr[s];
                 pass = act && !(sum < (double)thr);
                 const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));
-                if (lane == 0) {
-                    if (nm) atomicAdd(&s_ctr[2], __popc(nm));
-                    weak += (unsigned)min(32, n - w * 32) * (unsigned)(c_stage_first_node[s + 1] - c_stage_first_node[s]);
-                }
-                if (act && !pass && map) map[(r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31)] = (int16_t)s;
+                if (lane == 0 && nm) atomicAdd(&s_ctr[2], __popc(nm));
+                const int mpos = (r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31);
+                if (act && !pass && map) map[mpos] = (int16_t)s;
                 if (pass && s + 1 == nstages) {
                     emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + (my & 31)) * step, (r0 + (my >> 5)) * step, sum);
-                    if (map) map[(r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31)] = (int16_t)nstages;
+                    if (map) map[mpos] = (int16_t)nstages;
                     pass = false;                       // accepted: nothing left to do for it
                 }
             }
             const unsigned pm = __ballot_sync(0xffffffffu, pass);
-            __syncthreads();                            // everyone has read s_cnt / s_id[cur] of this round
-            if (lane == 0) s_cnt[w] = __popc(pm);
-            __syncthreads();
-            int base = 0, tot = 0;
-#pragma unroll
-            for (int j = 0; j < NW; ++j) { const int cj = s_cnt[j]; if (j < w) base += cj; tot += cj; }
+            int base = 0;
+            if (lane == 0 && pm) base = atomicAdd(&s_n[nxt], __popc(pm));
+            base = __shfl_sync(0xffffffffu, base, 0);
             if (pass) s_id[cur ^ 1][base + __popc(pm & below)] = (uint16_t)my;
-            cur ^= 1; n = tot; ++s;
             __syncthreads();
+            n = s_n[nxt];
+            cur ^= 1; rot = nxt; ++s;
         }
         // ---- 5. survivors -> the frame's work queue (they resume at stage s) ----
         if (n > 0 && s < nstages) {

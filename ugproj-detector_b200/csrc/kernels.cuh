@@ -11,7 +11,8 @@
 
 namespace ugd {
 
-constexpr int kMaxDenseNodes = 384;       // nodes of the in-tile stages, held in __constant__ (160 B each)
+constexpr int kMaxDenseNodes = 380;       // nodes of the in-tile stages, held in __constant__ (160 B each)
+constexpr int kMaxDenseStages = 48;
 constexpr int kScanRows = 8;              // grid rows (= warps) per scan block; a tile is 32 x kScanRows windows
 
 // In-tile node: merged corner list.  BYTE offsets into the shared-memory tile are precomputed for the
