@@ -1,5 +1,6 @@
 // C ABI of libugdet.so (include/ugdet.h): detector object, device buffers, launch sequence.
 // Host orchestration only -- all arithmetic of the path happens in the kernels of k_*.cu.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -50,7 +51,7 @@ struct ugd_detector {
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
-    DevPtr nodeA, nodeB, nodeC, st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
+    DevPtr nodeA, nodeB, nodeC, nodeM, st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
     DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, queue, qcount, raw, rawsum,
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
@@ -109,18 +110,39 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
 
 int upload_cascade(ugd_detector* d) {
     const Cascade& c = *d->casc;
-    std::vector<uint4> A(c.nnodes()), B(c.nnodes());
-    std::vector<uint2> C(c.nnodes());
+    // Tail arrays: merged corner lists with byte offsets into the (win+1)x(win+1) shared-memory patch.
+    // Inside a stage of a stump cascade the nodes are ordered by corner count so that the 32 nodes a
+    // warp evaluates together take the same branches (stage sums are order-independent).
+    const int PW = c.win_w + 1;
+    std::vector<int> order(c.nnodes());
+    for (int i = 0; i < c.nnodes(); ++i) order[i] = i;
+    if (c.max_tree_nodes == 1)
+        for (int s = 0; s < c.nstages(); ++s)
+            std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
+                             [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
+    std::vector<uint4> A(c.nnodes()), B(c.nnodes()), C(c.nnodes());
+    std::vector<uint32_t> M(c.nnodes());
     for (int i = 0; i < c.nnodes(); ++i) {
-        const PackedNode& p = c.packed[i];
-        A[i] = make_uint4(p.r0, p.r1, p.r2, p.thr_bits);
-        memcpy(&B[i], &p.lval, 16);
-        C[i] = make_uint2(p.meta, p.meta2);
+        const CornerNode& cn = c.corners[order[i]];
+        const HostNode& h = c.nodes[order[i]];
+        uint32_t off[12], cf[12];
+        for (int j = 0; j < 12; ++j) {
+            off[j] = (uint32_t)(4 * (cn.cy[j] * PW + cn.cx[j]));
+            cf[j] = (uint32_t)(uint8_t)cn.coef[j];
+        }
+        A[i] = make_uint4(off[0] | off[1] << 16, off[2] | off[3] << 16, off[4] | off[5] << 16, off[6] | off[7] << 16);
+        B[i] = make_uint4(off[8] | off[9] << 16, off[10] | off[11] << 16,
+                          cf[0] | cf[1] << 8 | cf[2] << 16 | cf[3] << 24, cf[4] | cf[5] << 8 | cf[6] << 16 | cf[7] << 24);
+        uint32_t thr, lv, rv;
+        memcpy(&thr, &h.thr, 4); memcpy(&lv, &h.left_val, 4); memcpy(&rv, &h.right_val, 4);
+        C[i] = make_uint4(cf[8] | cf[9] << 8 | cf[10] << 16 | cf[11] << 24, thr, lv, rv);
+        M[i] = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16;
     }
     int rc;
     if ((rc = upload(d, d->nodeA, A))) return rc;
     if ((rc = upload(d, d->nodeB, B))) return rc;
     if ((rc = upload(d, d->nodeC, C))) return rc;
+    if ((rc = upload(d, d->nodeM, M))) return rc;
     if ((rc = upload(d, d->st_first_tree, c.stage_first_tree))) return rc;
     if ((rc = upload(d, d->st_ntrees, c.stage_ntrees))) return rc;
     if ((rc = upload(d, d->st_thr, c.stage_thr))) return rc;
@@ -194,7 +216,9 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
     b.stumps_only = c.max_tree_nodes == 1;
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
-    b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint2>();
+    b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint4>();
+    b.nodeM = d->nodeM.as<uint32_t>();
+    b.tail_warps = std::max(1, std::min(8, 60000 / ((c.win_w + 1) * (c.win_h + 1) * 4)));
     b.stage_first_tree = d->st_first_tree.as<int32_t>(); b.stage_ntrees = d->st_ntrees.as<int32_t>();
     b.stage_thr = d->st_thr.as<float>(); b.tree_first_node = d->tree_first_node.as<int32_t>();
     b.stage_first_node = d->st_first_node.as<int32_t>();
@@ -247,7 +271,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 7);
     int tail_blocks = 0;
     if (d->dense_stages < c.nstages() && !p.levels.empty()) {
-        tail_blocks = std::max(1, (d->sm_count * 8 + nframes - 1) / nframes);
+        tail_blocks = std::max(1, (d->sm_count * 8 * (8 / b.tail_warps) + nframes - 1) / nframes);
         launch_tail(b, tail_blocks, st);
     }
     mark(d, 8);
@@ -393,8 +417,8 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     if (!(d->prm.scale_factor > 1.0)) return UGD_ERR_ARG;
     d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
     d->rawcap = d->prm.max_raw_per_frame > 0 ? (int)round_up((size_t)d->prm.max_raw_per_frame, 4) : 8192;
-    // in-tile stages: default 8, bounded by the __constant__ node budget
-    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 8;
+    // in-tile stages: default 6 (measured optimum for the frontalface cascades at 720p), bounded by the __constant__ node budget
+    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 6;
     if (const char* e = getenv("UGD_TILE_MIN")) d->tile_min = atoi(e);
     D = std::min(D, std::min(d->casc->nstages(), kMaxDenseStages));
     while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;
@@ -423,7 +447,7 @@ void ugd_destroy(ugd_detector* d) {
     if (d->stream) cudaStreamSynchronize(d->stream);
     { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     for (auto& kv : d->plans) kv.second->release();
-    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->nodeM, &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
                      &d->carryS, &d->carryQ, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};

@@ -342,21 +342,40 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t
 
 // ------------------------------------------------------------------------------------------------
 // Tail: one warp per queued window, lanes over the weak classifiers of a stage.
+// Node data: merged corner lists whose patch BYTE offsets were computed at load time; two offsets
+// share a 32-bit word, so one add of (patch base | patch base << 16) rebases both.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int rect_sum(const int32_t* __restrict__ p, uint32_t r, int pitch) {
-    const int x = r & 255u, y = (r >> 8) & 255u, w = (r >> 16) & 255u, h = r >> 24;
-    const int32_t* a = p + y * pitch + x;
-    const int32_t* c = a + h * pitch;
-    return a[0] - a[w] - c[0] + c[w];
+__device__ __forceinline__ int lds32(uint32_t addr) {
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
 }
+__device__ __forceinline__ int sx8(uint32_t w, int byte) { return (int)(int8_t)(w >> (8 * byte)); }
 
-__device__ __forceinline__ int sext8(uint32_t v) { return (int)(int8_t)(v & 255u); }
-
-__device__ __forceinline__ float node_val(const int32_t* __restrict__ p, int pitch, uint32_t r0, uint32_t r1, uint32_t r2,
-                                          uint32_t meta, uint32_t meta2, float vnf) {
-    int r = sext8(meta >> 16) * rect_sum(p, r0, pitch) + sext8(meta >> 24) * rect_sum(p, r1, pitch);
-    if (r2) r += sext8(meta2) * rect_sum(p, r2, pitch);
-    return __fmul_rn(__int2float_rn(r), vnf);
+// response of tail node n against the patch whose shared-memory byte address is packed in pb2
+__device__ __forceinline__ int tail_resp(const DevBufs& b, int n, uint32_t pb2, uint32_t nc, uint4& C) {
+    const uint4 A = __ldg(b.nodeA + n);
+    const uint4 B = __ldg(b.nodeB + n);
+    C = __ldg(b.nodeC + n);
+    const uint32_t o01 = A.x + pb2, o23 = A.y + pb2, o45 = A.z + pb2;
+    int a = sx8(B.z, 0) * lds32(o01 & 0xffffu) + sx8(B.z, 1) * lds32(o01 >> 16) + sx8(B.z, 2) * lds32(o23 & 0xffffu);
+    int c = sx8(B.z, 3) * lds32(o23 >> 16) + sx8(B.w, 0) * lds32(o45 & 0xffffu) + sx8(B.w, 1) * lds32(o45 >> 16);
+    if (nc > 6) {
+        const uint32_t o67 = A.w + pb2;
+        a += sx8(B.w, 2) * lds32(o67 & 0xffffu);
+        c += sx8(B.w, 3) * lds32(o67 >> 16);
+        if (nc > 8) {
+            const uint32_t o89 = B.x + pb2;
+            a += sx8(C.x, 0) * lds32(o89 & 0xffffu);
+            if (nc > 9) {
+                const uint32_t oab = B.y + pb2;
+                c += sx8(C.x, 1) * lds32(o89 >> 16);
+                a += sx8(C.x, 2) * lds32(oab & 0xffffu);
+                c += sx8(C.x, 3) * lds32(oab >> 16);
+            }
+        }
+    }
+    return a + c;
 }
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -366,16 +385,20 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
-    extern __shared__ int32_t s_patch[];                       // 8 warps x (win_h+1)*(win_w+1) ints
+    extern __shared__ int32_t s_patch[];                       // tail_warps x (win_h+1)*(win_w+1) ints
     const int frame = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nwarps = blockDim.x >> 5;
     const int PW = b.win_w + 1, PH = b.win_h + 1, PN = PW * PH;
     int32_t* patch = s_patch + warp * PN;
+    const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(patch);
+    const uint32_t pb2 = pbase | pbase << 16;                  // all patches sit below 64 KB (tail_warps)
     const int qn = min(b.qcount[frame], (int)b.pos_stride);
     const uint4* queue = b.queue + (size_t)frame * b.pos_stride;
     const int nstages = b.nstages;
+    const bool stumps = b.stumps_only != 0;
     unsigned near_cnt = 0;
     unsigned long long weak_cnt = 0;                          // per-lane tally of evaluated nodes
-    for (int i = blockIdx.x * 8 + warp; i < qn; i += gridDim.x * 8) {
+    for (int i = blockIdx.x * nwarps + warp; i < qn; i += gridDim.x * nwarps) {
         const uint4 e = queue[i];
         const int x = e.x & 4095u, y = (e.x >> 12) & 4095u, level = e.x >> 24;
         const float vnf = __uint_as_float(e.y);
@@ -384,12 +407,21 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
         const int32_t* S = b.S + (size_t)frame * b.int_stride + L.int_off + (size_t)y * P + x;
         __syncwarp();
         {
-            int r = 0, c = lane;                               // flattened patch index -> (row, col), incrementally
+            // flattened patch index -> (row, col) incrementally; four independent loads in flight per lane
+            int r = 0, c = lane;
             while (c >= PW) { c -= PW; ++r; }
-            for (int idx = lane; idx < PN; idx += 32) {
-                patch[idx] = S[r * P + c];
-                c += 32;
-                while (c >= PW) { c -= PW; ++r; }
+            for (int idx = lane; idx < PN; idx += 128) {
+                int off[4], v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    off[u] = r * P + c;
+                    c += 32;
+                    while (c >= PW) { c -= PW; ++r; }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (idx + 32 * u < PN) ? __ldg(S + off[u]) : 0;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (idx + 32 * u < PN) patch[idx + 32 * u] = v[u];
             }
         }
         __syncwarp();
@@ -398,23 +430,34 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
         for (; s < nstages; ++s) {
             const int t0 = b.stage_first_tree[s], nt = b.stage_ntrees[s];
             double part = 0.0;
-            for (int t = lane; t < nt; t += 32) {
-                const int base = b.stumps_only ? (t0 + t) : b.tree_first_node[t0 + t];
-                int at = 0;
-                double leaf;
-                for (;;) {
-                    const uint4 A = __ldg(b.nodeA + base + at);
-                    const uint2 C = __ldg(b.nodeC + base + at);
-                    const float val = node_val(patch, PW, A.x, A.y, A.z, C.x, C.y, vnf);
+            if (stumps) {
+                const int n0 = b.stage_first_node[s];
+                for (int t = lane; t < nt; t += 32) {
+                    const int n = n0 + t;
+                    uint4 C;
+                    const int r = tail_resp(b, n, pb2, __ldg(b.nodeM + n) & 255u, C);
+                    const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
+                    part += (double)__uint_as_float(lt ? C.z : C.w);
                     ++weak_cnt;
-                    const bool lt = val < __uint_as_float(A.w);
-                    const uint4 Bv = __ldg(b.nodeB + base + at);
-                    leaf = lt ? __hiloint2double((int)Bv.y, (int)Bv.x) : __hiloint2double((int)Bv.w, (int)Bv.z);
-                    const int go = lt ? (C.x & 255u) : ((C.x >> 8) & 255u);
-                    if (!go) break;
-                    at = go;
                 }
-                part += leaf;
+            } else {
+                for (int t = lane; t < nt; t += 32) {
+                    const int base = b.tree_first_node[t0 + t];
+                    int at = 0;
+                    float leaf;
+                    for (;;) {
+                        const uint32_t M = __ldg(b.nodeM + base + at);
+                        uint4 C;
+                        const int r = tail_resp(b, base + at, pb2, M & 255u, C);
+                        ++weak_cnt;
+                        const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
+                        leaf = __uint_as_float(lt ? C.z : C.w);
+                        const int go = lt ? ((M >> 8) & 255u) : ((M >> 16) & 255u);
+                        if (!go) break;
+                        at = go;
+                    }
+                    part += (double)leaf;
+                }
             }
             sum = warp_sum(part);
             const float thr = b.stage_thr[s];
@@ -455,8 +498,8 @@ cudaError_t init_kernel_attributes(int win_w, int win_h) {
 }
 
 void launch_tail(const DevBufs& b, int blocks_per_frame, cudaStream_t st) {
-    int smem = 8 * (b.win_w + 1) * (b.win_h + 1) * (int)sizeof(int32_t);
-    k_tail<<<dim3(blocks_per_frame, b.nframes), 256, smem, st>>>(b);
+    int smem = b.tail_warps * (b.win_w + 1) * (b.win_h + 1) * (int)sizeof(int32_t);
+    k_tail<<<dim3(blocks_per_frame, b.nframes), b.tail_warps * 32, smem, st>>>(b);
 }
 
 }  // namespace ugd

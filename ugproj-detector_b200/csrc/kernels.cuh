@@ -13,7 +13,6 @@ namespace ugd {
 
 constexpr int kMaxDenseNodes = 380;       // nodes of the in-tile stages, held in __constant__ (160 B each)
 constexpr int kMaxDenseStages = 48;
-constexpr int kScanRows = 8;              // grid rows (= warps) per scan block; a tile is 32 x kScanRows windows
 
 // In-tile node: merged corner list.  BYTE offsets into the shared-memory tile are precomputed for the
 // two tile layouts (index 0: grid step 1; index 1: grid step 2, even/odd columns de-interleaved).
@@ -45,7 +44,10 @@ struct DevBufs {
     const LevelInfo* levels;
     const uint32_t* xtab; const uint32_t* ytab;
     // cascade (tail evaluator, SoA in global memory; dense stages live in __constant__)
-    const uint4* nodeA; const uint4* nodeB; const uint2* nodeC;
+    // tail node n: A = 8 x u16 patch byte offsets (corners 0-7); B = {off8|off9<<16, off10|off11<<16, coef0-3, coef4-7};
+    //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
+    const uint4* nodeA; const uint4* nodeB; const uint4* nodeC; const uint32_t* nodeM;
+    int tail_warps;                                   // warps per k_tail block (all patches must sit below 64 KB)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
     const int32_t* tree_first_node; const int32_t* stage_first_node;
     // frames
