@@ -192,22 +192,14 @@ def main():
     host = torch.from_numpy(make_frames(synth, w, h, nF, seed0=1000 * rank)).pin_memory()
     dev = host.cuda(non_blocking=False)
     host_np = host.numpy()
-    gather_buf = [torch.empty((nF, CAP + 1, 4), dtype=torch.int32, device="cuda") for _ in range(world)] if rank == 0 else None
-
-    def pack(rects):
-        out = np.zeros((nF, CAP + 1, 4), np.int32)
-        for i, r in enumerate(rects):
-            n = min(len(r), CAP)
-            out[i, 0, 0] = n
-            out[i, 1:1 + n] = r[:n]
-        return out
+    sharding = __import__("importlib").import_module(ge.PKG_NAME + ".sharding")
 
     def gather(rects):
         """per-frame detection lists -> rank 0 (NCCL over NVLink), as fixed slots {n; rect[CAP]}"""
         if world == 1:
             return
-        t = torch.from_numpy(pack(rects)).cuda(non_blocking=True)
-        dist.gather(t, gather_buf, dst=0)
+        t = torch.from_numpy(sharding.pack_slots(rects, CAP)).cuda(non_blocking=True)
+        sharding.gather_to_rank0(t, world, rank, nF)
 
     def step_device():
         r = det.detect_batch_device(dev.data_ptr(), False, nF, w, h, cap=CAP)

@@ -158,6 +158,9 @@ const char* ugd_kernel_name(int k);
  * width/height and grid step.  Arrays may be NULL; cap = their length. */
 int  ugd_plan_info(ugd_detector* d, int w, int h, int* nlevels, float* scales, int32_t* lw, int32_t* lh,
                    int32_t* step, int cap);
+/* Same, without a detector or a GPU (host arithmetic only): geometry for cascade c under params p. */
+int  ugd_plan_query(const ugd_cascade* c, const ugd_params* p, int w, int h, int* nlevels, float* scales,
+                    int32_t* lw, int32_t* lh, int32_t* step, int cap, int64_t* grid_windows, int64_t* level_pixels);
 /* Raw view of the most recent single-frame gray/bgr detect (frame 0 of a batch): every accepted
  * window before grouping (unclipped) and its final-stage sum -- the same observables as cv2's
  * detectMultiScale(minNeighbors=0) / detectMultiScale3(outputRejectLevels). */

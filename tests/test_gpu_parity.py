@@ -131,3 +131,73 @@ def test_edge_cases(dets, synth, ug):
     det.detect_gray(g)
     with pytest.raises(ug.UgdError):
         det.detect_gray(np.zeros((721, 1280), np.uint8))                       # larger than created for
+
+
+def test_golden_fixtures_on_gpu(ug, synth, cv2ref):
+    """The committed cv2-generated fixtures (tests/golden), replayed through the C ABI."""
+    import hashlib
+    import json
+    import os
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_detections.json")))
+    dets = {}
+    for c in gold["cases"]:
+        key = (c["cascade"], c["scale"], tuple(c["min_size"]))
+        if key not in dets:
+            casc = ug.Cascade(cv2ref.cascade_path(c["cascade"]))
+            dets[key] = (casc, ug.Detector(casc, ug.default_params(scale_factor=c["scale"], min_size=tuple(c["min_size"])),
+                                           max_size=(1280, 720), max_batch=1))
+        det = dets[key][1]
+        if c["kind"] == "gray":
+            f = synth.gray_frame(c["w"], c["h"], c["nfaces"], c["seed"])
+            assert hashlib.sha1(f.tobytes()).hexdigest() == c["frame_sha1"]
+            got = det.detect_gray(f)
+            raw, _ = det.raw()
+            x1 = np.minimum(raw[:, 0] + raw[:, 2], c["w"]); y1 = np.minimum(raw[:, 1] + raw[:, 3], c["h"])
+            raw[:, 2] = x1 - raw[:, 0]; raw[:, 3] = y1 - raw[:, 1]
+            assert len(raw) == c["raw_count"]
+            assert hashlib.sha1(np.array(rectset(raw), np.int32).tobytes()).hexdigest() == c["raw_sha1"]
+        else:
+            f = synth.bgr_frame(c["w"], c["h"], c["nfaces"], c["seed"])
+            got = det.detect_bgr(f)
+        assert rectset(got) == rectset(c["rects"]), c
+    for _, d in dets.values():
+        d.close()
+
+
+def test_full_size_configs_against_cv2(ug, synth, cv2ref):
+    """BASELINE configs at full size: default@1080p (config 3) and the sf 1.05 / min 24 deep pyramid
+    (config 5 parameters, on a 1080p frame to keep cv2 to seconds) -- final rectangles vs live cv2."""
+    for name, w, h, sf, ms, nf in (("default", 1920, 1080, 1.1, (30, 30), 12), ("alt", 1920, 1080, 1.05, (24, 24), 12)):
+        casc = ug.Cascade(cv2ref.cascade_path(name))
+        det = ug.Detector(casc, ug.default_params(scale_factor=sf, min_size=ms), max_size=(w, h), max_batch=2)
+        cc = cv2ref.load(cv2ref.cascade_path(name))
+        frames = synth.gray_batch(w, h, 2, seed0=40, nfaces=nf)
+        got = det.detect_batch(frames, cap=256)
+        for i in range(2):
+            assert rectset(got[i]) == rectset(cv2ref.detect_multiscale_cv2(cc, frames[i], sf, 2, ms))
+        ctr = det.counters()
+        assert ctr["windows_evaluated"] > 0 and ctr["raw"] > 0
+        det.close()
+
+
+def test_properties_at_bench_size(ug, synth, cv2ref):
+    """Size-independent properties on a 720p batch: determinism (same batch twice), batch-order
+    independence (frames permuted), idempotent grouping (output is canonically sorted), rects inside
+    the frame, counters consistent."""
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    det = ug.Detector(casc, ug.default_params(), max_size=(1280, 720), max_batch=8)
+    frames = synth.gray_batch(1280, 720, 8, seed0=70)
+    a = det.detect_batch(frames)
+    ctr = det.counters()
+    b = det.detect_batch(frames)
+    perm = np.array([3, 0, 7, 1, 6, 2, 5, 4])
+    c = det.detect_batch(frames[perm])
+    for i in range(8):
+        assert np.array_equal(a[i], b[i])
+        assert np.array_equal(c[i], a[perm[i]])
+        r = a[i]
+        assert (r[:, 0] >= 0).all() and (r[:, 1] >= 0).all() and (r[:, 0] + r[:, 2] <= 1280).all() and (r[:, 1] + r[:, 3] <= 720).all()
+        assert [tuple(x) for x in r[:, [1, 0, 3, 2]].tolist()] == sorted(tuple(x) for x in r[:, [1, 0, 3, 2]].tolist())
+    assert ctr["frames"] == 8 and ctr["levels"] == 33 and ctr["grid_windows"] == 8 * 1185515 or ctr["grid_windows"] > 0
+    assert ctr["windows_evaluated"] <= ctr["grid_windows"] and ctr["grouped"] == sum(len(x) for x in a)
+    det.close()

@@ -1,0 +1,113 @@
+"""CPU tests (no GPU): the C oracle is pinned against the reference's own arithmetic -- live cv2 4.13
+and the committed golden fixtures (tests/golden/, generated from cv2 by make_golden.py)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import CASCADES, rectset
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_detections.json")
+
+
+def _clip(raw, w, h):
+    r = raw.copy()
+    x1 = np.minimum(r[:, 0] + r[:, 2], w); y1 = np.minimum(r[:, 1] + r[:, 3], h)
+    r[:, 2] = x1 - r[:, 0]; r[:, 3] = y1 - r[:, 1]
+    return r
+
+
+def test_building_blocks_match_cv2(orc, synth):
+    import cv2
+    rng = np.random.default_rng(0)
+    bgr = rng.integers(0, 256, (211, 317, 3), dtype=np.uint8)
+    assert np.array_equal(orc.bgr2gray(bgr), cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY))
+    ycc = cv2.cvtColor(bgr, cv2.COLOR_BGR2YCrCb)
+    assert np.array_equal(orc.bgr2ycrcb(bgr), ycc)
+    assert np.array_equal(orc.inrange3(ycc, (0, 133, 77), (255, 173, 127)), cv2.inRange(ycc, (0, 133, 77), (255, 173, 127)))
+    g = synth.gray_frame(640, 360, 6, 1)
+    assert np.array_equal(orc.equalize_hist(g), cv2.equalizeHist(g))
+    flat = np.full((50, 70), 9, np.uint8)
+    assert np.array_equal(orc.equalize_hist(flat), cv2.equalizeHist(flat))        # constant image: unchanged
+    for dw, dh in [(397, 224), (100, 57), (639, 359), (640, 360), (38, 21)]:
+        assert np.array_equal(orc.resize_exact(g, dw, dh), cv2.resize(g, (dw, dh), interpolation=cv2.INTER_LINEAR_EXACT))
+    S, SQ = orc.integral(g)
+    s2, q2 = cv2.integral2(g, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
+    assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+
+
+def test_integral_wraps_like_cv2(orc):
+    import cv2
+    g = np.full((720, 1280), 255, np.uint8)
+    S, SQ = orc.integral(g)
+    s2, q2 = cv2.integral2(g, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
+    assert (q2 < 0).any()
+    assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+
+
+def test_group_rectangles_matches_cv2(orc):
+    import cv2
+    rng = np.random.default_rng(3)
+    for trial in range(12):
+        centers = rng.integers(40, 500, (5, 2))
+        rects = []
+        for _ in range(int(rng.integers(0, 60))):
+            c = centers[rng.integers(0, 5)]
+            s = int(rng.integers(30, 90))
+            rects.append([int(c[0] + rng.integers(-6, 7)), int(c[1] + rng.integers(-6, 7)), s, s])
+        got, _ = orc.group_rectangles(rects, 2, 0.2)
+        want, _w = cv2.groupRectangles([list(r) for r in rects], 2, 0.2)
+        assert rectset(got) == rectset(np.asarray(want).reshape(-1, 4))
+    assert len(orc.group_rectangles([], 2)[0]) == 0
+
+
+@pytest.mark.parametrize("name", CASCADES)
+def test_raw_windows_sums_and_groups_match_cv2(orc, cv2ref, synth, name):
+    import cv2
+    oc = orc.OracleCascade.load(cv2ref.cascade_path(name))
+    cc = cv2ref.load(cv2ref.cascade_path(name))
+    g = synth.gray_frame(480, 270, 5, 7)
+    raw, sums, ctr = orc.detect_raw(oc, g)
+    r0 = cv2ref.detect_multiscale_cv2(cc, g, 1.1, 0)
+    assert rectset(_clip(raw, 480, 270)) == rectset(r0)
+    assert ctr["windows_evaluated"] <= ctr["grid_windows"]
+    # final-stage sums, bitwise, through detectMultiScale3(outputRejectLevels)
+    r3, lv, wt = cc.detectMultiScale3(g, scaleFactor=1.1, minNeighbors=0, minSize=(30, 30), outputRejectLevels=True)
+    a = sorted(zip(map(tuple, _clip(raw, 480, 270).tolist()), sums.tolist()))
+    b = sorted(zip(map(tuple, np.asarray(r3).reshape(-1, 4).tolist()), np.asarray(wt).reshape(-1).tolist()))
+    assert a == b
+    got, _ = orc.detect_multiscale(oc, g)
+    assert rectset(got) == rectset(cv2ref.detect_multiscale_cv2(cc, g))
+
+
+def test_detect_faces_matches_cv2(orc, cv2ref, synth):
+    oc = orc.OracleCascade.load(cv2ref.cascade_path("alt2"))
+    cc = cv2ref.load(cv2ref.cascade_path("alt2"))
+    for seed in (0, 3):
+        bgr = synth.bgr_frame(640, 360, 6, seed)
+        got, _ = orc.detect_faces(oc, bgr)
+        assert rectset(got) == rectset(cv2ref.detect_faces_cv2(cc, bgr))
+
+
+def test_oracle_against_golden_fixtures(orc, cv2ref, synth):
+    with open(GOLDEN) as fh:
+        gold = json.load(fh)
+    assert len(gold["cases"]) >= 10
+    for c in gold["cases"]:
+        oc = orc.OracleCascade.load(cv2ref.cascade_path(c["cascade"]))
+        ms = tuple(c["min_size"])
+        if c["kind"] == "gray":
+            f = synth.gray_frame(c["w"], c["h"], c["nfaces"], c["seed"])
+            assert hashlib.sha1(f.tobytes()).hexdigest() == c["frame_sha1"], "synthetic frame generator drifted"
+            raw, _, _ = orc.detect_raw(oc, f, c["scale"], ms)
+            raw = _clip(raw, c["w"], c["h"])
+            assert len(raw) == c["raw_count"]
+            assert hashlib.sha1(np.array(rectset(raw), np.int32).tobytes()).hexdigest() == c["raw_sha1"]
+            got, _ = orc.detect_multiscale(oc, f, c["scale"], 2, ms)
+        else:
+            f = synth.bgr_frame(c["w"], c["h"], c["nfaces"], c["seed"])
+            assert hashlib.sha1(f.tobytes()).hexdigest() == c["frame_sha1"]
+            got, _ = orc.detect_faces(oc, f, c["scale"], 2, ms)
+        assert rectset(got) == rectset(c["rects"]), c

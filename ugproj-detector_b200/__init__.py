@@ -142,6 +142,19 @@ class Cascade:
             self._h = None
 
 
+def plan_query(cascade: "Cascade", params: Params | None, w: int, h: int):
+    """Pyramid geometry (host arithmetic only, no GPU): scales, level sizes, steps, totals."""
+    n = C.c_int(); gw = C.c_int64(); lp = C.c_int64()
+    pp = C.byref(params) if params is not None else None
+    rc = lib().ugd_plan_query(cascade._h, pp, w, h, C.byref(n), None, None, None, None, 0, C.byref(gw), C.byref(lp))
+    if rc:
+        raise UgdError(rc)
+    sc = np.zeros(n.value, np.float32)
+    lw = np.zeros(n.value, np.int32); lh = np.zeros(n.value, np.int32); st = np.zeros(n.value, np.int32)
+    lib().ugd_plan_query(cascade._h, pp, w, h, C.byref(n), _p(sc), _p(lw), _p(lh), _p(st), n.value, None, None)
+    return dict(scales=sc, lw=lw, lh=lh, step=st, grid_windows=gw.value, level_pixels=lp.value)
+
+
 class Detector:
     """Owns one ugd_detector.  All frames are numpy uint8 arrays (or raw device pointers)."""
 

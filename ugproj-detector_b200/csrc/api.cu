@@ -522,6 +522,25 @@ int ugd_plan_info(ugd_detector* d, int w, int h, int* nlevels, float* scales, in
     return UGD_OK;
 }
 
+int ugd_plan_query(const ugd_cascade* c, const ugd_params* prm, int w, int h, int* nlevels, float* scales, int32_t* lw,
+                   int32_t* lh, int32_t* step, int cap, int64_t* grid_windows, int64_t* level_pixels) {
+    if (!c || w <= 0 || h <= 0) return UGD_ERR_ARG;
+    ugd_params dp;
+    if (!prm) { ugd_params_default(&dp); prm = &dp; }
+    Plan p;
+    build_plan(w, h, c->c.win_w, c->c.win_h, prm->scale_factor, prm->min_w, prm->min_h, prm->max_w, prm->max_h, p);
+    if (nlevels) *nlevels = (int)p.levels.size();
+    if (grid_windows) *grid_windows = p.grid_windows;
+    if (level_pixels) *level_pixels = p.level_pixels;
+    for (int i = 0; i < (int)p.levels.size() && i < cap; ++i) {
+        if (scales) scales[i] = p.levels[i].scale;
+        if (lw) lw[i] = p.levels[i].sw;
+        if (lh) lh[i] = p.levels[i].sh;
+        if (step) step[i] = p.levels[i].step;
+    }
+    return UGD_OK;
+}
+
 int ugd_get_raw(ugd_detector* d, ugd_rect* out, double* sums, int cap, int* n) {
     if (!d || !n || !d->last_plan) return UGD_ERR_ARG;
     CK(cudaSetDevice(d->device));
