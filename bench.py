@@ -67,11 +67,12 @@ def peaks():
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
+        self.t0 = self.t1 = None                      # wall-clock bounds of the timed region
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
@@ -96,6 +97,10 @@ class ClockSampler:
             if len(c) < 9:
                 continue
             try:
+                import datetime
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                if self.t0 is not None and not (self.t0 - 0.05 <= ts <= self.t1 + 0.05):
+                    continue                          # sample taken outside the timed region
                 sm.append(float(c[1])); mx.append(float(c[2]))
             except ValueError:
                 continue
@@ -174,6 +179,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"               # keep stdout to the one JSON line
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ug = ge.load_package()
@@ -212,19 +219,23 @@ def main():
         return r
 
     def timed(fn, steps, warmup, sample_clocks=False):
+        sampler = ClockSampler(local) if sample_clocks and rank == 0 else None   # nvidia-smi needs ~1 s to start
         for _ in range(warmup):
             fn()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        sampler = ClockSampler(local) if sample_clocks and rank == 0 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if sampler:
+            sampler.t0 = time.time()
         e0.record(stream)
         for _ in range(steps):
             fn()
         e1.record(stream)
         torch.cuda.synchronize()
+        if sampler:
+            sampler.t1 = time.time()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
