@@ -38,6 +38,7 @@ struct Cascade {
     int win_w = 0, win_h = 0;
     bool old_format = false;
     bool sum_exact = false;
+    bool delta_exact = false;               // base + sum of (left - right) is exact too (see cascade_xml.cc)
     int max_tree_nodes = 0;
     std::vector<int32_t> stage_first_tree, stage_ntrees;
     std::vector<float>   stage_thr;              // f32(xml) - 1e-5f

@@ -319,6 +319,10 @@ int validate_and_pack(Cascade& c, std::string& err) {
     // all leaves are multiples of 2^min_lsb and |stage sum| <= max_bound: exact in fp64 iff it fits 53 bits
     int need = (max_bound > 0 ? (int)ceil(log2(max_bound + 1)) : 0) - (min_lsb == 1000 ? 0 : min_lsb);
     c.sum_exact = need <= 52;
+    // the stump evaluator sums base = sum(right) plus (left - right) of the nodes that go left: every
+    // partial sum is bounded by 3 * max_bound, still a multiple of 2^min_lsb
+    int need3 = (max_bound > 0 ? (int)ceil(log2(3.0 * max_bound + 1)) : 0) - (min_lsb == 1000 ? 0 : min_lsb);
+    c.delta_exact = c.sum_exact && need3 <= 52;
     return UGD_OK;
 }
 

@@ -1,18 +1,23 @@
 // Window scan and cascade stage evaluation for sm_100a.
 //
-//   k_scan : one block = 8 grid rows of one level of one frame (one warp per row), walking the rows
-//            left to right in tiles of 32 x 8 windows.  Per tile:
-//              1. the (8*step+win) x (32*step+win) patch of the integral image S is staged in shared
-//                 memory (coalesced loads; for grid step 2 even/odd columns are de-interleaved so
-//                 that the 32 lanes of a warp always hit 32 consecutive banks);
-//              2. every lane computes the variance normalisation and stage 0 of its own window;
-//              3. the oracle's sequential x-skip rule is resolved in closed form with one ballot and
-//                 a run-parity carried along the row in a register;
-//              4. surviving windows are ballot/popc-compacted ACROSS the block into a dense list, and
-//                 stage by stage the list is re-evaluated and re-compacted, so every warp that works
-//                 has (almost) all lanes on live windows.  Node data is broadcast from __constant__
-//                 as merged corner lists (6/8/9 LDS + IMAD per weak classifier);
-//              5. when fewer than `tile_min` windows are left (or the in-tile stages are exhausted)
+//   k_scan : one block (8 warps) = 16 grid rows of one level of one frame, walking the rows left to
+//            right in tiles of 64 x 16 windows.  Per tile:
+//              1. the patch of the integral image S under the tile is staged in shared memory
+//                 (coalesced loads; for grid step 2 even/odd columns are de-interleaved so that
+//                 x-adjacent windows always sit in consecutive banks);
+//              2. row by row, every lane computes the variance normalisation and stage 0 of its own
+//                 window; the oracle's sequential x-skip rule is resolved in closed form with one
+//                 ballot and a run length carried along the row in a register;
+//              3. survivors are kept as 32 bit masks, one per BANK CLASS q = (col + SH*row) mod 32
+//                 (the bank of the window's origin in the tile; each class has exactly 32 candidate
+//                 windows).  A warp-round takes the j-th live window of every class: lane q always
+//                 works on a window of class q, so every corner load of a round is free of bank
+//                 conflicts whatever the survivor pattern is.  Rounds are dealt to the 8 warps;
+//                 passing windows set their bit in the next stage's masks (shared-memory atomicOr,
+//                 one address per lane) -- this is the ballot/popc compaction of the design, done
+//                 per bank class.  Node data is broadcast from __constant__ as merged corner lists
+//                 (6/8/9 LDS + IMAD per weak classifier);
+//              4. when fewer than `tile_min` windows are left (or the in-tile stages are exhausted)
 //                 the survivors go to the frame's global work queue.
 //   k_tail : persistent warps pull queued windows; the window's (win+1)^2 patch of S is staged in
 //            shared memory once, then the 32 lanes evaluate 32 weak classifiers of a stage in
@@ -28,16 +33,29 @@ namespace ugd {
 __constant__ DNode c_dn[kMaxDenseNodes];
 __constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[kMaxDenseStages];
+__constant__ double c_stage_base[kMaxDenseStages];          // exact stump evaluator: sum of the right leaves of stage s
 __constant__ ScanGeom c_geom;
+
+// Tile pitches are chosen so that the bank shift between consecutive window rows, (step * pitch) mod 32,
+// is one of {8, 12, 20, 24}: a window's bank class q = (col + SH * row) mod 32 then spreads 2-D clusters
+// of surviving windows over many classes (tools/sim_compaction3.py).
+static bool good_shift(int sh) { return sh == 8 || sh == 12 || sh == 20 || sh == 24; }
 
 ScanGeom make_scan_geom(int win_w, int win_h) {
     ScanGeom g{};
     for (int si = 0; si < 2; ++si) {
         const int step = si + 1;
-        g.TC[si] = 31 * step + win_w + 1;
-        g.TR[si] = (kScanRows - 1) * step + win_h + 1;
-        g.TCH[si] = si ? (g.TC[si] + 1) / 2 : 0;
-        g.TP[si] = si ? 2 * g.TCH[si] : g.TC[si];
+        g.TC[si] = (kTileCols - 1) * step + win_w + 1;
+        g.TR[si] = (kTileRows - 1) * step + win_h + 1;
+        if (si == 0) {
+            int tp = g.TC[0];
+            while (!good_shift(tp & 31)) ++tp;
+            g.TP[0] = tp; g.TCH[0] = 0; g.SH[0] = tp & 31;
+        } else {
+            int tch = (g.TC[1] + 1) / 2;
+            while (!good_shift((4 * tch) & 31)) ++tch;
+            g.TCH[1] = tch; g.TP[1] = 2 * tch; g.SH[1] = (4 * tch) & 31;
+        }
     }
     g.tile_ints = std::max(g.TR[0] * g.TP[0], g.TR[1] * g.TP[1]);
     return g;
@@ -57,6 +75,7 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         g.norm_off[si][2] = tile_off(g, si, 1, c.win_h - 1);
         g.norm_off[si][3] = tile_off(g, si, c.win_w - 1, c.win_h - 1);
     }
+    const bool fast = c.max_tree_nodes == 1 && c.delta_exact;
     std::vector<DNode> dn((size_t)std::max(nn, 1));
     for (int t = 0; t < c.ntrees(); ++t) {
         const int base = c.tree_first_node[t];
@@ -73,13 +92,20 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             }
             d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
                      (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
-            d.thr = h.thr; d.lval = h.left_val; d.rval = h.right_val;
+            d.thr = h.thr;
+            if (fast) d.delta = (double)h.left_val - (double)h.right_val;
+            else { d.lval = h.left_val; d.rval = h.right_val; }
         }
     }
+    std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
+    if (fast)
+        for (int s = 0; s < dense_stages; ++s)
+            for (int n = c.stage_first_node[s]; n < c.stage_first_node[s + 1]; ++n) base[s] += (double)c.nodes[n].right_val;
     cudaError_t e;
     if ((e = cudaMemcpyToSymbolAsync(c_dn, dn.data(), sizeof(DNode) * dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, c.stage_first_node.data(), sizeof(int) * (size_t)(dense_stages + 1), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, c.stage_thr.data(), sizeof(float) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_base, base.data(), sizeof(double) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_geom, &g, sizeof g, 0, cudaMemcpyHostToDevice, st))) return e;
     return cudaStreamSynchronize(st);      // dn is a local: the copy must finish before it goes away
 }
@@ -90,42 +116,47 @@ __device__ __forceinline__ int near_thr(double sum, float thr) {
 
 // One in-tile stage for one window.  `t` points at the window's origin inside the shared tile; the
 // loop and every node field are warp-uniform, so node data is broadcast from the constant bank.
-#define TILE_AT(d, o, j) ((d).coef[j] * *reinterpret_cast<const int*>(t + (o)[j]))
+#define TILE_AT(cf, of) ((cf) * *reinterpret_cast<const int*>(t + (of)))
 // feature response r of one node: two independent IMAD chains, extra corners behind uniform branches
 __device__ __forceinline__ int node_resp(const DNode& d, int si, const char* __restrict__ t) {
-    const int32_t* o = d.off[si];
-    int a = TILE_AT(d, o, 0) + TILE_AT(d, o, 1) + TILE_AT(d, o, 2);
-    int c = TILE_AT(d, o, 3) + TILE_AT(d, o, 4) + TILE_AT(d, o, 5);
+    const int4* o4 = reinterpret_cast<const int4*>(d.off[si]);
+    const int4* c4 = reinterpret_cast<const int4*>(d.coef);
+    const int4 o0 = o4[0], k0 = c4[0], o1 = o4[1], k1 = c4[1];
+    int a = TILE_AT(k0.x, o0.x) + TILE_AT(k0.y, o0.y) + TILE_AT(k0.z, o0.z);
+    int c = TILE_AT(k0.w, o0.w) + TILE_AT(k1.x, o1.x) + TILE_AT(k1.y, o1.y);
     const int nc = d.meta & 255u;
     if (nc > 6) {
-        a += TILE_AT(d, o, 6); c += TILE_AT(d, o, 7);
+        a += TILE_AT(k1.z, o1.z); c += TILE_AT(k1.w, o1.w);
         if (nc > 8) {
-            a += TILE_AT(d, o, 8);
-            if (nc > 9) { c += TILE_AT(d, o, 9); a += TILE_AT(d, o, 10); c += TILE_AT(d, o, 11); }
+            const int4 o2 = o4[2], k2 = c4[2];
+            a += TILE_AT(k2.x, o2.x);
+            if (nc > 9) { c += TILE_AT(k2.y, o2.y); a += TILE_AT(k2.z, o2.z); c += TILE_AT(k2.w, o2.w); }
         }
     }
     return a + c;
 }
+#undef TILE_AT
 
-template <bool STUMPS>
-__device__ __forceinline__ double tile_stage(int n0, int n1, int si, const char* __restrict__ t, float vnf) {
-    if (STUMPS) {
+// FAST: stump cascade whose leaf sums are exact in fp64 (Cascade::delta_exact).  The stage sum is
+// formed as base + sum over the nodes that go LEFT of (left - right): one predicated DADD per node.
+// It equals the oracle's sum of leaves bit for bit because every partial sum is exact.
+template <bool FAST>
+__device__ __forceinline__ double tile_stage(int s, int si, const char* __restrict__ t, float vnf) {
+    const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
+    if (FAST) {
         // two nodes per trip, separate accumulators: twice the independent work in flight per warp
-        double s0 = 0.0, s1 = 0.0;
+        double s0 = c_stage_base[s], s1 = 0.0;
         int n = n0;
         for (; n + 1 < n1; n += 2) {
             const DNode& d0 = c_dn[n];
             const DNode& d1 = c_dn[n + 1];
             const int r0 = node_resp(d0, si, t), r1 = node_resp(d1, si, t);
-            const bool l0 = __fmul_rn(__int2float_rn(r0), vnf) < d0.thr;
-            const bool l1 = __fmul_rn(__int2float_rn(r1), vnf) < d1.thr;
-            s0 += (double)(l0 ? d0.lval : d0.rval);
-            s1 += (double)(l1 ? d1.lval : d1.rval);
+            if (__fmul_rn(__int2float_rn(r0), vnf) < d0.thr) s0 += d0.delta;
+            if (__fmul_rn(__int2float_rn(r1), vnf) < d1.thr) s1 += d1.delta;
         }
         if (n < n1) {
             const DNode& d0 = c_dn[n];
-            const bool l0 = __fmul_rn(__int2float_rn(node_resp(d0, si, t)), vnf) < d0.thr;
-            s0 += (double)(l0 ? d0.lval : d0.rval);
+            if (__fmul_rn(__int2float_rn(node_resp(d0, si, t)), vnf) < d0.thr) s0 += d0.delta;
         }
         return s0 + s1;
     }
@@ -145,7 +176,6 @@ __device__ __forceinline__ double tile_stage(int n0, int n1, int si, const char*
     }
     return sum;
 }
-#undef TILE_AT
 
 __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scale, int rw, int rh, int x, int y, double sum) {
     int slot = atomicAdd(&b.rawcount[frame], 1);
@@ -159,28 +189,27 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
     }
 }
 
-template <bool STUMPS>
-__global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
-    constexpr int NW = kScanRows, NT = NW * 32;
+template <bool FAST>
+__global__ void __launch_bounds__(256, 6) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
+    constexpr int NW = 8, NT = NW * 32, R = kTileRows, C = kTileCols;
+    static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
     extern __shared__ int s_tile[];
-    __shared__ float s_vnf[NT];
-    __shared__ uint16_t s_id[2][NT];
-    __shared__ int s_n[3];                             // rotating list counters
+    __shared__ float s_vnf[R * C];
+    __shared__ unsigned s_alive[3][32];                // rotating survivor masks, one word per bank class
     __shared__ int s_qbase;
     __shared__ unsigned int s_ctr[4];                  // evaluated, lowvar, near, weak
 
     const WorkItem it = wk[blockIdx.x];
-    const int frame = blockIdx.y, tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const int frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);     // warp index, provably warp-uniform
     const LevelInfo& Lg = b.levels[it.level];
     const int sw = Lg.sw, sh = Lg.sh, P = Lg.P, step = Lg.step, nxg = Lg.nxg, nyg = Lg.nyg, nxg_pad = Lg.nxg_pad;
     const float scale = Lg.scale;
     const int rect_w = Lg.rect_w, rect_h = Lg.rect_h;
     const uint32_t pos_off = Lg.pos_off;
     const int si = step - 1;
-    const int TP = c_geom.TP[si], TCH = c_geom.TCH[si], TC = c_geom.TC[si], TR = c_geom.TR[si];
+    const int TP = c_geom.TP[si], TCH = c_geom.TCH[si], TC = c_geom.TC[si], TR = c_geom.TR[si], SH = c_geom.SH[si];
     const int r0 = it.first;
-    const int row = r0 + w;
-    const bool row_valid = row < nyg;
     const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
     const int32_t* Q = b.SQ + (size_t)frame * b.int_stride + Lg.int_off;
     const int ow = b.win_w, oh = b.win_h, D = b.dense_stages, nstages = b.nstages;
@@ -188,12 +217,15 @@ __global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkIt
     const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
     int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
     if (tid < 4) s_ctr[tid] = 0;
-    int run_in = 0;                                    // stage-0 failure run ending just before this segment
+    static_assert(R / NW == 2, "two rows per warp");
+    int run_a = 0, run_b = 0;                          // stage-0 failure run ending just before the next segment, per owned row
     unsigned weak = 0;                                 // lane 0 of each warp tallies weak classifiers
+    const int nw0 = c_stage_first_node[1] - c_stage_first_node[0];
+    const float thr0 = c_stage_thr[0];
 
-    for (int xi0 = 0; xi0 < nxg; xi0 += 32) {
+    for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
-        if (tid == 0) s_n[0] = 0;
+        if (tid < 96) (&s_alive[0][0])[tid] = 0;
         // ---- 1. stage the S tile ----
         {
             const int X0 = xi0 * step, Y0 = r0 * step;
@@ -207,119 +239,137 @@ __global__ void __launch_bounds__(kScanRows * 32) k_scan(DevBufs b, const WorkIt
             }
         }
         __syncthreads();
-        // ---- 2. variance normalisation + stage 0, every lane ----
-        const int xi = xi0 + lane;
-        const bool valid = row_valid && xi < nxg;
-        const int x = valid ? xi * step : 0, y = valid ? row * step : 0;
-        const char* t = reinterpret_cast<const char*>(s_tile + (w * step) * TP + lane);
-        float vnf = 1.f;
-        bool ok = false;
-        {
-            const int32_t* no = c_geom.norm_off[si];
-            const int vs = *reinterpret_cast<const int*>(t + no[0]) - *reinterpret_cast<const int*>(t + no[1]) -
-                           *reinterpret_cast<const int*>(t + no[2]) + *reinterpret_cast<const int*>(t + no[3]);
-            const int32_t* q = Q + (size_t)y * P + x;
-            const uint32_t vq = (uint32_t)q[P + 1] - (uint32_t)q[P + ow - 1] - (uint32_t)q[(oh - 1) * P + 1] + (uint32_t)q[(oh - 1) * P + ow - 1];
-            double nf = area * (double)vq - (double)vs * (double)vs;
-            if (nf > 0.0) {
-                nf = sqrt(nf);
-                vnf = (float)(1.0 / nf);
-                ok = area * (double)vnf < 1e-1;
+        // ---- 2. variance normalisation + stage 0 + x-skip, row segment by row segment ----
+#pragma unroll 1
+        for (int seg = 0; seg < (R / NW) * (C / 32); ++seg) {
+            const int k = seg >> 1, h = seg & 1;
+            const int rl = w + k * NW, row = r0 + rl;
+            const bool row_valid = row < nyg;
+            {
+                const int c = 32 * h + lane, xi = xi0 + c;
+                if (xi0 + 32 * h >= nxg) continue;     // warp-uniform: segment past the end of the row
+                const int run_in = k ? run_b : run_a;
+                const bool valid = row_valid && xi < nxg;
+                const int x = valid ? xi * step : 0, y = valid ? row * step : 0;
+                const char* t = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
+                float vnf = 1.f;
+                bool ok = false;
+                {
+                    const int32_t* no = c_geom.norm_off[si];
+                    const int vs = *reinterpret_cast<const int*>(t + no[0]) - *reinterpret_cast<const int*>(t + no[1]) -
+                                   *reinterpret_cast<const int*>(t + no[2]) + *reinterpret_cast<const int*>(t + no[3]);
+                    const int32_t* q = Q + (size_t)y * P + x;
+                    const uint32_t vq = (uint32_t)q[P + 1] - (uint32_t)q[P + ow - 1] - (uint32_t)q[(oh - 1) * P + 1] + (uint32_t)q[(oh - 1) * P + ow - 1];
+                    double nf = area * (double)vq - (double)vs * (double)vs;
+                    if (nf > 0.0) {
+                        nf = sqrt(nf);
+                        vnf = (float)(1.0 / nf);
+                        ok = area * (double)vnf < 1e-1;
+                    }
+                    if (!ok) vnf = 1.f;
+                }
+                const double sum = tile_stage<FAST>(0, si, t, vnf);
+                const bool pass0 = !(sum < (double)thr0);
+                // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
+                // ending at i-1 has even length (a failure is only seen at evaluated positions)
+                const bool f0 = valid && ok && !pass0;
+                const unsigned F = __ballot_sync(0xffffffffu, f0);
+                const unsigned inv = ~F & below;
+                const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
+                const int run_out = (F == 0xffffffffu) ? run_in + 32 : __clz((int)~F);
+                if (k) run_b = run_out; else run_a = run_out;
+                const bool evaluated = valid && !(run & 1);
+                const bool alive = evaluated && ok && pass0;
+                {
+                    const unsigned em = __ballot_sync(0xffffffffu, evaluated);
+                    const unsigned lm = __ballot_sync(0xffffffffu, evaluated && !ok);
+                    const unsigned s0 = __ballot_sync(0xffffffffu, evaluated && ok);
+                    const unsigned nm = __ballot_sync(0xffffffffu, evaluated && ok && near_thr(sum, thr0));
+                    if (lane == 0) {
+                        atomicAdd(&s_ctr[0], __popc(em));
+                        if (lm) atomicAdd(&s_ctr[1], __popc(lm));
+                        if (nm) atomicAdd(&s_ctr[2], __popc(nm));
+                        weak += __popc(s0) * (unsigned)nw0;
+                    }
+                }
+                if (map && valid) {
+                    if (!evaluated) map[row * nxg_pad + xi] = kMapSkip;
+                    else if (!ok) map[row * nxg_pad + xi] = kMapLowVar;
+                    else if (!pass0) map[row * nxg_pad + xi] = 0;
+                }
+                s_vnf[rl * C + c] = vnf;
+                if (alive) {
+                    if (nstages == 1) {                // one-stage cascade: accepted right here
+                        emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
+                        if (map) map[row * nxg_pad + xi] = 1;
+                    } else {
+                        atomicOr(&s_alive[0][(c + SH * rl) & 31], 1u << (rl * (C / 32) + h));
+                    }
+                }
             }
-            if (!ok) vnf = 1.f;
         }
-        double sum = tile_stage<STUMPS>(c_stage_first_node[0], c_stage_first_node[1], si, t, vnf);
-        const float thr0 = c_stage_thr[0];
-        const bool pass0 = !(sum < (double)thr0);
-        // ---- 3. x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
-        //         ending at i-1 has even length (a failure is only seen at evaluated positions) ----
-        const bool f0 = valid && ok && !pass0;
-        const unsigned F = __ballot_sync(0xffffffffu, f0);
-        const unsigned inv = ~F & below;
-        const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
-        run_in = (F == 0xffffffffu) ? run_in + 32 : __clz((int)~F);
-        const bool evaluated = valid && !(run & 1);
-        bool alive = evaluated && ok && pass0;
-        {
-            const unsigned em = __ballot_sync(0xffffffffu, evaluated);
-            const unsigned lm = __ballot_sync(0xffffffffu, evaluated && !ok);
-            const unsigned s0 = __ballot_sync(0xffffffffu, evaluated && ok);
-            const unsigned nm = __ballot_sync(0xffffffffu, evaluated && ok && near_thr(sum, thr0));
-            if (lane == 0) {
-                atomicAdd(&s_ctr[0], __popc(em));
-                if (lm) atomicAdd(&s_ctr[1], __popc(lm));
-                if (nm) atomicAdd(&s_ctr[2], __popc(nm));
-                weak += __popc(s0) * (unsigned)(c_stage_first_node[1] - c_stage_first_node[0]);
-            }
-        }
-        if (map && valid) {
-            if (!evaluated) map[row * nxg_pad + xi] = kMapSkip;
-            else if (!ok) map[row * nxg_pad + xi] = kMapLowVar;
-            else if (!pass0) map[row * nxg_pad + xi] = 0;
-        }
-        s_vnf[tid] = vnf;
-        // ---- 4. block-wide compaction, then stage by stage on the dense list ----
-        // The list of n live windows is cut into k = ceil(n/32) chunks, one warp each; list slots are
-        // handed out with one shared-memory atomic per warp, so a stage costs a single barrier.
-        int cur = 0, n, s = 1, rot = 0;                // rot: which of the three list counters is being filled
-        {
-            const unsigned am = __ballot_sync(0xffffffffu, alive);
-            int base = 0;
-            if (lane == 0 && am) base = atomicAdd(&s_n[0], __popc(am));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (alive) s_id[0][base + __popc(am & below)] = (uint16_t)tid;
-            if (tid == 0) { s_n[1] = 0; }
-            __syncthreads();
-            n = s_n[0];
-        }
-        if (nstages == 1 && alive) {                   // one-stage cascade: accepted right here
-            emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
-            if (map) map[row * nxg_pad + xi] = 1;
-        }
-        while (s < D && n > 0 && !(n < b.tile_min && s >= 2)) {
-            const int k = (n + 31) >> 5;
-            const int nxt = rot == 2 ? 0 : rot + 1, nxt2 = nxt == 2 ? 0 : nxt + 1;
-            if (tid == 0) s_n[nxt2] = 0;               // counter of the round after next: nobody reads it any more
-            bool pass = false;
-            int my = 0;
-            if (w < k) {                               // warp-uniform: this warp owns a chunk of the list
-                const int i = w * 32 + lane;
-                const bool act = i < n;
-                my = s_id[cur][act ? i : 0];
-                const char* tw = reinterpret_cast<const char*>(s_tile + ((my >> 5) * step) * TP + (my & 31));
-                const int b0 = c_stage_first_node[s], b1 = c_stage_first_node[s + 1];
-                sum = tile_stage<STUMPS>(b0, b1, si, tw, s_vnf[my]);
-                if (lane == 0) weak += (unsigned)min(32, n - w * 32) * (unsigned)(b1 - b0);
-                const float thr = c_stage_thr[s];
-                pass = act && !(sum < (double)thr);
+        __syncthreads();
+        // ---- 3. stage by stage on the per-class survivor masks ----
+        int cur = 0, s = 1, total;
+        unsigned m;
+        for (;;) {
+            m = s_alive[cur][lane];
+            const int cnt = __popc(m);
+            total = __reduce_add_sync(0xffffffffu, cnt);
+            if (s >= D || total == 0 || (total < b.tile_min && s >= 2)) break;   // block-uniform
+            const int rounds = __reduce_max_sync(0xffffffffu, cnt);
+            const int nxt = cur == 2 ? 0 : cur + 1, nxt2 = nxt == 2 ? 0 : nxt + 1;
+            if (w == 0) s_alive[nxt2][lane] = 0;        // masks of the stage before: nobody reads them any more
+            const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
+            const float thr = c_stage_thr[s];
+            unsigned mm = m;
+            for (int i = 0; i < w; ++i) mm &= mm - 1;   // this warp takes rounds w, w+8, ...
+            for (int j = w; j < rounds; j += NW) {
+                const bool act = mm != 0;
+                const int bit = act ? __ffs((int)mm) - 1 : 0;
+                const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
+                const char* tw = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
+                const double sum = tile_stage<FAST>(s, si, tw, s_vnf[rl * C + c]);
+                bool pass = act && !(sum < (double)thr);
+                const unsigned am = __ballot_sync(0xffffffffu, act);
                 const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));
-                if (lane == 0 && nm) atomicAdd(&s_ctr[2], __popc(nm));
-                const int mpos = (r0 + (my >> 5)) * nxg_pad + xi0 + (my & 31);
+                if (lane == 0) {
+                    weak += (unsigned)__popc(am) * (unsigned)nws;
+                    if (nm) atomicAdd(&s_ctr[2], __popc(nm));
+                }
+                const int mpos = (r0 + rl) * nxg_pad + xi0 + c;
                 if (act && !pass && map) map[mpos] = (int16_t)s;
                 if (pass && s + 1 == nstages) {
-                    emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + (my & 31)) * step, (r0 + (my >> 5)) * step, sum);
+                    emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum);
                     if (map) map[mpos] = (int16_t)nstages;
                     pass = false;                       // accepted: nothing left to do for it
                 }
+                if (pass) atomicOr(&s_alive[nxt][lane], 1u << bit);
+#pragma unroll
+                for (int i = 0; i < NW; ++i) mm &= mm - 1;
             }
-            const unsigned pm = __ballot_sync(0xffffffffu, pass);
-            int base = 0;
-            if (lane == 0 && pm) base = atomicAdd(&s_n[nxt], __popc(pm));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (pass) s_id[cur ^ 1][base + __popc(pm & below)] = (uint16_t)my;
             __syncthreads();
-            n = s_n[nxt];
-            cur ^= 1; rot = nxt; ++s;
+            cur = nxt; ++s;
         }
-        // ---- 5. survivors -> the frame's work queue (they resume at stage s) ----
-        if (n > 0 && s < nstages) {
-            if (tid == 0) s_qbase = atomicAdd(&b.qcount[frame], n);
-            __syncthreads();
-            if (tid < n) {
-                const int my = s_id[cur][tid];
-                const int qx = (xi0 + (my & 31)) * step, qy = (r0 + (my >> 5)) * step;
-                b.queue[(size_t)frame * b.pos_stride + s_qbase + tid] =
-                    make_uint4((uint32_t)qx | (uint32_t)qy << 12 | (uint32_t)it.level << 24, __float_as_uint(s_vnf[my]), (uint32_t)s, 0u);
+        // ---- 4. survivors -> the frame's work queue (they resume at stage s) ----
+        if (total > 0 && s < nstages && w == 0) {
+            const int cnt = __popc(m);
+            int incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            int qb = 0;
+            if (lane == 31) qb = atomicAdd(&b.qcount[frame], total);
+            qb = __shfl_sync(0xffffffffu, qb, 31) + incl - cnt;
+            uint4* qdst = b.queue + (size_t)frame * b.pos_stride + qb;
+            for (unsigned mm = m; mm; mm &= mm - 1) {
+                const int bit = __ffs((int)mm) - 1;
+                const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
+                const int qx = (xi0 + c) * step, qy = (r0 + rl) * step;
+                *qdst++ = make_uint4((uint32_t)qx | (uint32_t)qy << 12 | (uint32_t)it.level << 24,
+                                     __float_as_uint(s_vnf[rl * C + c]), (uint32_t)s, 0u);
             }
         }
     }
@@ -336,8 +386,8 @@ static int g_scan_smem = 0;
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
     if (!nblocks) return;
     const size_t smem = (size_t)make_scan_geom(b.win_w, b.win_h).tile_ints * sizeof(int);
-    if (b.stumps_only) k_scan<true><<<dim3(nblocks, b.nframes), kScanRows * 32, smem, st>>>(b, wk);
-    else k_scan<false><<<dim3(nblocks, b.nframes), kScanRows * 32, smem, st>>>(b, wk);
+    if (b.fast_scan) k_scan<true><<<dim3(nblocks, b.nframes), 256, smem, st>>>(b, wk);
+    else k_scan<false><<<dim3(nblocks, b.nframes), 256, smem, st>>>(b, wk);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -21,13 +21,20 @@ constexpr int kMaxDenseStages = 48;
 struct alignas(16) DNode {
     int32_t off[2][12];
     int32_t coef[12];
-    float   thr, lval, rval;
+    float   thr;
     uint32_t meta;                        // nc | lnode << 8 | rnode << 16 | last << 24
+    union {
+        struct { float lval, rval; };     // generic evaluator: the two leaves
+        double delta;                     // exact stump evaluator: (double)left - (double)right
+    };
 };
 static_assert(sizeof(DNode) == 160, "DNode layout");
 
+constexpr int kTileRows = 16;             // scan tile: kTileRows x kTileCols windows = 32 per bank class
+constexpr int kTileCols = 64;
 struct ScanGeom {                          // per layout (step 1 / step 2)
     int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
+    int SH[2];                             // bank shift between consecutive window rows: (step * TP) mod 32
     int32_t norm_off[2][4];                // tile BYTE offsets of the 4 variance-normalisation corners
     int tile_ints;                         // ints of shared memory for the tile
 };
@@ -41,6 +48,7 @@ struct DevBufs {
     // geometry
     int w, h, nlevels, nframes;
     int win_w, win_h, nstages, dense_stages, stumps_only;
+    int fast_scan;                                    // stump cascade with exact delta sums: k_scan<true>
     const LevelInfo* levels;
     const uint32_t* xtab; const uint32_t* ytab;
     // cascade (tail evaluator, SoA in global memory; dense stages live in __constant__)

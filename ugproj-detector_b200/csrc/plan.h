@@ -11,7 +11,7 @@ namespace ugd {
 constexpr int kStripRows = 32;       // integral strips: 32 output rows each
 constexpr int kChunkCols = 128;      // integral chunk: 128 output columns
 constexpr int kMaxLevels = 256;
-constexpr int kScanRows = 8;         // grid rows (= warps) per scan block; a scan tile is 32 x kScanRows windows
+constexpr int kScanRows = 16;        // grid rows per scan block (a scan tile is 64 x 16 windows, 8 warps)
 
 // Device-visible description of one pyramid level (all offsets are per frame).
 struct LevelInfo {
