@@ -47,7 +47,7 @@ struct ugd_detector {
     const Cascade* casc = nullptr;
     ugd_params prm{};
     int device = 0, max_w = 0, max_h = 0, max_batch = 1;
-    int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 12;
+    int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 32;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
@@ -418,8 +418,8 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     if (!(d->prm.scale_factor > 1.0)) return UGD_ERR_ARG;
     d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
     d->rawcap = d->prm.max_raw_per_frame > 0 ? (int)round_up((size_t)d->prm.max_raw_per_frame, 4) : 8192;
-    // in-tile stages: default 6 (measured optimum for the frontalface cascades at 720p), bounded by the __constant__ node budget
-    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 6;
+    // in-tile stages: default 8 (measured optimum for frontalface_alt at 720p), bounded by the __constant__ node budget
+    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 8;
     if (const char* e = getenv("UGD_TILE_MIN")) d->tile_min = atoi(e);
     D = std::min(D, std::min(d->casc->nstages(), kMaxDenseStages));
     while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;

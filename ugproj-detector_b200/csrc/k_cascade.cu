@@ -26,6 +26,9 @@
 // Exactness: feature sums are int32 (exact: weights are small integers), the one rounding step is
 // val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, exact for the shipped cascades
 // (ugd_cascade_info.sum_exact), hence independent of summation order.
+#include <algorithm>
+#include <vector>
+
 #include "kernels.cuh"
 
 namespace ugd {
@@ -33,7 +36,8 @@ namespace ugd {
 __constant__ DNode c_dn[kMaxDenseNodes];
 __constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[kMaxDenseStages];
-__constant__ double c_stage_base[kMaxDenseStages];          // exact stump evaluator: sum of the right leaves of stage s
+__constant__ double c_stage_base[kMaxDenseStages];
+__constant__ int c_stage_nc_first[kMaxDenseStages][5];      // exact stump evaluator: first node with 6 / 8 / 9 / 12 corners, end          // exact stump evaluator: sum of the right leaves of stage s
 __constant__ ScanGeom c_geom;
 
 // Tile pitches are chosen so that the bank shift between consecutive window rows, (step * pitch) mod 32,
@@ -98,14 +102,27 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         }
     }
     std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
+    std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 5, 0);
     if (fast)
-        for (int s = 0; s < dense_stages; ++s)
-            for (int n = c.stage_first_node[s]; n < c.stage_first_node[s + 1]; ++n) base[s] += (double)c.nodes[n].right_val;
+        for (int s = 0; s < dense_stages; ++s) {
+            const int a = c.stage_first_node[s], z = c.stage_first_node[s + 1];
+            for (int n = a; n < z; ++n) base[s] += (double)c.nodes[n].right_val;
+            std::stable_sort(dn.begin() + a, dn.begin() + z, [](const DNode& x, const DNode& y) { return (x.meta & 255u) < (y.meta & 255u); });
+            const int cls[4] = {6, 8, 9, 12};
+            int n = a;
+            for (int k = 0; k < 4; ++k) {
+                ncf[s * 5 + k] = n;
+                while (n < z && (int)(dn[n].meta & 255u) == cls[k]) ++n;
+            }
+            ncf[s * 5 + 4] = n;
+            if (n != z) return cudaErrorInvalidValue;      // a corner count outside {6, 8, 9, 12}
+        }
     cudaError_t e;
     if ((e = cudaMemcpyToSymbolAsync(c_dn, dn.data(), sizeof(DNode) * dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, c.stage_first_node.data(), sizeof(int) * (size_t)(dense_stages + 1), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, c.stage_thr.data(), sizeof(float) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_base, base.data(), sizeof(double) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_nc_first, ncf.data(), sizeof(int) * ncf.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_geom, &g, sizeof g, 0, cudaMemcpyHostToDevice, st))) return e;
     return cudaStreamSynchronize(st);      // dn is a local: the copy must finish before it goes away
 }
@@ -177,6 +194,43 @@ __device__ __forceinline__ double tile_stage(int s, int si, const char* __restri
     return sum;
 }
 
+// Exact stump evaluator for K windows per lane (the same node is applied to the K windows, so its
+// constant-bank fetches are paid once per K feature evaluations).  Nodes of a stage are sorted by corner
+// count at upload time (sums are exact, hence order-independent), so NC is a compile-time constant.
+template <int NC, int K>
+__device__ __forceinline__ void stage_nodes(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+#pragma unroll 1
+    for (int n = n0; n < n1; ++n) {
+        const DNode& d = c_dn[n];
+        const int32_t* o = d.off[si];
+        int acc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) acc[k] = 0;
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {                  // corner by corner: offset and coefficient fetched once for the K windows
+            const int oj = o[j], cj = d.coef[j];
+#pragma unroll
+            for (int k = 0; k < K; ++k) acc[k] += cj * *reinterpret_cast<const int*>(t[k] + oj);
+        }
+        const float thr = d.thr;
+        const double delta = d.delta;
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (__fmul_rn(__int2float_rn(acc[k]), vnf[k]) < thr) sum[k] += delta;
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void tile_stage_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    const int* f = c_stage_nc_first[s];
+#pragma unroll
+    for (int k = 0; k < K; ++k) sum[k] = k == 0 ? c_stage_base[s] : sum[0];
+    stage_nodes<6, K>(f[0], f[1], si, t, vnf, sum);
+    stage_nodes<8, K>(f[1], f[2], si, t, vnf, sum);
+    stage_nodes<9, K>(f[2], f[3], si, t, vnf, sum);
+    stage_nodes<12, K>(f[3], f[4], si, t, vnf, sum);
+}
+
 __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scale, int rw, int rh, int x, int y, double sum) {
     int slot = atomicAdd(&b.rawcount[frame], 1);
     if (slot < b.rawcap) {
@@ -190,7 +244,7 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
 }
 
 template <bool FAST>
-__global__ void __launch_bounds__(256, 6) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
+__global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
     constexpr int NW = 8, NT = NW * 32, R = kTileRows, C = kTileCols;
     static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
     extern __shared__ int s_tile[];
@@ -322,6 +376,59 @@ __global__ void __launch_bounds__(256, 6) k_scan(DevBufs b, const WorkItem* __re
             if (w == 0) s_alive[nxt2][lane] = 0;        // masks of the stage before: nobody reads them any more
             const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
+            if (FAST) {
+                // exact stump evaluator: a warp takes 4 consecutive rounds at once (4 windows per lane share
+                // every node fetch); ceil(rounds / 4) warps work, the others wait at the barrier
+                if (4 * w < rounds) {
+                    unsigned mm = m;
+                    for (int i = 0; i < 4 * w; ++i) mm &= mm - 1;
+                    const int K = min(4, rounds - 4 * w);
+                    int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        act[k] = mm != 0;
+                        bit[k] = act[k] ? __ffs((int)mm) - 1 : 0;
+                        mm &= mm - 1;
+                        const int rl = bit[k] >> 1, c = ((lane - SH * rl) & 31) + ((bit[k] & 1) << 5);
+                        tw[k] = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
+                        vn[k] = s_vnf[rl * C + c];
+                    }
+                    if (K == 1) {
+                        const char* t1[1] = {tw[0]}; float v1[1] = {vn[0]}; double s1[1];
+                        tile_stage_k<1>(s, si, t1, v1, s1);
+                        sum[0] = s1[0]; sum[1] = sum[2] = sum[3] = 0.0;
+                    } else if (K == 2) {
+                        const char* t2[2] = {tw[0], tw[1]}; float v2[2] = {vn[0], vn[1]}; double s2[2];
+                        tile_stage_k<2>(s, si, t2, v2, s2);
+                        sum[0] = s2[0]; sum[1] = s2[1]; sum[2] = sum[3] = 0.0;
+                    } else {
+                        tile_stage_k<4>(s, si, tw, vn, sum);
+                    }
+                    unsigned passbits = 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        if (k < K) {                    // warp-uniform
+                            bool pass = act[k] && !(sum[k] < (double)thr);
+                            const unsigned am = __ballot_sync(0xffffffffu, act[k]);
+                            const unsigned nm = __ballot_sync(0xffffffffu, act[k] && near_thr(sum[k], thr));
+                            if (lane == 0) {
+                                weak += (unsigned)__popc(am) * (unsigned)nws;
+                                if (nm) atomicAdd(&s_ctr[2], __popc(nm));
+                            }
+                            const int rl = bit[k] >> 1, c = ((lane - SH * rl) & 31) + ((bit[k] & 1) << 5);
+                            const int mpos = (r0 + rl) * nxg_pad + xi0 + c;
+                            if (act[k] && !pass && map) map[mpos] = (int16_t)s;
+                            if (pass && s + 1 == nstages) {
+                                emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum[k]);
+                                if (map) map[mpos] = (int16_t)nstages;
+                                pass = false;           // accepted: nothing left to do for it
+                            }
+                            if (pass) passbits |= 1u << bit[k];
+                        }
+                    }
+                    if (passbits) atomicOr(&s_alive[nxt][lane], passbits);
+                }
+            } else {
             unsigned mm = m;
             for (int i = 0; i < w; ++i) mm &= mm - 1;   // this warp takes rounds w, w+8, ...
             for (int j = w; j < rounds; j += NW) {
@@ -347,6 +454,7 @@ __global__ void __launch_bounds__(256, 6) k_scan(DevBufs b, const WorkItem* __re
                 if (pass) atomicOr(&s_alive[nxt][lane], 1u << bit);
 #pragma unroll
                 for (int i = 0; i < NW; ++i) mm &= mm - 1;
+            }
             }
             __syncthreads();
             cur = nxt; ++s;
