@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_STEP)
     ap.add_argument("--size", default=f"{W}x{H}")
     ap.add_argument("--dense-stages", type=int, default=0)
+    ap.add_argument("--scale-factor", type=float, default=1.1)
+    ap.add_argument("--min-size", type=int, default=30)
+    ap.add_argument("--group", type=int, default=GROUP, help="frames per launch group")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -113,16 +116,16 @@ class ClockSampler:
         return out
 
 
-def cpu_reference_run(cv2ref, frames, cascade_name, budget_s, max_frames):
+def cpu_reference_run(cv2ref, frames, cascade_name, budget_s, max_frames, sf=1.1, ms=(30, 30)):
     """The reference's CPU path: cv2.CascadeClassifier.detectMultiScale(gray, 1.1, 2, SCALE_IMAGE, (30,30))
     with all host threads.  Returns (frames/s, frames timed, seconds, threads)."""
     import cv2
     cv2.setNumThreads(os.cpu_count() or 1)
     cc = cv2ref.load(cv2ref.cascade_path(cascade_name))
-    cv2ref.detect_multiscale_cv2(cc, frames[0])            # warm-up
+    cv2ref.detect_multiscale_cv2(cc, frames[0], sf, 2, ms)   # warm-up
     n, t0 = 0, time.perf_counter()
     while n < max_frames:
-        cv2ref.detect_multiscale_cv2(cc, frames[n % len(frames)])
+        cv2ref.detect_multiscale_cv2(cc, frames[n % len(frames)], sf, 2, ms)
         n += 1
         if time.perf_counter() - t0 > budget_s:
             break
@@ -139,16 +142,17 @@ def run_reference(args, rank, world):
     synth = __import__("importlib").import_module(ge.PKG_NAME + ".synth")
     w, h = map(int, args.size.split("x"))
     per_step = 8                                            # bounded sample of the workload per step
+    sf, ms = args.scale_factor, (args.min_size, args.min_size)
     frames = make_frames(synth, w, h, per_step, seed0=0)
     import cv2
     cv2.setNumThreads(os.cpu_count() or 1)
     cc = cv2_ref.load(cv2_ref.cascade_path(args.cascade))
     for _ in range(args.warmup):
-        cv2_ref.detect_multiscale_cv2(cc, frames[0])
+        cv2_ref.detect_multiscale_cv2(cc, frames[0], sf, 2, ms)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         for f in frames:
-            cv2_ref.detect_multiscale_cv2(cc, f)
+            cv2_ref.detect_multiscale_cv2(cc, f, sf, 2, ms)
     dt = time.perf_counter() - t0
     fps = args.steps * per_step / dt
     line = {
@@ -156,7 +160,7 @@ def run_reference(args, rank, world):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
         "config": {"workload": f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, "
-                               "scale 1.1, minNeighbors 2, minSize 30x30", "frames_per_step": per_step},
+                               f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}", "frames_per_step": per_step},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cv2.getNumThreads(), "kind": "reference",
                          "sample": f"{per_step} frames/step x {args.steps} steps, cv2 {cv2.__version__} "
                                    f"detectMultiScale, {os.cpu_count()} host cpus"},
@@ -190,7 +194,9 @@ def main():
     w, h = map(int, args.size.split("x"))
     nF = args.frames
     casc = ug.Cascade(cv2_ref.cascade_path(args.cascade))
-    prm = ug.default_params(dense_stages=args.dense_stages)
+    GROUP = min(args.group, nF)
+    sf, ms = args.scale_factor, (args.min_size, args.min_size)
+    prm = ug.default_params(dense_stages=args.dense_stages, scale_factor=sf, min_size=ms)
     det = ug.Detector(casc, prm, device=local, max_size=(w, h), max_batch=GROUP)
     stream = torch.cuda.current_stream()
     det.set_stream(stream.cuda_stream)
@@ -313,18 +319,19 @@ def main():
 
         cpu = None
         if not args.no_cpu_baseline:
-            cfps, cn, cdt, cthreads = cpu_reference_run(cv2_ref, host_np[:DISTINCT], args.cascade, 12.0, 128)
+            cfps, cn, cdt, cthreads = cpu_reference_run(cv2_ref, host_np[:DISTINCT], args.cascade, 12.0, 128, sf, ms)
             cpu = {"value": cfps, "unit": "frames/s", "cores": cthreads, "kind": "reference",
                    "sample": f"{cn} of the step's {nF} frames in {cdt:.1f} s, cv2 detectMultiScale, "
                              f"{os.cpu_count()} host cpus"}
         groups = (nF + GROUP - 1) // GROUP
-        launches_per_step = groups * 7                          # resize, colsum, carry, integral, scan, tail, group
+        launches_per_step = groups * 8                          # resize, colsum, carry, integral, scan (2: grid step 2 / 1 levels), tail, group
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
             "config": {"workload": f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, "
-                                   "scale 1.1, minNeighbors 2, minSize 30x30 (BASELINE configs[0]/[1] frame+params)",
+                                   f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}"
+                                   + (" (BASELINE configs[0]/[1] frame+params)" if (w, h, sf, ms[0]) == (1280, 720, 1.1, 30) else ""),
                        "frames_per_step_per_gpu": nF, "launch_group": GROUP, "levels": plan_levels,
                        "l2": f"inputs larger than L2: {nF * w * h / 1e6:.0f} MB of frames per step, "
                              f"{GROUP * (level_px + 8 * int_entries) / 1e6:.0f} MB of integrals per launch group",

@@ -180,6 +180,21 @@ def test_full_size_configs_against_cv2(ug, synth, cv2ref):
         det.close()
 
 
+def test_4k_deep_pyramid_against_cv2(ug, synth, cv2ref):
+    """BASELINE config 5 at full size: one 3840x2160 frame, frontalface_alt, scale 1.05, min size 24
+    (92 levels, 29 M grid windows) -- final rectangles vs live cv2, and the level/window counts of the plan."""
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    det = ug.Detector(casc, ug.default_params(scale_factor=1.05, min_size=(24, 24)), max_size=(3840, 2160), max_batch=1)
+    cc = cv2ref.load(cv2ref.cascade_path("alt"))
+    frame = synth.gray_frame(3840, 2160, 24, 5)
+    got = det.detect_gray(frame, cap=1024)
+    want = cv2ref.detect_multiscale_cv2(cc, frame, 1.05, 2, (24, 24))
+    assert len(want) > 0 and rectset(got) == rectset(want)
+    ctr = det.counters()
+    assert ctr["levels"] == 92 and ctr["windows_evaluated"] <= ctr["grid_windows"]
+    det.close()
+
+
 def test_properties_at_bench_size(ug, synth, cv2ref):
     """Size-independent properties on a 720p batch: determinism (same batch twice), batch-order
     independence (frames permuted), idempotent grouping (output is canonically sorted), rects inside

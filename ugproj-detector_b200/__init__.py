@@ -65,7 +65,7 @@ def lib():
     """Loads libugdet.so (building it in-tree with nvcc if it is missing or stale)."""
     global _LIB
     if _LIB is None:
-        path = _build.build()
+        path = os.environ.get("UGD_LIB") or _build.build()     # UGD_LIB: A/B a differently built library
         L = C.CDLL(path)
         L.ugd_strerror.restype = C.c_char_p
         L.ugd_last_error.restype = C.c_char_p

@@ -268,7 +268,11 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 5);
     launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
     mark(d, 6);
-    launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), st);
+    {
+        int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
+        while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
+        launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st);
+    }
     mark(d, 7);
     int tail_blocks = 0;
     if (d->dense_stages < c.nstages() && !p.levels.empty()) {

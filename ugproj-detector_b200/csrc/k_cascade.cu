@@ -244,8 +244,8 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
 }
 
 template <bool FAST>
-__global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
-    constexpr int NW = 8, NT = NW * 32, R = kTileRows, C = kTileCols;
+__global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
+    constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols;
     static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
     extern __shared__ int s_tile[];
     __shared__ float s_vnf[R * C];
@@ -271,15 +271,14 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
     const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
     int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
     if (tid < 4) s_ctr[tid] = 0;
-    static_assert(R / NW == 2, "two rows per warp");
-    int run_a = 0, run_b = 0;                          // stage-0 failure run ending just before the next segment, per owned row
+    unsigned run_par = 0;                              // per owned row: parity of the stage-0 failure run ending just before the next segment
     unsigned weak = 0;                                 // lane 0 of each warp tallies weak classifiers
     const int nw0 = c_stage_first_node[1] - c_stage_first_node[0];
     const float thr0 = c_stage_thr[0];
 
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
-        if (tid < 96) (&s_alive[0][0])[tid] = 0;
+        for (int i = tid; i < 96; i += NW * 32) (&s_alive[0][0])[i] = 0;
         // ---- 1. stage the S tile ----
         {
             const int X0 = xi0 * step, Y0 = r0 * step;
@@ -302,7 +301,7 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
             {
                 const int c = 32 * h + lane, xi = xi0 + c;
                 if (xi0 + 32 * h >= nxg) continue;     // warp-uniform: segment past the end of the row
-                const int run_in = k ? run_b : run_a;
+                const int run_in = (run_par >> k) & 1;  // only the parity of the run length matters
                 const bool valid = row_valid && xi < nxg;
                 const int x = valid ? xi * step : 0, y = valid ? row * step : 0;
                 const char* t = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
@@ -331,7 +330,7 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
                 const unsigned inv = ~F & below;
                 const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
                 const int run_out = (F == 0xffffffffu) ? run_in + 32 : __clz((int)~F);
-                if (k) run_b = run_out; else run_a = run_out;
+                run_par = (run_par & ~(1u << k)) | ((unsigned)(run_out & 1) << k);
                 const bool evaluated = valid && !(run & 1);
                 const bool alive = evaluated && ok && pass0;
                 {
@@ -379,10 +378,10 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
             if (FAST) {
                 // exact stump evaluator: a warp takes 4 consecutive rounds at once (4 windows per lane share
                 // every node fetch); ceil(rounds / 4) warps work, the others wait at the barrier
-                if (4 * w < rounds) {
-                    unsigned mm = m;
-                    for (int i = 0; i < 4 * w; ++i) mm &= mm - 1;
-                    const int K = min(4, rounds - 4 * w);
+                unsigned mm = m;
+                for (int i = 0; i < 4 * w; ++i) mm &= mm - 1;
+                for (int g = 4 * w; g < rounds; g += 4 * NW) {
+                    const int K = min(4, rounds - g);
                     int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
@@ -427,6 +426,7 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
                         }
                     }
                     if (passbits) atomicOr(&s_alive[nxt][lane], passbits);
+                    for (int i = 0; i < 4 * (NW - 1); ++i) mm &= mm - 1;
                 }
             } else {
             unsigned mm = m;
@@ -491,11 +491,18 @@ __global__ void __launch_bounds__(256, FAST ? 4 : 6) k_scan(DevBufs b, const Wor
 
 static int g_scan_smem = 0;
 
-void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+// The work table is ordered by level and the grid-step-2 levels (scale < 2) come first, so the launch is
+// split in two: each half asks only for the shared memory its own tile layout needs.
+void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
     if (!nblocks) return;
-    const size_t smem = (size_t)make_scan_geom(b.win_w, b.win_h).tile_ints * sizeof(int);
-    if (b.fast_scan) k_scan<true><<<dim3(nblocks, b.nframes), 256, smem, st>>>(b, wk);
-    else k_scan<false><<<dim3(nblocks, b.nframes), 256, smem, st>>>(b, wk);
+    const ScanGeom g = make_scan_geom(b.win_w, b.win_h);
+    for (int half = 0; half < 2; ++half) {
+        const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
+        if (!n) continue;
+        const size_t smem = (size_t)g.TR[half ? 0 : 1] * g.TP[half ? 0 : 1] * sizeof(int);
+        if (b.fast_scan) k_scan<true><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+        else k_scan<false><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -32,6 +32,7 @@ static_assert(sizeof(DNode) == 160, "DNode layout");
 
 constexpr int kTileRows = 16;             // scan tile: kTileRows x kTileCols windows = 32 per bank class
 constexpr int kTileCols = 64;
+constexpr int kScanWarps = 4;              // warps per scan block
 struct ScanGeom {                          // per layout (step 1 / step 2)
     int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
     int SH[2];                             // bank shift between consecutive window rows: (step * TP) mod 32
@@ -93,7 +94,7 @@ void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
-void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
+void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
 void launch_tail(const DevBufs& b, int blocks_per_frame, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);
 cudaError_t init_kernel_attributes(int win_w, int win_h);
