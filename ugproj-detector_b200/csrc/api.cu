@@ -215,7 +215,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.w = p.w; b.h = p.h; b.nlevels = (int)p.levels.size(); b.nframes = nframes;
     b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
     b.stumps_only = c.max_tree_nodes == 1;
-    b.fast_scan = c.max_tree_nodes == 1 && c.delta_exact;
+    b.fast_scan = scan_mode(c);
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint4>();
     b.nodeM = d->nodeM.as<uint32_t>();

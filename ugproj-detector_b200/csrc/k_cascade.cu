@@ -69,6 +69,21 @@ static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     //
     return 4 * (si ? y * g.TP[1] + (x & 1) * g.TCH[1] + (x >> 1) : y * g.TP[0] + x);
 }
 
+// Which in-tile evaluator a cascade gets: 1 = stumps, 2 = two-node trees (root + one child), both with
+// exact "base + deltas" stage sums; 0 = the generic evaluator (any tree shape, plain leaf sums).
+int scan_mode(const Cascade& c) {
+    if (!c.delta_exact) return 0;
+    if (c.max_tree_nodes == 1) return 1;
+    for (int t = 0; t < c.ntrees(); ++t) {
+        if (c.tree_nnodes[t] != 2) return 0;
+        const HostNode& r = c.nodes[c.tree_first_node[t]];
+        const HostNode& k = c.nodes[c.tree_first_node[t] + 1];
+        const bool one_child = (r.left == 1 && r.right == 0) || (r.left == 0 && r.right == 1);
+        if (!one_child || k.left != 0 || k.right != 0) return 0;
+    }
+    return 2;
+}
+
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
     const int nn = c.stage_first_node[dense_stages];
     if (nn > kMaxDenseNodes || dense_stages > kMaxDenseStages) return cudaErrorInvalidValue;
@@ -79,7 +94,8 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         g.norm_off[si][2] = tile_off(g, si, 1, c.win_h - 1);
         g.norm_off[si][3] = tile_off(g, si, c.win_w - 1, c.win_h - 1);
     }
-    const bool fast = c.max_tree_nodes == 1 && c.delta_exact;
+    const int mode = scan_mode(c);
+    const bool fast = mode == 1;
     std::vector<DNode> dn((size_t)std::max(nn, 1));
     for (int t = 0; t < c.ntrees(); ++t) {
         const int base = c.tree_first_node[t];
@@ -97,12 +113,24 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
                      (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
             d.thr = h.thr;
-            if (fast) d.delta = (double)h.left_val - (double)h.right_val;
-            else { d.lval = h.left_val; d.rval = h.right_val; }
+            if (mode == 1) d.delta = (double)h.left_val - (double)h.right_val;
+            else if (mode == 2) {
+                // tree value = cr + [root takes its leaf](root leaf - cr) + [root takes the child and child goes left](cl - cr)
+                const HostNode& kid = c.nodes[base + 1];
+                if (k == 0) {
+                    const bool leaf_is_left = h.left == 0;
+                    d.delta = (double)(leaf_is_left ? h.left_val : h.right_val) - (double)kid.right_val;
+                    d.meta |= leaf_is_left ? 0u : 1u << 25;          // bit 25: the root's leaf is on its RIGHT
+                } else d.delta = (double)h.left_val - (double)h.right_val;
+            } else { d.lval = h.left_val; d.rval = h.right_val; }
         }
     }
     std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
     std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 5, 0);
+    if (mode == 2)
+        for (int s = 0; s < dense_stages; ++s)
+            for (int t = c.stage_first_tree[s]; t < c.stage_first_tree[s] + c.stage_ntrees[s]; ++t)
+                base[s] += (double)c.nodes[c.tree_first_node[t] + 1].right_val;
     if (fast)
         for (int s = 0; s < dense_stages; ++s) {
             const int a = c.stage_first_node[s], z = c.stage_first_node[s + 1];
@@ -231,6 +259,62 @@ __device__ __forceinline__ void tile_stage_k(int s, int si, const char* const (&
     stage_nodes<12, K>(f[3], f[4], si, t, vnf, sum);
 }
 
+// Exact evaluator for two-node trees (scan_mode 2), K windows per lane.  Corner counts differ from node to
+// node, so the extra corners sit behind warp-uniform branches (paid once per K windows).
+template <int K>
+__device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* const (&t)[K], int (&acc)[K]) {
+    const int32_t* o = d.off[si];
+    const int nc = d.meta & 255u;
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc[k] = 0;
+#define CORNER(j)                                                                                   \
+    {                                                                                               \
+        const int oj = o[j], cj = d.coef[j];                                                        \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += cj * *reinterpret_cast<const int*>(t[k] + oj); \
+    }
+    CORNER(0) CORNER(1) CORNER(2) CORNER(3) CORNER(4) CORNER(5)
+    if (nc > 6) {
+        CORNER(6) CORNER(7)
+        if (nc > 8) {
+            CORNER(8)
+            if (nc > 9) { CORNER(9) CORNER(10) CORNER(11) }
+        }
+    }
+#undef CORNER
+}
+
+template <int K>
+__device__ __forceinline__ void tile_trees_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
+#pragma unroll
+    for (int k = 0; k < K; ++k) sum[k] = c_stage_base[s];
+#pragma unroll 1
+    for (int n = n0; n < n1; n += 2) {
+        const DNode& root = c_dn[n];
+        const DNode& kid = c_dn[n + 1];
+        int ar[K], ak[K];
+        node_resp_k<K>(root, si, t, ar);
+        node_resp_k<K>(kid, si, t, ak);
+        const bool leaf_right = (root.meta >> 25) & 1u;
+        const float thr_r = root.thr, thr_k = kid.thr;
+        const double d_r = root.delta, d_k = kid.delta;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const bool lt_r = __fmul_rn(__int2float_rn(ar[k]), vnf[k]) < thr_r;
+            const bool lt_k = __fmul_rn(__int2float_rn(ak[k]), vnf[k]) < thr_k;
+            const bool takes_leaf = lt_r != leaf_right;      // left leaf: taken when lt; right leaf: taken when !lt
+            if (takes_leaf) sum[k] += d_r;
+            else if (lt_k) sum[k] += d_k;
+        }
+    }
+}
+
+template <int MODE, int K>
+__device__ __forceinline__ void stage_eval(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    if (MODE == 1) tile_stage_k<K>(s, si, t, vnf, sum);
+    else tile_trees_k<K>(s, si, t, vnf, sum);
+}
+
 __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scale, int rw, int rh, int x, int y, double sum) {
     int slot = atomicAdd(&b.rawcount[frame], 1);
     if (slot < b.rawcap) {
@@ -243,8 +327,8 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
     }
 }
 
-template <bool FAST>
-__global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
+template <int MODE>
+__global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
     constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols;
     static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
     extern __shared__ int s_tile[];
@@ -321,7 +405,12 @@ __global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 3
                     }
                     if (!ok) vnf = 1.f;
                 }
-                const double sum = tile_stage<FAST>(0, si, t, vnf);
+                double sum;
+                if (MODE) {
+                    const char* t1[1] = {t}; const float v1[1] = {vnf}; double s1[1];
+                    stage_eval<MODE, 1>(0, si, t1, v1, s1);
+                    sum = s1[0];
+                } else sum = tile_stage<false>(0, si, t, vnf);
                 const bool pass0 = !(sum < (double)thr0);
                 // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
                 // ending at i-1 has even length (a failure is only seen at evaluated positions)
@@ -375,8 +464,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 3
             if (w == 0) s_alive[nxt2][lane] = 0;        // masks of the stage before: nobody reads them any more
             const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
-            if (FAST) {
-                // exact stump evaluator: a warp takes 4 consecutive rounds at once (4 windows per lane share
+            if (MODE) {
+                // exact evaluators: a warp takes 4 consecutive rounds at once (4 windows per lane share
                 // every node fetch); ceil(rounds / 4) warps work, the others wait at the barrier
                 unsigned mm = m;
                 for (int i = 0; i < 4 * w; ++i) mm &= mm - 1;
@@ -394,14 +483,14 @@ __global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 3
                     }
                     if (K == 1) {
                         const char* t1[1] = {tw[0]}; float v1[1] = {vn[0]}; double s1[1];
-                        tile_stage_k<1>(s, si, t1, v1, s1);
+                        stage_eval<MODE, 1>(s, si, t1, v1, s1);
                         sum[0] = s1[0]; sum[1] = sum[2] = sum[3] = 0.0;
                     } else if (K == 2) {
                         const char* t2[2] = {tw[0], tw[1]}; float v2[2] = {vn[0], vn[1]}; double s2[2];
-                        tile_stage_k<2>(s, si, t2, v2, s2);
+                        stage_eval<MODE, 2>(s, si, t2, v2, s2);
                         sum[0] = s2[0]; sum[1] = s2[1]; sum[2] = sum[3] = 0.0;
                     } else {
-                        tile_stage_k<4>(s, si, tw, vn, sum);
+                        stage_eval<MODE, 4>(s, si, tw, vn, sum);
                     }
                     unsigned passbits = 0;
 #pragma unroll
@@ -436,7 +525,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, FAST ? 1024 / (kScanWarps * 3
                 const int bit = act ? __ffs((int)mm) - 1 : 0;
                 const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
                 const char* tw = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
-                const double sum = tile_stage<FAST>(s, si, tw, s_vnf[rl * C + c]);
+                const double sum = tile_stage<false>(s, si, tw, s_vnf[rl * C + c]);
                 bool pass = act && !(sum < (double)thr);
                 const unsigned am = __ballot_sync(0xffffffffu, act);
                 const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));
@@ -500,8 +589,9 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
         const size_t smem = (size_t)g.TR[half ? 0 : 1] * g.TP[half ? 0 : 1] * sizeof(int);
-        if (b.fast_scan) k_scan<true><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
-        else k_scan<false><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+        if (b.fast_scan == 1) k_scan<1><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+        else if (b.fast_scan == 2) k_scan<2><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+        else k_scan<0><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
     }
 }
 
@@ -654,8 +744,9 @@ cudaError_t init_kernel_attributes(int win_w, int win_h) {
     }
     const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int);
     if (scan_smem > g_scan_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+        cudaError_t e = cudaFuncSetAttribute(k_scan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
         if (e != cudaSuccess) return e;
         g_scan_smem = scan_smem;
     }

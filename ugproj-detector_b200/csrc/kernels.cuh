@@ -49,7 +49,7 @@ struct DevBufs {
     // geometry
     int w, h, nlevels, nframes;
     int win_w, win_h, nstages, dense_stages, stumps_only;
-    int fast_scan;                                    // stump cascade with exact delta sums: k_scan<true>
+    int fast_scan;                                    // scan_mode(cascade): 0 generic, 1 exact stumps, 2 exact two-node trees
     const LevelInfo* levels;
     const uint32_t* xtab; const uint32_t* ytab;
     // cascade (tail evaluator, SoA in global memory; dense stages live in __constant__)
@@ -86,6 +86,7 @@ struct DevBufs {
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
 ScanGeom make_scan_geom(int win_w, int win_h);
+int scan_mode(const Cascade& c);
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
