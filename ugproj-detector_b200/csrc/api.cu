@@ -51,7 +51,7 @@ struct ugd_detector {
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
-    DevPtr nodeA, nodeB, nodeC, nodeM, st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
+    DevPtr nodeA, nodeB, nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
     DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, queue, qcount, raw, rawsum,
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
@@ -120,7 +120,9 @@ int upload_cascade(ugd_detector* d) {
         for (int s = 0; s < c.nstages(); ++s)
             std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
-    std::vector<uint4> A(c.nnodes()), B(c.nnodes()), C(c.nnodes());
+    const ScanGeom geom = make_scan_geom(c.win_w, c.win_h);
+    std::vector<uint4> A(c.nnodes()), B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
+    for (int si = 0; si < 2; ++si) { TA[si].resize(c.nnodes()); TB[si].resize(c.nnodes()); }
     std::vector<uint32_t> M(c.nnodes());
     for (int i = 0; i < c.nnodes(); ++i) {
         const CornerNode& cn = c.corners[order[i]];
@@ -133,6 +135,12 @@ int upload_cascade(ugd_detector* d) {
         A[i] = make_uint4(off[0] | off[1] << 16, off[2] | off[3] << 16, off[4] | off[5] << 16, off[6] | off[7] << 16);
         B[i] = make_uint4(off[8] | off[9] << 16, off[10] | off[11] << 16,
                           cf[0] | cf[1] << 8 | cf[2] << 16 | cf[3] << 24, cf[4] | cf[5] << 8 | cf[6] << 16 | cf[7] << 24);
+        for (int si = 0; si < 2; ++si) {              // the same lists with offsets into the scan tile
+            uint32_t to[12];
+            for (int j = 0; j < 12; ++j) to[j] = (uint32_t)scan_tile_off(geom, si, cn.cx[j], cn.cy[j]);
+            TA[si][i] = make_uint4(to[0] | to[1] << 16, to[2] | to[3] << 16, to[4] | to[5] << 16, to[6] | to[7] << 16);
+            TB[si][i] = make_uint4(to[8] | to[9] << 16, to[10] | to[11] << 16, B[i].z, B[i].w);
+        }
         uint32_t thr, lv, rv;
         memcpy(&thr, &h.thr, 4); memcpy(&lv, &h.left_val, 4); memcpy(&rv, &h.right_val, 4);
         C[i] = make_uint4(cf[8] | cf[9] << 8 | cf[10] << 16 | cf[11] << 24, thr, lv, rv);
@@ -143,6 +151,10 @@ int upload_cascade(ugd_detector* d) {
     if ((rc = upload(d, d->nodeB, B))) return rc;
     if ((rc = upload(d, d->nodeC, C))) return rc;
     if ((rc = upload(d, d->nodeM, M))) return rc;
+    for (int si = 0; si < 2; ++si) {
+        if ((rc = upload(d, d->nodeTA[si], TA[si]))) return rc;
+        if ((rc = upload(d, d->nodeTB[si], TB[si]))) return rc;
+    }
     if ((rc = upload(d, d->st_first_tree, c.stage_first_tree))) return rc;
     if ((rc = upload(d, d->st_ntrees, c.stage_ntrees))) return rc;
     if ((rc = upload(d, d->st_thr, c.stage_thr))) return rc;
@@ -219,6 +231,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint4>();
     b.nodeM = d->nodeM.as<uint32_t>();
+    for (int si = 0; si < 2; ++si) { b.nodeTA[si] = d->nodeTA[si].as<uint4>(); b.nodeTB[si] = d->nodeTB[si].as<uint4>(); }
     b.tail_warps = std::max(1, std::min(8, 60000 / ((c.win_w + 1) * (c.win_h + 1) * 4)));
     b.stage_first_tree = d->st_first_tree.as<int32_t>(); b.stage_ntrees = d->st_ntrees.as<int32_t>();
     b.stage_thr = d->st_thr.as<float>(); b.tree_first_node = d->tree_first_node.as<int32_t>();
@@ -275,7 +288,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     }
     mark(d, 7);
     int tail_blocks = 0;
-    if (d->dense_stages < c.nstages() && !p.levels.empty()) {
+    if (false && d->dense_stages < c.nstages() && !p.levels.empty()) {   // the scan finishes every window in-tile
         tail_blocks = std::max(1, (d->sm_count * 8 * (8 / b.tail_warps) + nframes - 1) / nframes);
         launch_tail(b, tail_blocks, st);
     }
@@ -452,7 +465,7 @@ void ugd_destroy(ugd_detector* d) {
     if (d->stream) cudaStreamSynchronize(d->stream);
     { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     for (auto& kv : d->plans) kv.second->release();
-    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->nodeM, &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
                      &d->carryS, &d->carryQ, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};

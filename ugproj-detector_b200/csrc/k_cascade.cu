@@ -68,6 +68,7 @@ ScanGeom make_scan_geom(int win_w, int win_h) {
 static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     // byte offset
     return 4 * (si ? y * g.TP[1] + (x & 1) * g.TCH[1] + (x >> 1) : y * g.TP[0] + x);
 }
+int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y) { return tile_off(g, si, x, y); }
 
 // Which in-tile evaluator a cascade gets: 1 = stumps, 2 = two-node trees (root + one child), both with
 // exact "base + deltas" stage sums; 0 = the generic evaluator (any tree shape, plain leaf sums).
@@ -327,6 +328,48 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
     }
 }
 
+// ---- per-lane node evaluation against a window in shared memory (lanes = weak classifiers) ----
+// Node data: merged corner lists whose BYTE offsets (from the window's origin) were computed at load time
+// for each memory layout; two offsets share a 32-bit word, so one add of (base | base << 16) rebases both.
+__device__ __forceinline__ int lds32(uint32_t addr) {
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ int sx8(uint32_t w, int byte) { return (int)(int8_t)(w >> (8 * byte)); }
+
+// response of tail node n against the patch whose shared-memory byte address is packed in pb2
+__device__ __forceinline__ int tail_resp(const DevBufs& b, const uint4* __restrict__ nA, const uint4* __restrict__ nB, int n, uint32_t pb2, uint32_t nc, uint4& C) {
+    const uint4 A = __ldg(nA + n);
+    const uint4 B = __ldg(nB + n);
+    C = __ldg(b.nodeC + n);
+    const uint32_t o01 = A.x + pb2, o23 = A.y + pb2, o45 = A.z + pb2;
+    int a = sx8(B.z, 0) * lds32(o01 & 0xffffu) + sx8(B.z, 1) * lds32(o01 >> 16) + sx8(B.z, 2) * lds32(o23 & 0xffffu);
+    int c = sx8(B.z, 3) * lds32(o23 >> 16) + sx8(B.w, 0) * lds32(o45 & 0xffffu) + sx8(B.w, 1) * lds32(o45 >> 16);
+    if (nc > 6) {
+        const uint32_t o67 = A.w + pb2;
+        a += sx8(B.w, 2) * lds32(o67 & 0xffffu);
+        c += sx8(B.w, 3) * lds32(o67 >> 16);
+        if (nc > 8) {
+            const uint32_t o89 = B.x + pb2;
+            a += sx8(C.x, 0) * lds32(o89 & 0xffffu);
+            if (nc > 9) {
+                const uint32_t oab = B.y + pb2;
+                c += sx8(C.x, 1) * lds32(o89 >> 16);
+                a += sx8(C.x, 2) * lds32(oab & 0xffffu);
+                c += sx8(C.x, 3) * lds32(oab >> 16);
+            }
+        }
+    }
+    return a + c;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
     constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols;
@@ -334,7 +377,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     extern __shared__ int s_tile[];
     __shared__ float s_vnf[R * C];
     __shared__ unsigned s_alive[3][32];                // rotating survivor masks, one word per bank class
-    __shared__ int s_qbase;
+    __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
+    __shared__ int s_pop;
     __shared__ unsigned int s_ctr[4];                  // evaluated, lowvar, near, weak
 
     const WorkItem it = wk[blockIdx.x];
@@ -465,12 +509,14 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
             const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
             if (MODE) {
-                // exact evaluators: a warp takes 4 consecutive rounds at once (4 windows per lane share
-                // every node fetch); ceil(rounds / 4) warps work, the others wait at the barrier
+                // exact evaluators: the rounds are dealt evenly to the warps (warp w takes rounds
+                // [w*rounds/NW, (w+1)*rounds/NW)), up to 4 consecutive rounds at once: the windows a lane
+                // holds share every node fetch
                 unsigned mm = m;
-                for (int i = 0; i < 4 * w; ++i) mm &= mm - 1;
-                for (int g = 4 * w; g < rounds; g += 4 * NW) {
-                    const int K = min(4, rounds - g);
+                const int g_end = ((w + 1) * rounds) / NW;
+                for (int i = 0; i < (w * rounds) / NW; ++i) mm &= mm - 1;
+                for (int g = (w * rounds) / NW; g < g_end; g += 4) {
+                    const int K = min(4, g_end - g);
                     int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
@@ -489,6 +535,10 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                         const char* t2[2] = {tw[0], tw[1]}; float v2[2] = {vn[0], vn[1]}; double s2[2];
                         stage_eval<MODE, 2>(s, si, t2, v2, s2);
                         sum[0] = s2[0]; sum[1] = s2[1]; sum[2] = sum[3] = 0.0;
+                    } else if (K == 3) {
+                        const char* t3[3] = {tw[0], tw[1], tw[2]}; float v3[3] = {vn[0], vn[1], vn[2]}; double s3[3];
+                        stage_eval<MODE, 3>(s, si, t3, v3, s3);
+                        sum[0] = s3[0]; sum[1] = s3[1]; sum[2] = s3[2]; sum[3] = 0.0;
                     } else {
                         stage_eval<MODE, 4>(s, si, tw, vn, sum);
                     }
@@ -515,7 +565,6 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                         }
                     }
                     if (passbits) atomicOr(&s_alive[nxt][lane], passbits);
-                    for (int i = 0; i < 4 * (NW - 1); ++i) mm &= mm - 1;
                 }
             } else {
             unsigned mm = m;
@@ -548,25 +597,84 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
             __syncthreads();
             cur = nxt; ++s;
         }
-        // ---- 4. survivors -> the frame's work queue (they resume at stage s) ----
-        if (total > 0 && s < nstages && w == 0) {
-            const int cnt = __popc(m);
-            int incl = cnt;
+        // ---- 4. the few survivors of the in-tile stages: block-local work queue, one window per warp at a
+        //         time, the 32 lanes evaluate 32 weak classifiers of a stage against the tile in shared memory ----
+        if (total > 0 && s < nstages) {
+            if (w == 0) {
+                const int cnt = __popc(m);
+                int incl = cnt;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d) incl += v;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                int pos = incl - cnt;
+                for (unsigned mm = m; mm; mm &= mm - 1) {
+                    const int bit = __ffs((int)mm) - 1;
+                    const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
+                    s_list[pos++] = (uint16_t)(rl * C + c);
+                }
+                if (lane == 0) s_pop = 0;
             }
-            int qb = 0;
-            if (lane == 31) qb = atomicAdd(&b.qcount[frame], total);
-            qb = __shfl_sync(0xffffffffu, qb, 31) + incl - cnt;
-            uint4* qdst = b.queue + (size_t)frame * b.pos_stride + qb;
-            for (unsigned mm = m; mm; mm &= mm - 1) {
-                const int bit = __ffs((int)mm) - 1;
-                const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
-                const int qx = (xi0 + c) * step, qy = (r0 + rl) * step;
-                *qdst++ = make_uint4((uint32_t)qx | (uint32_t)qy << 12 | (uint32_t)it.level << 24,
-                                     __float_as_uint(s_vnf[rl * C + c]), (uint32_t)s, 0u);
+            __syncthreads();
+            const uint4* __restrict__ nA = b.nodeTA[si];
+            const uint4* __restrict__ nB = b.nodeTB[si];
+            for (;;) {
+                int i = 0;
+                if (lane == 0) i = atomicAdd(&s_pop, 1);
+                i = __shfl_sync(0xffffffffu, i, 0);
+                if (i >= total) break;
+                const int id = s_list[i], rl = id >> 6, c = id & (C - 1);
+                const float vnf = s_vnf[id];
+                const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + (rl * step) * TP + c);
+                const uint32_t pb2 = pbase | pbase << 16;
+                int st = s;
+                double sum = 0.0;
+                for (; st < nstages; ++st) {
+                    const int nt = b.stage_ntrees[st];
+                    double part = 0.0;
+                    if (MODE == 1) {
+                        const int n0 = b.stage_first_node[st];
+                        for (int t = lane; t < nt; t += 32) {
+                            const int n = n0 + t;
+                            uint4 Cq;
+                            const int r = tail_resp(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
+                            const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
+                            part += (double)__uint_as_float(lt ? Cq.z : Cq.w);
+                        }
+                        if (lane == 0) weak += (unsigned)nt;
+                    } else {
+                        const int t0 = b.stage_first_tree[st];
+                        unsigned visited = 0;
+                        for (int t = lane; t < nt; t += 32) {
+                            const int base = b.tree_first_node[t0 + t];
+                            int at = 0;
+                            float leaf;
+                            for (;;) {
+                                const uint32_t M = __ldg(b.nodeM + base + at);
+                                uint4 Cq;
+                                const int r = tail_resp(b, nA, nB, base + at, pb2, M & 255u, Cq);
+                                ++visited;
+                                const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
+                                leaf = __uint_as_float(lt ? Cq.z : Cq.w);
+                                const int go = lt ? ((M >> 8) & 255u) : ((M >> 16) & 255u);
+                                if (!go) break;
+                                at = go;
+                            }
+                            part += (double)leaf;
+                        }
+                        visited = __reduce_add_sync(0xffffffffu, visited);
+                        if (lane == 0) weak += visited;
+                    }
+                    sum = warp_sum(part);
+                    const float thr = b.stage_thr[st];
+                    if (lane == 0 && near_thr(sum, thr)) atomicAdd(&s_ctr[2], 1u);
+                    if (sum < (double)thr) break;
+                }
+                if (lane == 0) {
+                    if (st == nstages) emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum);
+                    if (map) map[(r0 + rl) * nxg_pad + xi0 + c] = (int16_t)st;
+                }
             }
         }
     }
@@ -600,45 +708,6 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
 // Node data: merged corner lists whose patch BYTE offsets were computed at load time; two offsets
 // share a 32-bit word, so one add of (patch base | patch base << 16) rebases both.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int lds32(uint32_t addr) {
-    int v;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ int sx8(uint32_t w, int byte) { return (int)(int8_t)(w >> (8 * byte)); }
-
-// response of tail node n against the patch whose shared-memory byte address is packed in pb2
-__device__ __forceinline__ int tail_resp(const DevBufs& b, int n, uint32_t pb2, uint32_t nc, uint4& C) {
-    const uint4 A = __ldg(b.nodeA + n);
-    const uint4 B = __ldg(b.nodeB + n);
-    C = __ldg(b.nodeC + n);
-    const uint32_t o01 = A.x + pb2, o23 = A.y + pb2, o45 = A.z + pb2;
-    int a = sx8(B.z, 0) * lds32(o01 & 0xffffu) + sx8(B.z, 1) * lds32(o01 >> 16) + sx8(B.z, 2) * lds32(o23 & 0xffffu);
-    int c = sx8(B.z, 3) * lds32(o23 >> 16) + sx8(B.w, 0) * lds32(o45 & 0xffffu) + sx8(B.w, 1) * lds32(o45 >> 16);
-    if (nc > 6) {
-        const uint32_t o67 = A.w + pb2;
-        a += sx8(B.w, 2) * lds32(o67 & 0xffffu);
-        c += sx8(B.w, 3) * lds32(o67 >> 16);
-        if (nc > 8) {
-            const uint32_t o89 = B.x + pb2;
-            a += sx8(C.x, 0) * lds32(o89 & 0xffffu);
-            if (nc > 9) {
-                const uint32_t oab = B.y + pb2;
-                c += sx8(C.x, 1) * lds32(o89 >> 16);
-                a += sx8(C.x, 2) * lds32(oab & 0xffffu);
-                c += sx8(C.x, 3) * lds32(oab >> 16);
-            }
-        }
-    }
-    return a + c;
-}
-
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-    return v;
-}
-
 __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
     extern __shared__ int32_t s_patch[];                       // tail_warps x (win_h+1)*(win_w+1) ints
     const int frame = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -690,7 +759,7 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
                 for (int t = lane; t < nt; t += 32) {
                     const int n = n0 + t;
                     uint4 C;
-                    const int r = tail_resp(b, n, pb2, __ldg(b.nodeM + n) & 255u, C);
+                    const int r = tail_resp(b, b.nodeA, b.nodeB, n, pb2, __ldg(b.nodeM + n) & 255u, C);
                     const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
                     part += (double)__uint_as_float(lt ? C.z : C.w);
                     ++weak_cnt;
@@ -703,7 +772,7 @@ __global__ void __launch_bounds__(256) k_tail(DevBufs b) {
                     for (;;) {
                         const uint32_t M = __ldg(b.nodeM + base + at);
                         uint4 C;
-                        const int r = tail_resp(b, base + at, pb2, M & 255u, C);
+                        const int r = tail_resp(b, b.nodeA, b.nodeB, base + at, pb2, M & 255u, C);
                         ++weak_cnt;
                         const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
                         leaf = __uint_as_float(lt ? C.z : C.w);

@@ -32,7 +32,7 @@ static_assert(sizeof(DNode) == 160, "DNode layout");
 
 constexpr int kTileRows = 16;             // scan tile: kTileRows x kTileCols windows = 32 per bank class
 constexpr int kTileCols = 64;
-constexpr int kScanWarps = 4;              // warps per scan block
+constexpr int kScanWarps = 8;              // warps per scan block
 struct ScanGeom {                          // per layout (step 1 / step 2)
     int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
     int SH[2];                             // bank shift between consecutive window rows: (step * TP) mod 32
@@ -56,6 +56,7 @@ struct DevBufs {
     // tail node n: A = 8 x u16 patch byte offsets (corners 0-7); B = {off8|off9<<16, off10|off11<<16, coef0-3, coef4-7};
     //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
     const uint4* nodeA; const uint4* nodeB; const uint4* nodeC; const uint32_t* nodeM;
+    const uint4* nodeTA[2]; const uint4* nodeTB[2];   // A/B with byte offsets into the scan tile (grid step 1 / 2 layouts)
     int tail_warps;                                   // warps per k_tail block (all patches must sit below 64 KB)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
     const int32_t* tree_first_node; const int32_t* stage_first_node;
@@ -86,6 +87,7 @@ struct DevBufs {
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
 ScanGeom make_scan_geom(int win_w, int win_h);
+int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int scan_mode(const Cascade& c);
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
 
