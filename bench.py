@@ -282,7 +282,7 @@ def main():
             "k_resize": src_px + level_px,                         # 1 B/source px read once + 1 B/level px written
             "k_colsum": level_px,                                  # 1 B/level px read (carry rows are noise)
             "k_integral": level_px + 8 * int_entries,              # 1 B read + two int32 planes written
-            "k_scan": 0.0, "k_tail": 0.0,                          # L1/shared-bound, see roofline below
+            "k_scan": 0.0,                                         # L1/shared-bound, see roofline below
         }
         # cascade: 4-byte gathers; merged corner lists need 7.5 per weak classifier on average for alt
         # (6/8/9 distinct corners instead of 8/12), + 8 for the variance norm of every window
@@ -299,12 +299,12 @@ def main():
             if alg.get(k):
                 gbs = alg[k] * GROUP / (v["ms_per_launch"] * 1e-3) / 1e9
                 v.update({"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak})
-        casc_ms = sum(kern[k]["ms_per_launch"] for k in ("k_scan", "k_tail") if k in kern)
+        casc_ms = kern["k_scan"]["ms_per_launch"] if "k_scan" in kern else 0.0   # both scan launches of a group
         l1_peak = 148 * 128 * sm_max * 1e6 / 1e9               # GB/s: 148 SMs x 128 B/clk x max SM clock
         casc_gbs = gather_bytes * GROUP / (casc_ms * 1e-3) / 1e9 if casc_ms else 0.0
         dominant = max(kern, key=lambda k: kern[k]["ms_per_launch"]) if kern else None
-        if dominant in ("k_scan", "k_tail"):
-            roof = {"kernel": "cascade (k_scan+k_tail)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
+        if dominant == "k_scan":
+            roof = {"kernel": "k_scan (window scan + all cascade stages)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
                     "unit": "GB/s", "frac": casc_gbs / l1_peak, "traffic": None,
                     "note": "gather/threshold work: bounded by L1/shared-memory throughput (148 SM x 128 B/clk x "
                             f"{sm_max:.0f} MHz), not HBM; algorithmic bytes = 4 B x (8 norm corners per window + "
@@ -324,7 +324,7 @@ def main():
                    "sample": f"{cn} of the step's {nF} frames in {cdt:.1f} s, cv2 detectMultiScale, "
                              f"{os.cpu_count()} host cpus"}
         groups = (nF + GROUP - 1) // GROUP
-        launches_per_step = groups * 8                          # resize, colsum, carry, integral, scan (2: grid step 2 / 1 levels), tail, group
+        launches_per_step = groups * 7                          # resize, colsum, carry, integral, scan x2 (grid step 2 / step 1 levels), group
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,

@@ -52,7 +52,7 @@ typedef struct {
     uint8_t skin_upper[3];    /* Y,Cr,Cb  default 255,173,127            (structure.cc:79-82)        */
     uint8_t _pad[2];
     int32_t dense_stages;     /* engine tuning: cascade stages evaluated inside the scan tiles before
-                                 survivors move to the global work queue; 0 = engine default.
+                                 survivors move to the block-local work queue; 0 = engine default.
                                  Does not change results.                                            */
     int32_t max_raw_per_frame;/* capacity of the per-frame candidate list fed to groupRectangles;
                                  0 = engine default (8192)                                           */
@@ -78,7 +78,7 @@ typedef struct {
     int64_t grid_windows;       /* grid positions (all frames)                                       */
     int64_t windows_evaluated;  /* grid positions minus x-skipped ones == oracle runAt calls         */
     int64_t lowvar;             /* windows rejected by the variance test                             */
-    int64_t queued;             /* windows that survived the dense stages and entered the work queue */
+    int64_t queued;             /* windows that survived the dense stages and entered a work queue */
     int64_t raw;                /* accepted windows before grouping                                  */
     int64_t grouped;            /* rectangles returned                                               */
     int64_t near_threshold;     /* windows whose stage sum lay within 1e-5 relative of a stage
@@ -97,7 +97,7 @@ enum { UGD_K_PREPROCESS = 0,    /* BGR -> gray + skin mask + histogram          
        UGD_K_INTEGRAL,          /* integral phase 3: S and SQ planes                  (a8)           */
        UGD_K_SCAN,              /* tiled window scan: variance norm, x-skip, in-tile
                                    stages with block-wide compaction                  (a9)           */
-       UGD_K_TAIL,              /* queued windows, remaining stages                   (a9)           */
+       UGD_K_TAIL,              /* slot kept for ABI stability: never launched (the scan finishes every window) */
        UGD_K_GROUP,             /* groupRectangles + clip + skin post-filter          (a10-a12)      */
        UGD_K_COUNT };
 

@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM = range(8)
-K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_scan", "k_tail",
+K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_scan", "k_tail(unused)",
            "k_group")
 
 

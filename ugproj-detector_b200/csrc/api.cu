@@ -51,9 +51,9 @@ struct ugd_detector {
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
-    DevPtr nodeA, nodeB, nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
+    DevPtr nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
-    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, queue, qcount, raw, rawsum,
+    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, raw, rawsum,
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
     // host staging (pinned)
     ugd_rect* h_out = nullptr; int* h_counts = nullptr; unsigned long long* h_ctr = nullptr;
@@ -110,10 +110,9 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
 
 int upload_cascade(ugd_detector* d) {
     const Cascade& c = *d->casc;
-    // Tail arrays: merged corner lists with byte offsets into the (win+1)x(win+1) shared-memory patch.
+    // Per-lane evaluator arrays: merged corner lists with byte offsets into the scan tile (two layouts).
     // Inside a stage of a stump cascade the nodes are ordered by corner count so that the 32 nodes a
     // warp evaluates together take the same branches (stage sums are order-independent).
-    const int PW = c.win_w + 1;
     std::vector<int> order(c.nnodes());
     for (int i = 0; i < c.nnodes(); ++i) order[i] = i;
     if (c.max_tree_nodes == 1)
@@ -121,19 +120,17 @@ int upload_cascade(ugd_detector* d) {
             std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
     const ScanGeom geom = make_scan_geom(c.win_w, c.win_h);
-    std::vector<uint4> A(c.nnodes()), B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
+    std::vector<uint4> B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
     for (int si = 0; si < 2; ++si) { TA[si].resize(c.nnodes()); TB[si].resize(c.nnodes()); }
     std::vector<uint32_t> M(c.nnodes());
     for (int i = 0; i < c.nnodes(); ++i) {
         const CornerNode& cn = c.corners[order[i]];
         const HostNode& h = c.nodes[order[i]];
-        uint32_t off[12], cf[12];
+        uint32_t cf[12];
         for (int j = 0; j < 12; ++j) {
-            off[j] = (uint32_t)(4 * (cn.cy[j] * PW + cn.cx[j]));
             cf[j] = (uint32_t)(uint8_t)cn.coef[j];
         }
-        A[i] = make_uint4(off[0] | off[1] << 16, off[2] | off[3] << 16, off[4] | off[5] << 16, off[6] | off[7] << 16);
-        B[i] = make_uint4(off[8] | off[9] << 16, off[10] | off[11] << 16,
+        B[i] = make_uint4(0u, 0u,
                           cf[0] | cf[1] << 8 | cf[2] << 16 | cf[3] << 24, cf[4] | cf[5] << 8 | cf[6] << 16 | cf[7] << 24);
         for (int si = 0; si < 2; ++si) {              // the same lists with offsets into the scan tile
             uint32_t to[12];
@@ -147,8 +144,6 @@ int upload_cascade(ugd_detector* d) {
         M[i] = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16;
     }
     int rc;
-    if ((rc = upload(d, d->nodeA, A))) return rc;
-    if ((rc = upload(d, d->nodeB, B))) return rc;
     if ((rc = upload(d, d->nodeC, C))) return rc;
     if ((rc = upload(d, d->nodeM, M))) return rc;
     for (int si = 0; si < 2; ++si) {
@@ -190,8 +185,6 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->SQ.reserve(F * p.int_ints * 4 + 256));
     CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
     CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
-    CK(d->queue.reserve(F * p.pos_entries * 16 + 256));
-    CK(d->qcount.reserve(F * 4));
     CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
     CK(d->rawsum.reserve(F * d->rawcap * sizeof(double)));
     CK(d->rawcount.reserve(F * 4));
@@ -229,10 +222,9 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.stumps_only = c.max_tree_nodes == 1;
     b.fast_scan = scan_mode(c);
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
-    b.nodeA = d->nodeA.as<uint4>(); b.nodeB = d->nodeB.as<uint4>(); b.nodeC = d->nodeC.as<uint4>();
+    b.nodeC = d->nodeC.as<uint4>();
     b.nodeM = d->nodeM.as<uint32_t>();
     for (int si = 0; si < 2; ++si) { b.nodeTA[si] = d->nodeTA[si].as<uint4>(); b.nodeTB[si] = d->nodeTB[si].as<uint4>(); }
-    b.tail_warps = std::max(1, std::min(8, 60000 / ((c.win_w + 1) * (c.win_h + 1) * 4)));
     b.stage_first_tree = d->st_first_tree.as<int32_t>(); b.stage_ntrees = d->st_ntrees.as<int32_t>();
     b.stage_thr = d->st_thr.as<float>(); b.tree_first_node = d->tree_first_node.as<int32_t>();
     b.stage_first_node = d->st_first_node.as<int32_t>();
@@ -251,7 +243,6 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.S = d->S.as<int32_t>(); b.SQ = d->SQ.as<int32_t>(); b.int_stride = p.int_ints;
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
     b.pos_stride = p.pos_entries;
-    b.queue = d->queue.as<uint4>(); b.qcount = d->qcount.as<int>();
     b.tile_min = d->tile_min;
     b.raw = d->raw.as<ugd_rect>(); b.rawsum = d->rawsum.as<double>(); b.rawcap = d->rawcap; b.rawcount = d->rawcount.as<int>();
     b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
@@ -261,7 +252,6 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.counters = d->counters.as<unsigned long long>();
     cudaStream_t st = d->stream;
 
-    CK(cudaMemsetAsync(b.qcount, 0, (size_t)nframes * 4, st));
     CK(cudaMemsetAsync(b.rawcount, 0, (size_t)nframes * 4, st));
     CK(cudaMemsetAsync(b.counters, 0, (size_t)nframes * kCtrPerFrame * 8, st));
     if (b.stage_map) CK(cudaMemsetAsync(b.stage_map, 0x80, p.pos_entries * 2, st));
@@ -287,11 +277,6 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
         launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st);
     }
     mark(d, 7);
-    int tail_blocks = 0;
-    if (false && d->dense_stages < c.nstages() && !p.levels.empty()) {   // the scan finishes every window in-tile
-        tail_blocks = std::max(1, (d->sm_count * 8 * (8 / b.tail_warps) + nframes - 1) / nframes);
-        launch_tail(b, tail_blocks, st);
-    }
     mark(d, 8);
     launch_group(b, st);
     mark(d, 9);
@@ -308,23 +293,19 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
         const unsigned long long* k = d->h_ctr + (size_t)f * kCtrPerFrame;
         d->ctr.windows_evaluated += (int64_t)k[CTR_EVALUATED];
         d->ctr.lowvar += (int64_t)k[CTR_LOWVAR];
+        d->ctr.queued += (int64_t)k[CTR_QUEUED];
         d->ctr.raw += (int64_t)k[CTR_RAW];
         d->ctr.grouped += (int64_t)k[CTR_GROUPED];
         d->ctr.near_threshold += (int64_t)k[CTR_NEAR];
         d->ctr.weak_evals += (int64_t)k[CTR_WEAK];
         if (k[CTR_RAW_OVERFLOW]) overflow = true;
     }
-    {
-        std::vector<int> qc(nframes);
-        CK(cudaMemcpy(qc.data(), b.qcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost));
-        for (int v : qc) d->ctr.queued += v;
-    }
     d->ctr.frames += nframes;
     d->ctr.grid_windows += p.grid_windows * nframes;
     d->ctr.levels = (int64_t)p.levels.size();
     d->ctr.level_pixels = p.level_pixels;
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, tail_blocks ? 1 : 0, 1};
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 0, 1};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_COUNT; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
@@ -427,7 +408,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
                ugd_detector** out) {
     if (!c || !out || max_w <= 0 || max_h <= 0 || max_batch <= 0) return UGD_ERR_ARG;
     *out = nullptr;
-    if (max_w > 4095 + c->c.win_w || max_h > 4095 + c->c.win_h) return UGD_ERR_CAPACITY;   // queue packs x,y in 12 bits
+    if (max_w > 4095 + c->c.win_w || max_h > 4095 + c->c.win_h) return UGD_ERR_CAPACITY;   // window ids and tile offsets are sized for frames up to 4K
     std::unique_ptr<ugd_detector> up(new ugd_detector);
     ugd_detector* d = up.get();
     d->casc = &c->c;
@@ -465,9 +446,9 @@ void ugd_destroy(ugd_detector* d) {
     if (d->stream) cudaStreamSynchronize(d->stream);
     { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     for (auto& kv : d->plans) kv.second->release();
-    DevPtr* all[] = {&d->nodeA, &d->nodeB, &d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+    DevPtr* all[] = {&d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
-                     &d->carryS, &d->carryQ, &d->queue, &d->qcount, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
+                     &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};
     for (DevPtr* p : all) p->release();
     if (d->h_out) cudaFreeHost(d->h_out);
@@ -521,7 +502,7 @@ int ugd_get_kernel_times(const ugd_detector* d, float* t, int64_t* l) {
 
 const char* ugd_kernel_name(int k) {
     static const char* names[UGD_K_COUNT] = {"k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry",
-                                             "k_integral", "k_scan", "k_tail", "k_group"};
+                                             "k_integral", "k_scan", "k_tail(unused)", "k_group"};
     return k >= 0 && k < UGD_K_COUNT ? names[k] : "?";
 }
 

@@ -17,11 +17,12 @@
 //                 one address per lane) -- this is the ballot/popc compaction of the design, done
 //                 per bank class.  Node data is broadcast from __constant__ as merged corner lists
 //                 (6/8/9 LDS + IMAD per weak classifier);
-//              4. when fewer than `tile_min` windows are left (or the in-tile stages are exhausted)
-//                 the survivors go to the frame's global work queue.
-//   k_tail : persistent warps pull queued windows; the window's (win+1)^2 patch of S is staged in
-//            shared memory once, then the 32 lanes evaluate 32 weak classifiers of a stage in
-//            parallel and a warp reduction forms the stage sum.
+//              4. this goes on for the `dense_stages` first stages, or until fewer than `tile_min` windows
+//                 are left in the tile;
+//              5. the few windows that are left are finished by a block-local work queue: each warp pops
+//                 one window at a time and its 32 lanes evaluate 32 weak classifiers of a stage in
+//                 parallel against the same shared tile (node data from global memory through L1), a
+//                 warp reduction forms the stage sum.
 //
 // Exactness: feature sums are int32 (exact: weights are small integers), the one rounding step is
 // val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, exact for the shipped cascades
@@ -338,8 +339,8 @@ __device__ __forceinline__ int lds32(uint32_t addr) {
 }
 __device__ __forceinline__ int sx8(uint32_t w, int byte) { return (int)(int8_t)(w >> (8 * byte)); }
 
-// response of tail node n against the patch whose shared-memory byte address is packed in pb2
-__device__ __forceinline__ int tail_resp(const DevBufs& b, const uint4* __restrict__ nA, const uint4* __restrict__ nB, int n, uint32_t pb2, uint32_t nc, uint4& C) {
+// response of node n against the window whose shared-memory byte address is packed in pb2
+__device__ __forceinline__ int lane_resp(const DevBufs& b, const uint4* __restrict__ nA, const uint4* __restrict__ nB, int n, uint32_t pb2, uint32_t nc, uint4& C) {
     const uint4 A = __ldg(nA + n);
     const uint4 B = __ldg(nB + n);
     C = __ldg(b.nodeC + n);
@@ -379,7 +380,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     __shared__ unsigned s_alive[3][32];                // rotating survivor masks, one word per bank class
     __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
     __shared__ int s_pop;
-    __shared__ unsigned int s_ctr[4];                  // evaluated, lowvar, near, weak
+    __shared__ unsigned int s_ctr[5];                  // evaluated, lowvar, near, weak, queued
 
     const WorkItem it = wk[blockIdx.x];
     const int frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
@@ -398,7 +399,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     const double area = (double)((ow - 2) * (oh - 2));
     const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
     int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
-    if (tid < 4) s_ctr[tid] = 0;
+    if (tid < 5) s_ctr[tid] = 0;
     unsigned run_par = 0;                              // per owned row: parity of the stage-0 failure run ending just before the next segment
     unsigned weak = 0;                                 // lane 0 of each warp tallies weak classifiers
     const int nw0 = c_stage_first_node[1] - c_stage_first_node[0];
@@ -614,7 +615,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                     const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
                     s_list[pos++] = (uint16_t)(rl * C + c);
                 }
-                if (lane == 0) s_pop = 0;
+                if (lane == 0) { s_pop = 0; s_ctr[4] += (unsigned)total; }
             }
             __syncthreads();
             const uint4* __restrict__ nA = b.nodeTA[si];
@@ -638,7 +639,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                         for (int t = lane; t < nt; t += 32) {
                             const int n = n0 + t;
                             uint4 Cq;
-                            const int r = tail_resp(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
+                            const int r = lane_resp(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
                             const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
                             part += (double)__uint_as_float(lt ? Cq.z : Cq.w);
                         }
@@ -653,7 +654,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                             for (;;) {
                                 const uint32_t M = __ldg(b.nodeM + base + at);
                                 uint4 Cq;
-                                const int r = tail_resp(b, nA, nB, base + at, pb2, M & 255u, Cq);
+                                const int r = lane_resp(b, nA, nB, base + at, pb2, M & 255u, Cq);
                                 ++visited;
                                 const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
                                 leaf = __uint_as_float(lt ? Cq.z : Cq.w);
@@ -680,8 +681,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     }
     if (lane == 0 && weak) atomicAdd(&s_ctr[3], weak);
     __syncthreads();
-    if (tid < 4 && s_ctr[tid]) {
-        const int slot[4] = {CTR_EVALUATED, CTR_LOWVAR, CTR_NEAR, CTR_WEAK};
+    if (tid < 5 && s_ctr[tid]) {
+        const int slot[5] = {CTR_EVALUATED, CTR_LOWVAR, CTR_NEAR, CTR_WEAK, CTR_QUEUED};
         atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + slot[tid]], (unsigned long long)s_ctr[tid]);
     }
 }
@@ -703,114 +704,7 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// Tail: one warp per queued window, lanes over the weak classifiers of a stage.
-// Node data: merged corner lists whose patch BYTE offsets were computed at load time; two offsets
-// share a 32-bit word, so one add of (patch base | patch base << 16) rebases both.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_tail(DevBufs b) {
-    extern __shared__ int32_t s_patch[];                       // tail_warps x (win_h+1)*(win_w+1) ints
-    const int frame = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nwarps = blockDim.x >> 5;
-    const int PW = b.win_w + 1, PH = b.win_h + 1, PN = PW * PH;
-    int32_t* patch = s_patch + warp * PN;
-    const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(patch);
-    const uint32_t pb2 = pbase | pbase << 16;                  // all patches sit below 64 KB (tail_warps)
-    const int qn = min(b.qcount[frame], (int)b.pos_stride);
-    const uint4* queue = b.queue + (size_t)frame * b.pos_stride;
-    const int nstages = b.nstages;
-    const bool stumps = b.stumps_only != 0;
-    unsigned near_cnt = 0;
-    unsigned long long weak_cnt = 0;                          // per-lane tally of evaluated nodes
-    for (int i = blockIdx.x * nwarps + warp; i < qn; i += gridDim.x * nwarps) {
-        const uint4 e = queue[i];
-        const int x = e.x & 4095u, y = (e.x >> 12) & 4095u, level = e.x >> 24;
-        const float vnf = __uint_as_float(e.y);
-        const LevelInfo& L = b.levels[level];
-        const int P = L.P;
-        const int32_t* S = b.S + (size_t)frame * b.int_stride + L.int_off + (size_t)y * P + x;
-        __syncwarp();
-        {
-            // flattened patch index -> (row, col) incrementally; four independent loads in flight per lane
-            int r = 0, c = lane;
-            while (c >= PW) { c -= PW; ++r; }
-            for (int idx = lane; idx < PN; idx += 128) {
-                int off[4], v[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    off[u] = r * P + c;
-                    c += 32;
-                    while (c >= PW) { c -= PW; ++r; }
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) v[u] = (idx + 32 * u < PN) ? __ldg(S + off[u]) : 0;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) if (idx + 32 * u < PN) patch[idx + 32 * u] = v[u];
-            }
-        }
-        __syncwarp();
-        int s = (int)e.z;
-        double sum = 0.0;
-        for (; s < nstages; ++s) {
-            const int t0 = b.stage_first_tree[s], nt = b.stage_ntrees[s];
-            double part = 0.0;
-            if (stumps) {
-                const int n0 = b.stage_first_node[s];
-                for (int t = lane; t < nt; t += 32) {
-                    const int n = n0 + t;
-                    uint4 C;
-                    const int r = tail_resp(b, b.nodeA, b.nodeB, n, pb2, __ldg(b.nodeM + n) & 255u, C);
-                    const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
-                    part += (double)__uint_as_float(lt ? C.z : C.w);
-                    ++weak_cnt;
-                }
-            } else {
-                for (int t = lane; t < nt; t += 32) {
-                    const int base = b.tree_first_node[t0 + t];
-                    int at = 0;
-                    float leaf;
-                    for (;;) {
-                        const uint32_t M = __ldg(b.nodeM + base + at);
-                        uint4 C;
-                        const int r = tail_resp(b, b.nodeA, b.nodeB, base + at, pb2, M & 255u, C);
-                        ++weak_cnt;
-                        const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(C.y);
-                        leaf = __uint_as_float(lt ? C.z : C.w);
-                        const int go = lt ? ((M >> 8) & 255u) : ((M >> 16) & 255u);
-                        if (!go) break;
-                        at = go;
-                    }
-                    part += (double)leaf;
-                }
-            }
-            sum = warp_sum(part);
-            const float thr = b.stage_thr[s];
-            if (lane == 0 && near_thr(sum, thr)) ++near_cnt;
-            if (sum < (double)thr) break;
-        }
-        if (lane == 0) {
-            if (s == nstages) emit_raw(b, frame, L.scale, L.rect_w, L.rect_h, x, y, sum);
-            if (b.stage_map && frame == 0) {
-                const int step = L.step;
-                b.stage_map[L.pos_off + (y / step) * L.nxg_pad + x / step] = (int16_t)s;
-            }
-        }
-    }
-    if (lane == 0 && near_cnt) atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + CTR_NEAR], (unsigned long long)near_cnt);
-#pragma unroll
-    for (int d = 16; d; d >>= 1) weak_cnt += __shfl_xor_sync(0xffffffffu, weak_cnt, d);
-    if (lane == 0 && weak_cnt) atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + CTR_WEAK], weak_cnt);
-}
-
-static int g_tail_smem = 0;
-
 cudaError_t init_kernel_attributes(int win_w, int win_h) {
-    int smem = 8 * (win_w + 1) * (win_h + 1) * (int)sizeof(int32_t);
-    if (smem > g_tail_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        g_tail_smem = smem;
-    }
     const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int);
     if (scan_smem > g_scan_smem) {
         cudaError_t e = cudaFuncSetAttribute(k_scan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
@@ -822,9 +716,5 @@ cudaError_t init_kernel_attributes(int win_w, int win_h) {
     return cudaSuccess;
 }
 
-void launch_tail(const DevBufs& b, int blocks_per_frame, cudaStream_t st) {
-    int smem = b.tail_warps * (b.win_w + 1) * (b.win_h + 1) * (int)sizeof(int32_t);
-    k_tail<<<dim3(blocks_per_frame, b.nframes), b.tail_warps * 32, smem, st>>>(b);
-}
 
 }  // namespace ugd

@@ -52,12 +52,11 @@ struct DevBufs {
     int fast_scan;                                    // scan_mode(cascade): 0 generic, 1 exact stumps, 2 exact two-node trees
     const LevelInfo* levels;
     const uint32_t* xtab; const uint32_t* ytab;
-    // cascade (tail evaluator, SoA in global memory; dense stages live in __constant__)
-    // tail node n: A = 8 x u16 patch byte offsets (corners 0-7); B = {off8|off9<<16, off10|off11<<16, coef0-3, coef4-7};
+    // cascade (per-lane evaluator of the late stages, SoA in global memory; the dense stages live in __constant__)
+    // node n: A = 8 x u16 byte offsets from the window origin (corners 0-7); B = {off8|off9<<16, off10|off11<<16, coef0-3, coef4-7};
     //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
-    const uint4* nodeA; const uint4* nodeB; const uint4* nodeC; const uint32_t* nodeM;
+    const uint4* nodeC; const uint32_t* nodeM;
     const uint4* nodeTA[2]; const uint4* nodeTB[2];   // A/B with byte offsets into the scan tile (grid step 1 / 2 layouts)
-    int tail_warps;                                   // warps per k_tail block (all patches must sit below 64 KB)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
     const int32_t* tree_first_node; const int32_t* stage_first_node;
     // frames
@@ -73,8 +72,7 @@ struct DevBufs {
     uint32_t* carryS; uint32_t* carryQ; size_t carry_stride;
     // window scan
     size_t pos_stride;                                // padded grid positions per frame
-    uint4* queue; int* qcount;                        // per frame: pos_stride entries {x|y<<12|level<<24, vnf, stage, -}, count
-    int tile_min;                                     // hand a tile's survivors to the queue once fewer than this remain
+    int tile_min;                                     // hand a tile's survivors to the per-warp evaluator once fewer than this remain
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
     int16_t* stage_map;                               // frame 0 only, padded layout; may be null
     // grouping / output
@@ -98,7 +96,6 @@ void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
-void launch_tail(const DevBufs& b, int blocks_per_frame, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);
 cudaError_t init_kernel_attributes(int win_w, int win_h);
 
