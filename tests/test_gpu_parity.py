@@ -123,6 +123,21 @@ def test_batch_equals_single_and_720p(dets, synth, orc, cv2ref):
         assert rectset(got[f]) == rectset(cv2ref.detect_multiscale_cv2(cc, frames[f]))
 
 
+def test_pipelined_host_batches(dets, synth):
+    """Host batches larger than max_batch run as a copy/compute pipeline over two staging buffers:
+    9 frames = groups of 4, 4, 1 -- results equal the one-frame calls, for the gray and the BGR entry."""
+    _, det = dets["alt2"]
+    gray = synth.gray_batch(640, 360, 9, seed0=300, nfaces=5)
+    got = det.detect_batch(gray)
+    for f in range(9):
+        assert rectset(got[f]) == rectset(det.detect_gray(gray[f]))
+    bgr = np.stack([synth.bgr_frame(640, 360, 5, 400 + i) for i in range(9)])
+    got = det.detect_batch(bgr)
+    assert det.counters()["frames"] == 9
+    for f in range(9):
+        assert rectset(got[f]) == rectset(det.detect_bgr(bgr[f]))
+
+
 def test_edge_cases(dets, synth, ug):
     casc, det = dets["alt"]
     assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance

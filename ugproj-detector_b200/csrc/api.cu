@@ -48,7 +48,9 @@ struct ugd_detector {
     ugd_params prm{};
     int device = 0, max_w = 0, max_h = 0, max_batch = 1;
     int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 32;
-    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};   // host-input pipeline
+    DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     // cascade on device
     DevPtr nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
@@ -57,7 +59,7 @@ struct ugd_detector {
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
     // host staging (pinned)
     ugd_rect* h_out = nullptr; int* h_counts = nullptr; unsigned long long* h_ctr = nullptr;
-    size_t h_out_cap = 0; int h_outcap_rects = 0;
+    size_t h_out_cap = 0, h_frames_cap = 0;
     // state of the last call
     DevBufs last{};
     const DevPlan* last_plan = nullptr;
@@ -169,7 +171,7 @@ int bind_constants(ugd_detector* d) {
     return UGD_OK;
 }
 
-int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, int outcap) {
+int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, int outcap, int total_frames) {
     const size_t F = (size_t)nframes;
     const size_t px = round_up((size_t)p.w * p.h, 256);
     if (need_bgr) {
@@ -193,25 +195,51 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->outcount.reserve(F * 4));
     CK(d->counters.reserve(F * kCtrPerFrame * 8));
     if (d->want_map) CK(d->stage_map.reserve(p.pos_entries * 2 + 256));
-    size_t need = F * (size_t)outcap;
-    if (need > d->h_out_cap || !d->h_out) {
+    // pinned result staging for the whole call (groups are finished on the host after the last one is enqueued)
+    const size_t need = (size_t)total_frames * (size_t)outcap;
+    if (need > d->h_out_cap || (size_t)total_frames > d->h_frames_cap || !d->h_out) {
         if (d->h_out) cudaFreeHost(d->h_out);
         if (d->h_counts) cudaFreeHost(d->h_counts);
         if (d->h_ctr) cudaFreeHost(d->h_ctr);
         d->h_out = nullptr; d->h_counts = nullptr; d->h_ctr = nullptr;
-        CK(cudaMallocHost((void**)&d->h_out, std::max<size_t>(need, 1) * sizeof(ugd_rect)));
-        CK(cudaMallocHost((void**)&d->h_counts, (size_t)d->max_batch * sizeof(int)));
-        CK(cudaMallocHost((void**)&d->h_ctr, (size_t)d->max_batch * kCtrPerFrame * 8));
-        d->h_out_cap = need;
+        const size_t fr = std::max<size_t>({(size_t)total_frames, d->h_frames_cap, (size_t)d->max_batch});
+        const size_t rects = std::max<size_t>({need, d->h_out_cap, (size_t)1});
+        CK(cudaMallocHost((void**)&d->h_out, rects * sizeof(ugd_rect)));
+        CK(cudaMallocHost((void**)&d->h_counts, fr * sizeof(int)));
+        CK(cudaMallocHost((void**)&d->h_ctr, fr * kCtrPerFrame * 8));
+        d->h_out_cap = rects; d->h_frames_cap = fr;
     }
     return UGD_OK;
 }
 
 void mark(ugd_detector* d, int k) { if (d->profiling) cudaEventRecord(d->ev[k], d->stream); }
 
-// One group of <= max_batch frames already resident on the device.
+// Host side of a finished group: results and counters from the pinned staging area (frames f0 .. f0+n of the call).
+void finish_group(ugd_detector* d, const Plan& p, int f0, int nframes, ugd_rect* out, int cap, int* counts, bool* overflow) {
+    for (int f = 0; f < nframes; ++f) {
+        const int n = d->h_counts[f0 + f];
+        counts[f] = n;
+        memcpy(out + (size_t)f * cap, d->h_out + (size_t)(f0 + f) * cap, (size_t)std::min(n, cap) * sizeof(ugd_rect));
+        const unsigned long long* k = d->h_ctr + (size_t)(f0 + f) * kCtrPerFrame;
+        d->ctr.windows_evaluated += (int64_t)k[CTR_EVALUATED];
+        d->ctr.lowvar += (int64_t)k[CTR_LOWVAR];
+        d->ctr.queued += (int64_t)k[CTR_QUEUED];
+        d->ctr.raw += (int64_t)k[CTR_RAW];
+        d->ctr.grouped += (int64_t)k[CTR_GROUPED];
+        d->ctr.near_threshold += (int64_t)k[CTR_NEAR];
+        d->ctr.weak_evals += (int64_t)k[CTR_WEAK];
+        if (k[CTR_RAW_OVERFLOW]) *overflow = true;
+    }
+    d->ctr.frames += nframes;
+    d->ctr.grid_windows += p.grid_windows * nframes;
+    d->ctr.levels = (int64_t)p.levels.size();
+    d->ctr.level_pixels = p.level_pixels;
+}
+
+// One group of <= max_batch frames already resident on the device (frames f0.. of the call).  With `defer` the
+// function only enqueues (kernels + result copies to pinned memory); the caller synchronises and calls finish_group.
 int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t frame_stride, bool is_bgr, int nframes,
-              ugd_rect* out, int cap, int* counts) {
+              ugd_rect* out, int cap, int* counts, int f0, bool defer) {
     const Plan& p = dp->host;
     const Cascade& c = *d->casc;
     int rc;
@@ -281,29 +309,14 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     launch_group(b, st);
     mark(d, 9);
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(d->h_out, b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(d->h_counts, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(d->h_ctr, b.counters, (size_t)nframes * kCtrPerFrame * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->h_out + (size_t)f0 * cap, b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->h_counts + f0, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->h_ctr + (size_t)f0 * kCtrPerFrame, b.counters, (size_t)nframes * kCtrPerFrame * 8, cudaMemcpyDeviceToHost, st));
+    d->last = b; d->last_plan = dp; d->last_was_bgr = is_bgr;
+    if (defer) return UGD_OK;
     CK(cudaStreamSynchronize(st));
     bool overflow = false;
-    for (int f = 0; f < nframes; ++f) {
-        int n = d->h_counts[f];
-        counts[f] = n;
-        memcpy(out + (size_t)f * cap, d->h_out + (size_t)f * cap, (size_t)std::min(n, cap) * sizeof(ugd_rect));
-        const unsigned long long* k = d->h_ctr + (size_t)f * kCtrPerFrame;
-        d->ctr.windows_evaluated += (int64_t)k[CTR_EVALUATED];
-        d->ctr.lowvar += (int64_t)k[CTR_LOWVAR];
-        d->ctr.queued += (int64_t)k[CTR_QUEUED];
-        d->ctr.raw += (int64_t)k[CTR_RAW];
-        d->ctr.grouped += (int64_t)k[CTR_GROUPED];
-        d->ctr.near_threshold += (int64_t)k[CTR_NEAR];
-        d->ctr.weak_evals += (int64_t)k[CTR_WEAK];
-        if (k[CTR_RAW_OVERFLOW]) overflow = true;
-    }
-    d->ctr.frames += nframes;
-    d->ctr.grid_windows += p.grid_windows * nframes;
-    d->ctr.levels = (int64_t)p.levels.size();
-    d->ctr.level_pixels = p.level_pixels;
+    finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
         const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 0, 1};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_COUNT; ++k) {
@@ -329,12 +342,18 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
     memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
     const size_t ch = is_bgr ? 3 : 1;
     const size_t tight = (size_t)w * h * ch;
-    for (int f0 = 0; f0 < nframes; f0 += d->max_batch) {
+    const size_t st_stride = round_up(tight, 256);
+    // Host frames in more than one group: copies of group g+1 (copy stream) overlap the kernels of group g.
+    const bool tight_host = !is_device && host_row_stride == (size_t)w * ch;
+    const bool pipelined = tight_host && !d->profiling && nframes > d->max_batch;
+    if (pipelined) CK(d->stage2.reserve((size_t)d->max_batch * st_stride + 256));
+    int g = 0;
+    for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
         const int nf = std::min(d->max_batch, nframes - f0);
-        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap))) return rc;
+        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap, nframes))) return rc;
         const uint8_t* dev; size_t stride;
         uint8_t* staging = is_bgr ? d->bgr.as<uint8_t>() : d->gray_in.as<uint8_t>();
-        const size_t st_stride = is_bgr ? round_up(tight, 256) : round_up(tight, 256);
+        if (pipelined && (g & 1)) staging = d->stage2.as<uint8_t>();
         if (is_device) {
             const uint8_t* src = static_cast<const uint8_t*>(frames) + (size_t)f0 * tight;
             if (is_bgr && (((uintptr_t)src & 3) || (tight & 3))) {   // K1 reads 32-bit words: realign
@@ -343,14 +362,28 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
             } else { dev = src; stride = tight; }
         } else {
             const uint8_t* src = static_cast<const uint8_t*>(frames);
-            if (host_row_stride == (size_t)w * ch) {
+            if (pipelined) {
+                const int bi = g & 1;
+                if (g >= 2) CK(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[bi], 0));   // staging[bi] free again
+                CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->copy_stream));
+                CK(cudaEventRecord(d->ev_copied[bi], d->copy_stream));
+                CK(cudaStreamWaitEvent(d->stream, d->ev_copied[bi], 0));
+            } else if (tight_host) {
                 CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->stream));
             } else {                                                   // single strided frame (cv::Mat with step)
                 CK(cudaMemcpy2DAsync(staging, (size_t)w * ch, src, host_row_stride, (size_t)w * ch, h, cudaMemcpyHostToDevice, d->stream));
             }
             dev = staging; stride = st_stride;
         }
-        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, out + (size_t)f0 * cap, cap, counts + f0))) return rc;
+        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, pipelined))) return rc;
+        if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));
+    }
+    if (pipelined) {
+        CK(cudaStreamSynchronize(d->stream));
+        bool overflow = false;
+        for (int f0 = 0; f0 < nframes; f0 += d->max_batch)
+            finish_group(d, dp->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
+        if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     }
     return UGD_OK;
 }
@@ -429,6 +462,8 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
         fprintf(stderr, "ugdet: cudaStreamCreate: %s\n", cudaGetErrorString(e)); return UGD_ERR_CUDA;
     }
     d->stream = d->own_stream;
+    cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&d->ev_copied[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&d->ev_consumed[i], cudaEventDisableTiming); }
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
     if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h)) != cudaSuccess) {
@@ -455,6 +490,9 @@ void ugd_destroy(ugd_detector* d) {
     if (d->h_counts) cudaFreeHost(d->h_counts);
     if (d->h_ctr) cudaFreeHost(d->h_ctr);
     for (auto& ev : d->ev) if (ev) cudaEventDestroy(ev);
+    for (int i = 0; i < 2; ++i) { if (d->ev_copied[i]) cudaEventDestroy(d->ev_copied[i]); if (d->ev_consumed[i]) cudaEventDestroy(d->ev_consumed[i]); }
+    if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
+    d->stage2.release();
     if (d->own_stream) cudaStreamDestroy(d->own_stream);
     delete d;
 }
