@@ -19,8 +19,52 @@ __device__ __forceinline__ bool rect_less(const ugd_rect& a, const ugd_rect& b) 
     return a.width < b.width;
 }
 
+// Phase 1: label[i] = i.   Phase 2: every similar pair (i < j) is united; the pair space of a frame is cut into
+// (i-block, j-chunk) tiles over many CTAs, so deep pyramids with thousands of candidates do not serialise on one SM.
+constexpr int kLinkI = 128, kLinkJ = 8;
+
+__global__ void __launch_bounds__(256) k_group_init(DevBufs b) {
+    const int frame = blockIdx.y, i = blockIdx.x * 256 + threadIdx.x;
+    if (i < min(b.rawcount[frame], b.rawcap)) b.grp_scratch[(size_t)frame * b.grp_stride + i] = i;
+}
+
+// find with path halving.  Only roots are ever CAS-linked, so shortening a non-root's pointer to its
+// grandparent (which is in the same tree and smaller) can never undo a link.
+__device__ __forceinline__ int uf_find(volatile int* parent, int x) {
+    int p = parent[x];
+    while (p != x) {
+        const int g = parent[p];
+        if (g != p) parent[x] = g;
+        x = p; p = g;
+    }
+    return x;
+}
+
+__global__ void __launch_bounds__(kLinkI) k_group_link(DevBufs b) {
+    const int frame = blockIdx.z;
+    const int n = min(b.rawcount[frame], b.rawcap);
+    const int i = blockIdx.x * kLinkI + threadIdx.x;
+    if (blockIdx.x * kLinkI >= n || b.min_neighbors <= 0) return;
+    const ugd_rect* raw = b.raw + (size_t)frame * b.rawcap;
+    int* parent = b.grp_scratch + (size_t)frame * b.grp_stride;
+    const int chunk = (n + kLinkJ - 1) / kLinkJ;
+    const int j0 = max(blockIdx.y * chunk, blockIdx.x * kLinkI + 1), j1 = min((blockIdx.y + 1) * chunk, n);
+    if (i >= n) return;
+    const ugd_rect ri = raw[i];
+    for (int j = max(j0, i + 1); j < j1; ++j) {
+        if (!similar_rects(ri, raw[j])) continue;
+        int a = i, c = j;
+        for (;;) {                                           // unite: the larger root is hung under the smaller one
+            a = uf_find(parent, a); c = uf_find(parent, c);
+            if (a == c) break;
+            const int hi = max(a, c), lo = min(a, c);
+            if (atomicCAS(&parent[hi], hi, lo) == hi) break;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k_group(DevBufs b) {
-    __shared__ int s_changed, s_nkept, s_nfinal;
+    __shared__ int s_nkept, s_nfinal;
     __shared__ unsigned long long s_red[8];
     const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = b.rawcount[frame];
@@ -45,33 +89,15 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
         if (tid == 0) s_nkept = n;
         __syncthreads();
     } else {
-        // ---- connected components of the similarity graph: min-label propagation + pointer jumping ----
-        for (int i = tid; i < n; i += 256) label[i] = i;
-        __syncthreads();
-        for (;;) {
-            if (tid == 0) s_changed = 0;
-            __syncthreads();
-            for (int i = tid; i < n; i += 256) {
-                const ugd_rect ri = raw[i];
-                const int li = label[i];
-                int m = li;
-                for (int j = 0; j < n; ++j) {
-                    const int lj = ((volatile int*)label)[j];
-                    if (lj < m && similar_rects(ri, raw[j])) m = lj;
-                }
-                if (m < li) { atomicMin(&label[i], m); s_changed = 1; }
-            }
-            __syncthreads();
-            for (int i = tid; i < n; i += 256) {             // pointer jumping (labels only ever point inside the class)
-                int l = ((volatile int*)label)[i];
-                int r = ((volatile int*)label)[l];
-                while (r != l) { l = r; r = ((volatile int*)label)[l]; }
-                label[i] = l;
-            }
-            __syncthreads();
-            if (!s_changed) break;
-            __syncthreads();
+        // ---- connected components of the similarity graph: the links were made by k_group_link
+        //      (lock-free union-find, larger root -> smaller root); flatten to the class minimum ----
+        for (int i = tid; i < n; i += 256) {
+            int l = ((volatile int*)label)[i];
+            int r = ((volatile int*)label)[l];
+            while (r != l) { l = r; r = ((volatile int*)label)[l]; }
+            label[i] = l;                                    // roots never change here, so concurrent writes are benign
         }
+        __syncthreads();
         // ---- per-class integer sums -> rounded means ----
         for (int i = tid; i < n; i += 256) { acc[4 * i] = acc[4 * i + 1] = acc[4 * i + 2] = acc[4 * i + 3] = 0; cnt[i] = 0; }
         __syncthreads();
@@ -164,6 +190,10 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
 }
 
 void launch_group(const DevBufs& b, cudaStream_t st) {
+    if (b.min_neighbors > 0) {
+        k_group_init<<<dim3((b.rawcap + 255) / 256, b.nframes), 256, 0, st>>>(b);
+        k_group_link<<<dim3((b.rawcap + kLinkI - 1) / kLinkI, kLinkJ, b.nframes), kLinkI, 0, st>>>(b);
+    }
     k_group<<<b.nframes, 256, 0, st>>>(b);
 }
 
