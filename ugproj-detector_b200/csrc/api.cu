@@ -31,9 +31,9 @@ struct DevPtr {                       // grow-only device allocation
 
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
-    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_scan;
+    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_bands, wk_scan;
     void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release(); wk_colsum.release();
-                     wk_carry.release(); wk_integral.release(); wk_scan.release(); }
+                     wk_carry.release(); wk_integral.release(); wk_bands.release(); wk_scan.release(); }
 };
 
 std::mutex g_const_mu;
@@ -103,6 +103,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_colsum, dp->host.wk_colsum))) return rc;
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_integral, dp->host.wk_integral))) return rc;
+    if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
     *out = dp.get();
@@ -293,11 +294,13 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 2);
     launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), st);
     mark(d, 3);
-    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
+    static const bool old_integral = getenv("UGD_INTEGRAL_3PASS") != nullptr;     // A/B switch: colsum + carry + integral
+    if (old_integral) launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
     mark(d, 4);
-    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
+    if (old_integral) launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
     mark(d, 5);
-    launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
+    if (old_integral) launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
+    else launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
     mark(d, 6);
     {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
@@ -318,7 +321,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     bool overflow = false;
     finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 0, 1};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, old_integral ? 1 : 0, old_integral ? 1 : 0, 1, 1, 0, 1};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_COUNT; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);

@@ -304,6 +304,108 @@ __global__ void __launch_bounds__(256) k_integral(DevBufs b, const WorkItem* __r
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K4'  integral images in ONE pass (replaces colsum + carry + integral): one warp owns a band of 512
+// output columns of one level of one frame and walks it top to bottom.  Lane l holds 16 consecutive columns:
+// per row it loads 16 pixels (one 16-byte load), forms their exclusive prefix (and that of their squares),
+// a warp shuffle scan supplies the offset of the lanes to its left, and the running column sums live in
+// registers from the first row to the last, so nothing is ever re-read and every output element is written
+// once with 16-byte stores.  Bands to the right of the first one add the row sums of the bands on their left
+// (dp4a + redux.sync on pixels that sit in L2).  All arithmetic is uint32 modular, like cv2's int32 SQ plane.
+// ------------------------------------------------------------------------------------------------
+constexpr int kBandCols = 512;
+
+// 256-bit store (sm_100: STG.E.256): a lane's 8 consecutive ints go out as one fully written 32-byte sector
+__device__ __forceinline__ void st256(uint32_t* p, const uint32_t* v) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+                 "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+
+__device__ __forceinline__ uint4 load_px16(const uint8_t* row, int x, int pitch) {
+    return x < pitch ? *reinterpret_cast<const uint4*>(row + x) : make_uint4(0u, 0u, 0u, 0u);
+}
+
+__global__ void __launch_bounds__(32) k_integral_bands(DevBufs b, const WorkItem* __restrict__ wk) {
+    // grid = (frames, bands): consecutive blocks are the SAME band of different frames, so the tall bands of
+    // the large levels are dealt evenly over the SMs and start first
+    const WorkItem it = wk[blockIdx.y];
+    const LevelInfo& L = b.levels[it.level];
+    const int frame = blockIdx.x, lane = threadIdx.x;
+    const int sw = L.sw, sh = L.sh, pitch = L.img_pitch, P = L.P;
+    const int band = it.first, X0 = band * kBandCols + lane * 16;          // first output column of this lane
+    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
+    uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off);
+    uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off);
+    const bool stores = X0 < P;                                            // P and X0 are multiples of 16: all 16 columns or none
+    uint32_t accS[16], accQ[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { accS[k] = 0; accQ[k] = 0; }
+    // row 0 of both planes is zero
+    if (stores) { st256(outS + X0, accS); st256(outS + X0 + 8, accS + 8); st256(outQ + X0, accQ); st256(outQ + X0 + 8, accQ + 8); }
+    constexpr int PF = 4;                                                  // rows in flight: loads run PF rows ahead of the stores
+    uint4 nx[PF];
+#pragma unroll
+    for (int r = 0; r < PF; ++r) nx[r] = r < sh ? load_px16(img + (size_t)r * pitch, X0, pitch) : make_uint4(0u, 0u, 0u, 0u);
+    for (int y0 = 0; y0 < sh; y0 += PF) {
+        uint4 cur[PF];
+        uint32_t leftS[PF], leftQ[PF];
+#pragma unroll
+        for (int r = 0; r < PF; ++r) {
+            cur[r] = nx[r];
+            const int yn = y0 + PF + r;
+            if (yn < sh) nx[r] = load_px16(img + (size_t)yn * pitch, X0, pitch);
+            leftS[r] = 0; leftQ[r] = 0;
+        }
+        // row sums of the bands to the left (pixels beyond sw are zero padding)
+        for (int lb = 0; lb < band; ++lb) {
+            uint4 q[PF];
+#pragma unroll
+            for (int r = 0; r < PF; ++r)
+                q[r] = y0 + r < sh ? load_px16(img + (size_t)(y0 + r) * pitch, lb * kBandCols + lane * 16, pitch) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int r = 0; r < PF; ++r) {
+                uint32_t s = __dp4a(q[r].x, 0x01010101u, 0u), t = __dp4a(q[r].x, q[r].x, 0u);
+                s = __dp4a(q[r].y, 0x01010101u, s); t = __dp4a(q[r].y, q[r].y, t);
+                s = __dp4a(q[r].z, 0x01010101u, s); t = __dp4a(q[r].z, q[r].z, t);
+                s = __dp4a(q[r].w, 0x01010101u, s); t = __dp4a(q[r].w, q[r].w, t);
+                leftS[r] += __reduce_add_sync(0xffffffffu, s);
+                leftQ[r] += __reduce_add_sync(0xffffffffu, t);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < PF; ++r) {
+            const int y = y0 + r;
+            if (y >= sh) break;
+            const uint32_t w4[4] = {cur[r].x, cur[r].y, cur[r].z, cur[r].w};
+            // exclusive prefix inside the lane, added straight into the running column sums
+            uint32_t rs = 0, rq = 0;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const uint32_t p = (w4[k >> 2] >> (8 * (k & 3))) & 255u;
+                accS[k] += rs; accQ[k] += rq;
+                rs += p; rq += p * p;
+            }
+            // exclusive scan of the lane totals across the warp
+            uint32_t is = rs, iq = rq;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t a = __shfl_up_sync(0xffffffffu, is, d), e = __shfl_up_sync(0xffffffffu, iq, d);
+                if (lane >= d) { is += a; iq += e; }
+            }
+            const uint32_t offS = is - rs + leftS[r], offQ = iq - rq + leftQ[r];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) { accS[k] += offS; accQ[k] += offQ; }
+            uint32_t* oS = outS + (size_t)(y + 1) * P + X0;
+            uint32_t* oQ = outQ + (size_t)(y + 1) * P + X0;
+            if (stores) { st256(oS, accS); st256(oS + 8, accS + 8); st256(oQ, accQ); st256(oQ + 8, accQ + 8); }
+        }
+    }
+}
+
+void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_integral_bands<<<dim3(b.nframes, nblocks), 32, 0, st>>>(b, wk);
+}
+
 void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
     if (nblocks) k_colsum<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
 }

@@ -10,6 +10,7 @@ namespace ugd {
 
 constexpr int kStripRows = 32;       // integral strips: 32 output rows each
 constexpr int kChunkCols = 128;      // integral chunk: 128 output columns
+constexpr int kIntBand = 512;        // one-pass integral: output columns per warp (band)
 constexpr int kMaxLevels = 256;
 constexpr int kScanRows = 16;        // grid rows per scan block (a scan tile is 64 x 16 windows, 8 warps)
 
@@ -40,7 +41,7 @@ struct Plan {
     int w = 0, h = 0;
     std::vector<LevelInfo> levels;
     std::vector<uint32_t> xtab, ytab;           // entry = i0 | c1 << 16  (c1 in 0..256)
-    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_integral, wk_scan;
+    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_integral, wk_bands, wk_scan;
     // per-frame sizes
     size_t pyr_bytes = 0, int_ints = 0, pos_entries = 0, carry_ints = 0, map_entries = 0;
     int64_t level_pixels = 0, grid_windows = 0;
