@@ -305,17 +305,27 @@ def main():
         dominant = max(kern, key=lambda k: kern[k]["ms_per_launch"]) if kern else None
         if dominant == "k_scan":
             roof = {"kernel": "k_scan (window scan + all cascade stages)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
-                    "unit": "GB/s", "frac": casc_gbs / l1_peak, "traffic": None,
+                    "unit": "GB/s", "frac": casc_gbs / l1_peak,
+                    # ncu --set full, r01 (profiles/r01_ncu_k_scan_v2_summary.txt, one 64-frame 720p launch group):
+                    # dram read 962.9 MB + write 42.7 MB; the algorithmic HBM bytes are the S and SQ planes read once
+                    "traffic": 1005.6e6 if (w, h, GROUP) == (1280, 720, 64) else None,
+                    "hbm": {"algorithmic_bytes": 8 * int_entries * GROUP,
+                            "achieved": 8 * int_entries * GROUP / (casc_ms * 1e-3) / 1e9 if casc_ms else None,
+                            "peak": hbm_peak, "unit": "GB/s",
+                            "frac": 8 * int_entries * GROUP / (casc_ms * 1e-3) / 1e9 / hbm_peak if casc_ms else None},
                     "note": "gather/threshold work: bounded by L1/shared-memory throughput (148 SM x 128 B/clk x "
                             f"{sm_max:.0f} MHz), not HBM; algorithmic bytes = 4 B x (8 norm corners per window + "
-                            "7.5 corners per weak classifier)"}
+                            "7.5 corners per weak classifier); the `hbm` sub-object gives the same launch against the "
+                            "HBM roofline (planes read once) to show how far from HBM-bound it is"}
         else:
             v = kern.get(dominant, {})
             roof = {"kernel": dominant, "bound": v.get("bound", "hbm"), "achieved": v.get("achieved"), "peak": hbm_peak,
                     "unit": "GB/s", "frac": v.get("frac"), "traffic": None}
         hi = kern.get("k_integral", {})
-        roof_hbm = {"kernel": "k_integral", "bound": "hbm", "achieved": hi.get("achieved"), "peak": hbm_peak,
-                    "unit": "GB/s", "frac": hi.get("frac"), "traffic": None, "peak_source": peak_src}
+        roof_hbm = {"kernel": "k_integral (one-pass k_integral_bands)", "bound": "hbm", "achieved": hi.get("achieved"), "peak": hbm_peak,
+                    "unit": "GB/s", "frac": hi.get("frac"),
+                    # ncu r01 (profiles/r01_ncu_resize_integral_bands_summary.txt): dram read 191.1 MB + write 1030.5 MB per launch
+                    "traffic": 1221.6e6 if (w, h, GROUP) == (1280, 720, 64) else None, "peak_source": peak_src}
 
         cpu = None
         if not args.no_cpu_baseline:

@@ -147,6 +147,16 @@ int  ugd_detect_batch(ugd_detector* d, const void* frames, int is_device, int is
                       ugd_rect* out, int cap, int* counts);
 
 /* ---- observability / parity hooks ------------------------------------------------------------- */
+/* The step right before detectFaces in the tracker: cv::resize(orig, scan.frame_size, INTER_AREA)
+ * (src/tracker/face_tracker.cc:112-114, cfg key scan.frame_size, src/structure.cc:63-67), fused in front of
+ * the detector: full-size BGR frames in, rects in SCAN-frame coordinates out (what track_frame works in).
+ * scan_w/scan_h <= 0 means "no resize" (structure.cc:64-65).  Decimation only. */
+int  ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, int nframes, int src_w, int src_h,
+                             int scan_w, int scan_h, ugd_rect* out, int cap, int* counts);
+/* The resize alone (host in, host out; 1 or 3 channels), for parity tests against cv2.resize(INTER_AREA). */
+int  ugd_resize_area(ugd_detector* d, const uint8_t* src, int src_w, int src_h, int channels, size_t stride_bytes,
+                     uint8_t* dst, int dst_w, int dst_h);
+
 int  ugd_get_counters(const ugd_detector* d, ugd_counters* c);
 /* Per-kernel device time (ms, CUDA events on the detector's stream) of the most recent detect call;
  * recorded only after ugd_set_profiling(d, 1).  times_ms: UGD_K_COUNT entries. */

@@ -35,6 +35,7 @@ void orc_bgr2gray(const uint8_t* bgr, int n, uint8_t* gray);
 void orc_bgr2ycrcb(const uint8_t* bgr, int n, uint8_t* ycrcb);
 void orc_inrange3(const uint8_t* src, int n, const uint8_t lo[3], const uint8_t hi[3], uint8_t* mask);
 void orc_equalize_hist(const uint8_t* src, int n, uint8_t* dst);
+int  orc_resize_area(const uint8_t* src, int sw, int sh, int cn, size_t sstride, uint8_t* dst, int dw, int dh);
 void orc_resize_exact(const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw, int dh);
 void orc_integral(const uint8_t* img, int w, int h, int32_t* S, int32_t* SQ);
 int  orc_scale_list(int W, int H, int ow, int oh, double scale_factor, int min_w, int min_h, int max_w,

@@ -113,6 +113,18 @@ def equalize_hist(gray):
     return out
 
 
+def resize_area(img, dw, dh):
+    """cv2.resize(img, (dw, dh), interpolation=INTER_AREA) for decimation (face_tracker.cc:112-114)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape[:2]
+    cn = 1 if img.ndim == 2 else img.shape[2]
+    out = np.zeros((dh, dw) if img.ndim == 2 else (dh, dw, cn), np.uint8)
+    rc = lib().orc_resize_area(_p(img), w, h, cn, C.c_size_t(w * cn), _p(out), dw, dh)
+    if rc:
+        raise ValueError("INTER_AREA restatement covers decimation only")
+    return out
+
+
 def resize_exact(gray, dw, dh):
     gray = np.ascontiguousarray(gray, np.uint8)
     h, w = gray.shape

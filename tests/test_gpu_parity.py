@@ -138,6 +138,38 @@ def test_pipelined_host_batches(dets, synth):
         assert rectset(got[f]) == rectset(det.detect_bgr(bgr[f]))
 
 
+def test_inter_area_decimation_bit_exact(dets, synth, orc):
+    """SURVEY 8(f) N1: cv::resize(orig, scan.frame_size, INTER_AREA) (face_tracker.cc:112-114) on the device,
+    bit-exact with cv2 and the oracle: the shipped cfg's 2x case, other integral factors, rational factors, gray."""
+    import cv2
+    _, det = dets["alt2"]
+    rng = np.random.default_rng(7)
+    cases = [((720, 1280, 3), (640, 360)), ((1080, 1920, 3), (640, 360)), ((720, 1280, 3), (427, 240)),
+             ((720, 1280, 3), (854, 480)), ((97, 161, 3), (64, 36)), ((360, 640), (320, 180)), ((200, 300, 3), (150, 200))]
+    for shape, (dw, dh) in cases:
+        src = rng.integers(0, 256, shape, dtype=np.uint8)
+        got = det.resize_area(src, dw, dh)
+        assert np.array_equal(got, cv2.resize(src, (dw, dh), interpolation=cv2.INTER_AREA)), (shape, dw, dh)
+        assert np.array_equal(got, orc.resize_area(src, dw, dh))
+    with pytest.raises(Exception):
+        det.resize_area(np.zeros((100, 100, 3), np.uint8), 200, 200)           # enlarging is not the reference's use
+
+
+def test_scaled_detection_matches_reference_pipeline(dets, synth, orc, cv2ref):
+    """Full-size BGR frames -> INTER_AREA to the cfg's 640x360 scan size -> detectFaces, as the tracker does
+    (face_tracker.cc:112-114 then :295): equal to the oracle run on cv2-resized frames."""
+    import cv2
+    _, det = dets["alt2"]
+    oc = orc.OracleCascade.load(cv2ref.cascade_path("alt2"))
+    frames = np.stack([synth.bgr_frame(1280, 720, 8, 500 + i) for i in range(5)])      # 5 frames > max_batch 4
+    got = det.detect_batch_scaled(frames, (640, 360))
+    for f in range(5):
+        small = cv2.resize(frames[f], (640, 360), interpolation=cv2.INTER_AREA)
+        want, _ = orc.detect_faces(oc, small)
+        assert rectset(got[f]) == rectset(want)
+        assert rectset(got[f]) == rectset(det.detect_bgr(small))
+
+
 def test_edge_cases(dets, synth, ug):
     casc, det = dets["alt"]
     assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance

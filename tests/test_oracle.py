@@ -38,6 +38,16 @@ def test_building_blocks_match_cv2(orc, synth):
     assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
 
 
+def test_inter_area_matches_cv2(orc):
+    """8(f) N1: the INTER_AREA restatement (integral and rational factors, 1 and 3 channels) vs cv2.resize."""
+    import cv2
+    rng = np.random.default_rng(3)
+    for shape, (dw, dh) in [((720, 1280, 3), (640, 360)), ((360, 640, 3), (213, 120)), ((90, 160, 3), (107, 60)),
+                            ((90, 160), (100, 50)), ((97, 161, 3), (64, 36)), ((200, 300, 3), (300, 200)), ((200, 300, 3), (100, 50))]:
+        src = rng.integers(0, 256, shape, dtype=np.uint8)
+        assert np.array_equal(orc.resize_area(src, dw, dh), cv2.resize(src, (dw, dh), interpolation=cv2.INTER_AREA)), (shape, dw, dh)
+
+
 def test_integral_wraps_like_cv2(orc):
     import cv2
     g = np.full((720, 1280), 255, np.uint8)

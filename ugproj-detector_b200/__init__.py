@@ -210,6 +210,27 @@ class Detector:
         n, h, w = frames.shape[:3]
         return self._batch(_p(frames), 0, frames.ndim == 4, n, w, h, cap)
 
+    def detect_batch_scaled(self, frames: np.ndarray, scan_size, cap: int = 256):
+        """frames: [N,H,W,3] full-size BGR host array; scan_size = (w, h) as cfg scan.frame_size.  INTER_AREA
+        decimation (face_tracker.cc:112-114) + detectFaces on the device; rects in scan-frame coordinates."""
+        assert frames.dtype == np.uint8 and frames.ndim == 4 and frames.shape[3] == 3
+        frames = np.ascontiguousarray(frames)
+        n, h, w = frames.shape[:3]
+        out = np.zeros((n, cap, 4), np.int32)
+        cnt = np.zeros(n, np.int32)
+        self._ck(lib().ugd_detect_batch_scaled(self._h, _p(frames), 0, n, w, h, int(scan_size[0]), int(scan_size[1]),
+                                               _p(out), cap, _p(cnt)))
+        return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(n)]
+
+    def resize_area(self, img: np.ndarray, dw: int, dh: int) -> np.ndarray:
+        """cv2.resize(img, (dw, dh), interpolation=INTER_AREA) on the device (decimation only)."""
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape[:2]
+        cn = 1 if img.ndim == 2 else img.shape[2]
+        out = np.zeros((dh, dw) if img.ndim == 2 else (dh, dw, cn), np.uint8)
+        self._ck(lib().ugd_resize_area(self._h, _p(img), w, h, cn, C.c_size_t(0), _p(out), dw, dh))
+        return out
+
     def detect_batch_device(self, dev_ptr: int, is_bgr: bool, n: int, w: int, h: int, cap: int = 256):
         return self._batch(C.c_void_p(dev_ptr), 1, is_bgr, n, w, h, cap)
 

@@ -36,6 +36,12 @@ struct DevPlan {                      // a Plan plus its device copies
                      wk_carry.release(); wk_integral.release(); wk_bands.release(); wk_scan.release(); }
 };
 
+struct DevAreaPlan {                  // INTER_AREA tables for one (source size -> scan size) pair
+    AreaPlanHost host;
+    DevPtr xfirst, yfirst, xtaps, ytaps;
+    void release() { xfirst.release(); yfirst.release(); xtaps.release(); ytaps.release(); }
+};
+
 std::mutex g_const_mu;
 const void* g_const_owner = nullptr;  // which detector's dense nodes currently sit in __constant__
 
@@ -52,6 +58,8 @@ struct ugd_detector {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};   // host-input pipeline
     DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
+    std::map<std::vector<int>, std::unique_ptr<DevAreaPlan>> area_plans;
+    DevPtr src_full, area_dst;                        // full-size input frames / standalone resize output
     // cascade on device
     DevPtr nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
@@ -333,6 +341,33 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     return UGD_OK;
 }
 
+int get_area_plan(ugd_detector* d, int sw, int sh, int dw, int dh, DevAreaPlan** out) {
+    const std::vector<int> key{sw, sh, dw, dh};
+    auto it = d->area_plans.find(key);
+    if (it != d->area_plans.end()) { *out = it->second.get(); return UGD_OK; }
+    std::unique_ptr<DevAreaPlan> ap(new DevAreaPlan);
+    if (!build_area_plan(sw, sh, dw, dh, ap->host)) { d->err = "INTER_AREA path covers decimation only (scan size <= frame size)"; return UGD_ERR_UNSUPPORTED; }
+    int rc;
+    if ((rc = upload(d, ap->xfirst, ap->host.xfirst))) return rc;
+    if ((rc = upload(d, ap->yfirst, ap->host.yfirst))) return rc;
+    if ((rc = upload(d, ap->xtaps, ap->host.xtaps))) return rc;
+    if ((rc = upload(d, ap->ytaps, ap->host.ytaps))) return rc;
+    CK(cudaStreamSynchronize(d->stream));
+    *out = ap.get();
+    d->area_plans[key] = std::move(ap);
+    return UGD_OK;
+}
+
+AreaArgs area_args(const DevAreaPlan& ap, const uint8_t* src, size_t row_stride, size_t frame_stride, uint8_t* dst, size_t dst_frame_stride) {
+    AreaArgs a{};
+    a.src = src; a.src_row_stride = row_stride; a.src_frame_stride = frame_stride;
+    a.dst = dst; a.dst_frame_stride = dst_frame_stride;
+    a.dw = ap.host.dw; a.dh = ap.host.dh; a.ix = ap.host.ix; a.iy = ap.host.iy; a.fast = ap.host.fast ? 1 : 0;
+    a.xfirst = ap.xfirst.as<int32_t>(); a.yfirst = ap.yfirst.as<int32_t>();
+    a.xtaps = ap.xtaps.as<AreaTap>(); a.ytaps = ap.ytaps.as<AreaTap>();
+    return a;
+}
+
 int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
                   size_t host_row_stride, ugd_rect* out, int cap, int* counts) {
     if (!d || !frames || !out || !counts || nframes < 0 || cap <= 0 || w <= 0 || h <= 0) return UGD_ERR_ARG;
@@ -484,6 +519,8 @@ void ugd_destroy(ugd_detector* d) {
     if (d->stream) cudaStreamSynchronize(d->stream);
     { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     for (auto& kv : d->plans) kv.second->release();
+    for (auto& kv : d->area_plans) kv.second->release();
+    d->src_full.release(); d->area_dst.release();
     DevPtr* all[] = {&d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
                      &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
@@ -525,6 +562,55 @@ int ugd_detect_gray(ugd_detector* d, const uint8_t* gray, int w, int h, size_t s
 int ugd_detect_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h,
                      ugd_rect* out, int cap, int* counts) {
     return detect_common(d, frames, is_device != 0, is_bgr != 0, nframes, w, h, (size_t)w * (is_bgr ? 3 : 1), out, cap, counts);
+}
+
+int ugd_resize_area(ugd_detector* d, const uint8_t* src, int sw, int sh, int channels, size_t stride, uint8_t* dst, int dw, int dh) {
+    if (!d || !src || !dst || (channels != 1 && channels != 3) || sw <= 0 || sh <= 0) return UGD_ERR_ARG;
+    if (stride == 0) stride = (size_t)sw * channels;
+    if (stride < (size_t)sw * channels) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    DevAreaPlan* ap = nullptr;
+    int rc;
+    if ((rc = get_area_plan(d, sw, sh, dw, dh, &ap))) return rc;
+    const size_t sbytes = (size_t)sw * channels * sh, dbytes = (size_t)dw * channels * dh;
+    CK(d->src_full.reserve(sbytes + 256));
+    CK(d->area_dst.reserve(dbytes + 256));
+    CK(cudaMemcpy2DAsync(d->src_full.p, (size_t)sw * channels, src, stride, (size_t)sw * channels, sh, cudaMemcpyHostToDevice, d->stream));
+    launch_area(area_args(*ap, d->src_full.as<uint8_t>(), (size_t)sw * channels, sbytes, d->area_dst.as<uint8_t>(), dbytes), channels, 1, d->stream);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, d->area_dst.p, dbytes, cudaMemcpyDeviceToHost, d->stream));
+    CK(cudaStreamSynchronize(d->stream));
+    return UGD_OK;
+}
+
+int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, int nframes, int src_w, int src_h, int scan_w,
+                            int scan_h, ugd_rect* out, int cap, int* counts) {
+    if (!d || !frames || !out || !counts || nframes < 0 || cap <= 0 || src_w <= 0 || src_h <= 0) return UGD_ERR_ARG;
+    if (scan_w <= 0 || scan_h <= 0) { scan_w = src_w; scan_h = src_h; }           // scan.frame_size absent: structure.cc:64-65
+    if (scan_w == src_w && scan_h == src_h) return ugd_detect_batch(d, frames, is_device, 1, nframes, src_w, src_h, out, cap, counts);
+    if (scan_w > d->max_w || scan_h > d->max_h) { d->err = "scan size larger than the detector was created for"; return UGD_ERR_CAPACITY; }
+    CK(cudaSetDevice(d->device));
+    DevAreaPlan* ap = nullptr;
+    DevPlan* dp = nullptr;
+    int rc;
+    if ((rc = get_area_plan(d, src_w, src_h, scan_w, scan_h, &ap))) return rc;
+    if ((rc = get_plan(d, scan_w, scan_h, &dp))) return rc;
+    d->ctr = ugd_counters{};
+    memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
+    const size_t stight = (size_t)src_w * src_h * 3, dstride = round_up((size_t)scan_w * scan_h * 3, 256);
+    for (int f0 = 0; f0 < nframes; f0 += d->max_batch) {
+        const int nf = std::min(d->max_batch, nframes - f0);
+        if ((rc = ensure_buffers(d, dp->host, nf, true, cap, nframes))) return rc;
+        const uint8_t* src = static_cast<const uint8_t*>(frames) + (size_t)f0 * stight;
+        if (!is_device) {
+            CK(d->src_full.reserve((size_t)d->max_batch * stight + 256));
+            CK(cudaMemcpyAsync(d->src_full.p, src, (size_t)nf * stight, cudaMemcpyHostToDevice, d->stream));
+            src = d->src_full.as<uint8_t>();
+        }
+        launch_area(area_args(*ap, src, (size_t)src_w * 3, stight, d->bgr.as<uint8_t>(), dstride), 3, nf, d->stream);
+        if ((rc = run_group(d, dp, d->bgr.as<uint8_t>(), dstride, true, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, false))) return rc;
+    }
+    return UGD_OK;
 }
 
 int ugd_get_counters(const ugd_detector* d, ugd_counters* c) {

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <vector>
 
 #include "../../include/ugdet.h"
 #include "cascade.h"
@@ -88,6 +89,23 @@ ScanGeom make_scan_geom(int win_w, int win_h);
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int scan_mode(const Cascade& c);
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
+
+// ---- INTER_AREA decimation to the scan size (k_area.cu) ----
+struct AreaTap { int32_t si; float a; };              // source index, weight
+struct AreaPlanHost {
+    int sw = 0, sh = 0, dw = 0, dh = 0, ix = 1, iy = 1;
+    bool fast = false;                                // both scale factors integral: integer box sums
+    std::vector<int32_t> xfirst, yfirst;              // CSR: taps of destination index i are [first[i], first[i+1])
+    std::vector<AreaTap> xtaps, ytaps;
+};
+struct AreaArgs {
+    const uint8_t* src; size_t src_row_stride, src_frame_stride;
+    uint8_t* dst; size_t dst_frame_stride;
+    int dw, dh, ix, iy, fast;
+    const int32_t* xfirst; const int32_t* yfirst; const AreaTap* xtaps; const AreaTap* ytaps;
+};
+bool build_area_plan(int sw, int sh, int dw, int dh, AreaPlanHost& p);
+void launch_area(const AreaArgs& a, int channels, int nframes, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
 void launch_equalize(const DevBufs& b, cudaStream_t st);
