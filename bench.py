@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--dense-stages", type=int, default=0)
     ap.add_argument("--scale-factor", type=float, default=1.1)
     ap.add_argument("--min-size", type=int, default=30)
+    ap.add_argument("--scan-size", default="", help="WxH: BGR frames of --size are decimated (INTER_AREA) to this scan size "
+                                                    "and run through detectFaces, as the tracker does with conf/*.cfg")
     ap.add_argument("--group", type=int, default=GROUP, help="frames per launch group")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -197,12 +199,18 @@ def main():
     GROUP = min(args.group, nF)
     sf, ms = args.scale_factor, (args.min_size, args.min_size)
     prm = ug.default_params(dense_stages=args.dense_stages, scale_factor=sf, min_size=ms)
-    det = ug.Detector(casc, prm, device=local, max_size=(w, h), max_batch=GROUP)
+    scan = tuple(map(int, args.scan_size.split("x"))) if args.scan_size else None
+    det = ug.Detector(casc, prm, device=local, max_size=scan or (w, h), max_batch=GROUP)
     stream = torch.cuda.current_stream()
     det.set_stream(stream.cuda_stream)
 
     # rank r takes its own contiguous frame range (weak scaling: nF frames per rank per step)
-    host = torch.from_numpy(make_frames(synth, w, h, nF, seed0=1000 * rank)).pin_memory()
+    if scan:
+        base = np.stack([synth.bgr_frame(w, h, synth.default_nfaces(w, h), 1000 * rank + i) for i in range(min(DISTINCT, nF))])
+        frames_np = np.ascontiguousarray(np.concatenate([base] * ((nF + len(base) - 1) // len(base)))[:nF])
+    else:
+        frames_np = make_frames(synth, w, h, nF, seed0=1000 * rank)
+    host = torch.from_numpy(frames_np).pin_memory()
     dev = host.cuda(non_blocking=False)
     host_np = host.numpy()
     sharding = __import__("importlib").import_module(ge.PKG_NAME + ".sharding")
@@ -215,12 +223,15 @@ def main():
         sharding.gather_to_rank0(t, world, rank, nF)
 
     def step_device():
-        r = det.detect_batch_device(dev.data_ptr(), False, nF, w, h, cap=CAP)
+        if scan:
+            r = det.detect_batch_scaled_ptr(dev.data_ptr(), True, nF, w, h, scan, cap=CAP)
+        else:
+            r = det.detect_batch_device(dev.data_ptr(), False, nF, w, h, cap=CAP)
         gather(r)
         return r
 
     def step_host():
-        r = det.detect_batch(host_np, cap=CAP)
+        r = det.detect_batch_scaled(host_np, scan, cap=CAP) if scan else det.detect_batch(host_np, cap=CAP)
         gather(r)
         return r
 
@@ -272,8 +283,9 @@ def main():
         fps = total_frames / (ms_dev * 1e-3)
         fps_e2e = total_frames / (ms_host * 1e-3)
         plan_levels = ctr["levels"]; level_px = ctr["level_pixels"]
-        src_px = w * h
-        sc, lw, lh, stp = det.plan_info(w, h)
+        pw, ph = scan or (w, h)                                 # size the pyramid is built from
+        src_px = pw * ph
+        sc, lw, lh, stp = det.plan_info(pw, ph)
         int_entries = int(sum((int(a) + 1) * (int(b) + 1) for a, b in zip(lw, lh)))
         weak_per_frame = ctr["weak_evals"] / max(ctr["frames"], 1)
         win_per_frame = ctr["windows_evaluated"] / max(ctr["frames"], 1)
@@ -283,6 +295,9 @@ def main():
             "k_colsum": level_px,                                  # 1 B/level px read (carry rows are noise)
             "k_integral": level_px + 8 * int_entries,              # 1 B read + two int32 planes written
             "k_scan": 0.0,                                         # L1/shared-bound, see roofline below
+            "k_area": 3 * (w * h + src_px) if scan else 0.0,       # BGR: 3 B read per source px + 3 B written per scan px
+            "k_preprocess": 5 * src_px if scan else 0.0,           # 3 B read + gray + mask written
+            "k_equalize": 3 * src_px if scan else 0.0,             # gray + mask read, equalised gray written
         }
         # cascade: 4-byte gathers; merged corner lists need 7.5 per weak classifier on average for alt
         # (6/8/9 distinct corners instead of 8/12), + 8 for the variance norm of every window
@@ -329,7 +344,19 @@ def main():
 
         cpu = None
         if not args.no_cpu_baseline:
-            cfps, cn, cdt, cthreads = cpu_reference_run(cv2_ref, host_np[:DISTINCT], args.cascade, 12.0, 128, sf, ms)
+            if scan:                                            # reference pipeline: INTER_AREA resize + detectFaces (skin mask path)
+                import cv2
+                cv2.setNumThreads(os.cpu_count() or 1)
+                cc = cv2_ref.load(cv2_ref.cascade_path(args.cascade))
+                n_, t0_ = 0, time.perf_counter()
+                while n_ < 128 and time.perf_counter() - t0_ < 12.0:
+                    small = cv2.resize(host_np[n_ % DISTINCT], scan, interpolation=cv2.INTER_AREA)
+                    cv2_ref.detect_faces_cv2(cc, small, sf)
+                    n_ += 1
+                cdt = time.perf_counter() - t0_
+                cfps, cn, cthreads = n_ / cdt, n_, cv2.getNumThreads()
+            else:
+                cfps, cn, cdt, cthreads = cpu_reference_run(cv2_ref, host_np[:DISTINCT], args.cascade, 12.0, 128, sf, ms)
             cpu = {"value": cfps, "unit": "frames/s", "cores": cthreads, "kind": "reference",
                    "sample": f"{cn} of the step's {nF} frames in {cdt:.1f} s, cv2 detectMultiScale, "
                              f"{os.cpu_count()} host cpus"}
@@ -339,16 +366,18 @@ def main():
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
-            "config": {"workload": f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, "
-                                   f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}"
-                                   + (" (BASELINE configs[0]/[1] frame+params)" if (w, h, sf, ms[0]) == (1280, 720, 1.1, 30) else ""),
+            "config": {"workload": (f"tracker front end: synthetic {w}x{h} BGR frames -> INTER_AREA to {scan[0]}x{scan[1]} -> detectFaces "
+                                    f"(skin mask), haarcascade_frontalface_{args.cascade}.xml, " if scan else
+                                    f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, ")
+                                   + f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}"
+                                   + (" (BASELINE configs[0]/[1] frame+params)" if (w, h, sf, ms[0]) == (1280, 720, 1.1, 30) and not scan else ""),
                        "frames_per_step_per_gpu": nF, "launch_group": GROUP, "levels": plan_levels,
                        "l2": f"inputs larger than L2: {nF * w * h / 1e6:.0f} MB of frames per step, "
                              f"{GROUP * (level_px + 8 * int_entries) / 1e6:.0f} MB of integrals per launch group",
                        "parallelism": f"frames sharded, {world} rank(s), lists gathered to rank 0"},
             "windows_evaluated_per_s": win_per_frame * fps,
             "weak_classifiers_per_s": weak_per_frame * fps,
-            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": nF * w * h,
+            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": nF * w * h * (3 if scan else 1),
                     "d2h_bytes_per_step": nF * (CAP * 16 + 4 + 64), "ms_per_step": ms_host / args.steps},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof, "roofline_hbm": roof_hbm, "kernels": kern,

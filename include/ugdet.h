@@ -99,6 +99,7 @@ enum { UGD_K_PREPROCESS = 0,    /* BGR -> gray + skin mask + histogram          
                                    stages with block-wide compaction                  (a9)           */
        UGD_K_TAIL,              /* slot kept for ABI stability: never launched (the scan finishes every window) */
        UGD_K_GROUP,             /* groupRectangles + clip + skin post-filter          (a10-a12)      */
+       UGD_K_AREA,              /* INTER_AREA decimation to the scan size (ugd_detect_batch_scaled)  (8(f) N1) */
        UGD_K_COUNT };
 
 /* ---- parameters / configuration -------------------------------------------------------------- */

@@ -22,7 +22,7 @@ _LIB = None
 
 OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM = range(8)
 K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_scan", "k_tail(unused)",
-           "k_group")
+           "k_group", "k_area")
 
 
 class Rect(C.Structure):
@@ -216,9 +216,14 @@ class Detector:
         assert frames.dtype == np.uint8 and frames.ndim == 4 and frames.shape[3] == 3
         frames = np.ascontiguousarray(frames)
         n, h, w = frames.shape[:3]
+        return self.detect_batch_scaled_ptr(_p(frames), False, n, w, h, scan_size, cap)
+
+    def detect_batch_scaled_ptr(self, ptr, is_device: bool, n: int, w: int, h: int, scan_size, cap: int = 256):
+        if not isinstance(ptr, C.c_void_p):
+            ptr = C.c_void_p(ptr)
         out = np.zeros((n, cap, 4), np.int32)
         cnt = np.zeros(n, np.int32)
-        self._ck(lib().ugd_detect_batch_scaled(self._h, _p(frames), 0, n, w, h, int(scan_size[0]), int(scan_size[1]),
+        self._ck(lib().ugd_detect_batch_scaled(self._h, ptr, int(is_device), n, w, h, int(scan_size[0]), int(scan_size[1]),
                                                _p(out), cap, _p(cnt)))
         return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(n)]
 

@@ -76,6 +76,7 @@ struct ugd_detector {
     bool profiling = false, want_map = false;
     float ktime[UGD_K_COUNT] = {0}; int64_t klaunch[UGD_K_COUNT] = {0};
     cudaEvent_t ev[UGD_K_COUNT + 1] = {nullptr};
+    cudaEvent_t ev_area[2] = {nullptr, nullptr};
     std::string err;
     int sm_count = 148;
 };
@@ -329,8 +330,8 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     bool overflow = false;
     finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, old_integral ? 1 : 0, old_integral ? 1 : 0, 1, 1, 0, 1};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
-        for (int k = 0; k < UGD_K_COUNT; ++k) {
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, old_integral ? 1 : 0, old_integral ? 1 : 0, 1, 1, 0, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
+        for (int k = 0; k < UGD_K_AREA; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
             d->ktime[k] += ms; d->klaunch[k] += launches[k];
@@ -504,6 +505,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&d->ev_copied[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&d->ev_consumed[i], cudaEventDisableTiming); }
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
+    for (auto& ev : d->ev_area) cudaEventCreate(&ev);
     if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
     }
@@ -530,6 +532,7 @@ void ugd_destroy(ugd_detector* d) {
     if (d->h_counts) cudaFreeHost(d->h_counts);
     if (d->h_ctr) cudaFreeHost(d->h_ctr);
     for (auto& ev : d->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : d->ev_area) if (ev) cudaEventDestroy(ev);
     for (int i = 0; i < 2; ++i) { if (d->ev_copied[i]) cudaEventDestroy(d->ev_copied[i]); if (d->ev_consumed[i]) cudaEventDestroy(d->ev_consumed[i]); }
     if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
     d->stage2.release();
@@ -598,17 +601,45 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
     d->ctr = ugd_counters{};
     memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
     const size_t stight = (size_t)src_w * src_h * 3, dstride = round_up((size_t)scan_w * scan_h * 3, 256);
-    for (int f0 = 0; f0 < nframes; f0 += d->max_batch) {
+    // host frames in more than one group: the H2D copy of group g+1 overlaps the kernels of group g (two input buffers)
+    const bool pipelined = !is_device && !d->profiling && nframes > d->max_batch;
+    const size_t in_stride = round_up((size_t)d->max_batch * stight, 256);
+    if (!is_device) CK(d->src_full.reserve((pipelined ? 2 : 1) * in_stride + 256));
+    int g = 0;
+    for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
         const int nf = std::min(d->max_batch, nframes - f0);
         if ((rc = ensure_buffers(d, dp->host, nf, true, cap, nframes))) return rc;
         const uint8_t* src = static_cast<const uint8_t*>(frames) + (size_t)f0 * stight;
         if (!is_device) {
-            CK(d->src_full.reserve((size_t)d->max_batch * stight + 256));
-            CK(cudaMemcpyAsync(d->src_full.p, src, (size_t)nf * stight, cudaMemcpyHostToDevice, d->stream));
-            src = d->src_full.as<uint8_t>();
+            uint8_t* in = d->src_full.as<uint8_t>() + (pipelined && (g & 1) ? in_stride : 0);
+            if (pipelined) {
+                const int bi = g & 1;
+                if (g >= 2) CK(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[bi], 0));
+                CK(cudaMemcpyAsync(in, src, (size_t)nf * stight, cudaMemcpyHostToDevice, d->copy_stream));
+                CK(cudaEventRecord(d->ev_copied[bi], d->copy_stream));
+                CK(cudaStreamWaitEvent(d->stream, d->ev_copied[bi], 0));
+            } else {
+                CK(cudaMemcpyAsync(in, src, (size_t)nf * stight, cudaMemcpyHostToDevice, d->stream));
+            }
+            src = in;
         }
+        if (d->profiling) cudaEventRecord(d->ev_area[0], d->stream);
         launch_area(area_args(*ap, src, (size_t)src_w * 3, stight, d->bgr.as<uint8_t>(), dstride), 3, nf, d->stream);
-        if ((rc = run_group(d, dp, d->bgr.as<uint8_t>(), dstride, true, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, false))) return rc;
+        if (d->profiling) cudaEventRecord(d->ev_area[1], d->stream);
+        if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));      // the input buffer is free once k_area has run
+        if ((rc = run_group(d, dp, d->bgr.as<uint8_t>(), dstride, true, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, pipelined))) return rc;
+        if (d->profiling) {                            // run_group synchronised the stream
+            float ms = 0;
+            cudaEventElapsedTime(&ms, d->ev_area[0], d->ev_area[1]);
+            d->ktime[UGD_K_AREA] += ms; d->klaunch[UGD_K_AREA] += 1;
+        }
+    }
+    if (pipelined) {
+        CK(cudaStreamSynchronize(d->stream));
+        bool overflow = false;
+        for (int f0 = 0; f0 < nframes; f0 += d->max_batch)
+            finish_group(d, dp->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
+        if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     }
     return UGD_OK;
 }
@@ -629,7 +660,7 @@ int ugd_get_kernel_times(const ugd_detector* d, float* t, int64_t* l) {
 
 const char* ugd_kernel_name(int k) {
     static const char* names[UGD_K_COUNT] = {"k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry",
-                                             "k_integral", "k_scan", "k_tail(unused)", "k_group"};
+                                             "k_integral", "k_scan", "k_tail(unused)", "k_group", "k_area"};
     return k >= 0 && k < UGD_K_COUNT ? names[k] : "?";
 }
 
