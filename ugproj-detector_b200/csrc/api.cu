@@ -304,9 +304,9 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), st);
     mark(d, 3);
     static const bool old_integral = getenv("UGD_INTEGRAL_3PASS") != nullptr;     // A/B switch: colsum + carry + integral
-    if (old_integral) launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
+    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
     mark(d, 4);
-    if (old_integral) launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
+    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
     mark(d, 5);
     if (old_integral) launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
     else launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
@@ -330,7 +330,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     bool overflow = false;
     finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, old_integral ? 1 : 0, old_integral ? 1 : 0, 1, 1, 0, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 0, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_AREA; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);

@@ -220,12 +220,23 @@ __global__ void __launch_bounds__(256) k_carry(DevBufs b, const WorkItem* __rest
     const int frame = blockIdx.y;
     size_t o = (size_t)frame * b.carry_stride + L.carry_off + qx * 4;
     uint4 as = make_uint4(0, 0, 0, 0), aq = as;
-    for (int t = 0; t < L.nstrips; ++t, o += L.img_pitch) {
-        uint4 vs = *reinterpret_cast<uint4*>(b.carryS + o), vq = *reinterpret_cast<uint4*>(b.carryQ + o);
-        *reinterpret_cast<uint4*>(b.carryS + o) = as;
-        *reinterpret_cast<uint4*>(b.carryQ + o) = aq;
-        as.x += vs.x; as.y += vs.y; as.z += vs.z; as.w += vs.w;
-        aq.x += vq.x; aq.y += vq.y; aq.z += vq.z; aq.w += vq.w;
+    for (int t0 = 0; t0 < L.nstrips; t0 += 8) {                      // 8 strips of loads in flight, then the serial prefix
+        uint4 vs[8], vq[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (t0 + u < L.nstrips) {
+                vs[u] = *reinterpret_cast<const uint4*>(b.carryS + o + (size_t)u * L.img_pitch);
+                vq[u] = *reinterpret_cast<const uint4*>(b.carryQ + o + (size_t)u * L.img_pitch);
+            }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (t0 + u < L.nstrips) {
+                *reinterpret_cast<uint4*>(b.carryS + o + (size_t)u * L.img_pitch) = as;
+                *reinterpret_cast<uint4*>(b.carryQ + o + (size_t)u * L.img_pitch) = aq;
+                as.x += vs[u].x; as.y += vs[u].y; as.z += vs[u].z; as.w += vs[u].w;
+                aq.x += vq[u].x; aq.y += vq[u].y; aq.z += vq[u].z; aq.w += vq[u].w;
+            }
+        o += (size_t)8 * L.img_pitch;
     }
 }
 
@@ -314,6 +325,7 @@ __global__ void __launch_bounds__(256) k_integral(DevBufs b, const WorkItem* __r
 // (dp4a + redux.sync on pixels that sit in L2).  All arithmetic is uint32 modular, like cv2's int32 SQ plane.
 // ------------------------------------------------------------------------------------------------
 constexpr int kBandCols = 512;
+constexpr int kSegRows = kIntSegRows;
 
 // 256-bit store (sm_100: STG.E.256): a lane's 8 consecutive ints go out as one fully written 32-byte sector
 __device__ __forceinline__ void st256(uint32_t* p, const uint32_t* v) {
@@ -331,17 +343,61 @@ __global__ void __launch_bounds__(32) k_integral_bands(DevBufs b, const WorkItem
     const WorkItem it = wk[blockIdx.y];
     const LevelInfo& L = b.levels[it.level];
     const int frame = blockIdx.x, lane = threadIdx.x;
-    const int sw = L.sw, sh = L.sh, pitch = L.img_pitch, P = L.P;
-    const int band = it.first, X0 = band * kBandCols + lane * 16;          // first output column of this lane
-    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
-    uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off);
-    uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off);
+    const int pitch = L.img_pitch, P = L.P;
+    const int band = it.first & 255, seg = it.first >> 8;                  // a band is cut into segments of kSegRows pixel rows
+    const int X0 = band * kBandCols + lane * 16;                           // first output column of this lane
+    const int Y0 = seg * kSegRows, Y1 = min(Y0 + kSegRows, L.sh);          // pixel rows [Y0, Y1) -> output rows Y0+1 .. Y1
+    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + (size_t)Y0 * pitch;
+    uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off) + (size_t)Y0 * P;
+    uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off) + (size_t)Y0 * P;
     const bool stores = X0 < P;                                            // P and X0 are multiples of 16: all 16 columns or none
     uint32_t accS[16], accQ[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) { accS[k] = 0; accQ[k] = 0; }
-    // row 0 of both planes is zero
-    if (stores) { st256(outS + X0, accS); st256(outS + X0 + 8, accS + 8); st256(outQ + X0, accQ); st256(outQ + X0 + 8, accQ + 8); }
+    if (seg == 0) {                                                        // row 0 of both planes is zero
+        if (stores) { st256(outS + X0, accS); st256(outS + X0 + 8, accS + 8); st256(outQ + X0, accQ); st256(outQ + X0 + 8, accQ + 8); }
+    } else {
+        // output row Y0 = prefix along x of the column sums of all pixel rows above (k_colsum + k_carry, strip = 32 rows)
+        const size_t co = (size_t)frame * b.carry_stride + L.carry_off + (size_t)(Y0 / kStripRows) * pitch;
+        const uint32_t* cS = b.carryS + co;
+        const uint32_t* cQ = b.carryQ + co;
+        uint32_t leftS = 0, leftQ = 0;
+        for (int lb = 0; lb < band; ++lb) {
+            const int x = lb * kBandCols + lane * 16;
+            uint32_t s = 0, q = 0;
+            if (x < pitch) {
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint4 a = *reinterpret_cast<const uint4*>(cS + x + 4 * v), c = *reinterpret_cast<const uint4*>(cQ + x + 4 * v);
+                    s += a.x + a.y + a.z + a.w; q += c.x + c.y + c.z + c.w;
+                }
+            }
+            leftS += __reduce_add_sync(0xffffffffu, s);
+            leftQ += __reduce_add_sync(0xffffffffu, q);
+        }
+        uint32_t rs = 0, rq = 0;
+        if (X0 < pitch) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const uint4 a = *reinterpret_cast<const uint4*>(cS + X0 + 4 * v), c = *reinterpret_cast<const uint4*>(cQ + X0 + 4 * v);
+                accS[4 * v] = rs; rs += a.x; accS[4 * v + 1] = rs; rs += a.y; accS[4 * v + 2] = rs; rs += a.z; accS[4 * v + 3] = rs; rs += a.w;
+                accQ[4 * v] = rq; rq += c.x; accQ[4 * v + 1] = rq; rq += c.y; accQ[4 * v + 2] = rq; rq += c.z; accQ[4 * v + 3] = rq; rq += c.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) { accS[k] = 0; accQ[k] = 0; }
+        }
+        uint32_t is = rs, iq = rq;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, is, d), e = __shfl_up_sync(0xffffffffu, iq, d);
+            if (lane >= d) { is += a; iq += e; }
+        }
+        const uint32_t offS = is - rs + leftS, offQ = iq - rq + leftQ;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { accS[k] += offS; accQ[k] += offQ; }
+    }
+    const int sh = Y1 - Y0;                                                // rows of this segment (the loop below is segment-relative)
     constexpr int PF = 4;                                                  // rows in flight: loads run PF rows ahead of the stores
     uint4 nx[PF];
 #pragma unroll

@@ -10,7 +10,8 @@ namespace ugd {
 
 constexpr int kStripRows = 32;       // integral strips: 32 output rows each
 constexpr int kChunkCols = 128;      // integral chunk: 128 output columns
-constexpr int kIntBand = 512;        // one-pass integral: output columns per warp (band)
+constexpr int kIntBand = 512;        // band integral: output columns per warp
+constexpr int kIntSegRows = 64;      // band integral: pixel rows per warp (a multiple of kStripRows)
 constexpr int kMaxLevels = 256;
 constexpr int kScanRows = 16;        // grid rows per scan block (a scan tile is 64 x 16 windows, 8 warps)
 
