@@ -180,6 +180,35 @@ def test_edge_cases(dets, synth, ug):
         det.detect_gray(np.zeros((721, 1280), np.uint8))                       # larger than created for
 
 
+def test_parameter_variants_against_cv2(ug, synth, cv2ref):
+    """The runtime parameters the reference hard-codes or reads from the cfg (detector.cc:25-31, structure.cc:83-85):
+    minNeighbors 0 (raw list, clipped) and 4, maxSize, a different scale factor, non-square minSize -- vs live cv2."""
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    cc = cv2ref.load(cv2ref.cascade_path("alt"))
+    g = synth.gray_frame(640, 360, 6, 21)
+    variants = [dict(min_neighbors=0), dict(min_neighbors=4), dict(max_size=(120, 120)), dict(scale_factor=1.25),
+                dict(min_size=(40, 60)), dict(scale_factor=1.05, min_size=(24, 24), max_size=(200, 200))]
+    for v in variants:
+        det = ug.Detector(casc, ug.default_params(**v), max_size=(640, 360), max_batch=1)
+        got = det.detect_gray(g, cap=8192)
+        want = cv2ref.detect_multiscale_cv2(cc, g, v.get("scale_factor", 1.1), v.get("min_neighbors", 2),
+                                            v.get("min_size", (30, 30)), v.get("max_size"))
+        assert len(want) > 0, v
+        assert sorted(map(tuple, got.tolist())) == sorted(map(tuple, want.tolist())), v     # multiset (minNeighbors 0 repeats rects)
+        det.close()
+
+
+def test_capacity_errors_are_reported(ug, synth, cv2ref):
+    """A candidate list that does not fit max_raw_per_frame is an error (UGD_ERR_CAPACITY), never a silent truncation;
+    an output list longer than the caller's cap reports the true count."""
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    g = synth.gray_frame(640, 360, 6, 21)
+    det = ug.Detector(casc, ug.default_params(max_raw_per_frame=16), max_size=(640, 360), max_batch=1)
+    with pytest.raises(ug.UgdError):
+        det.detect_gray(g)
+    det.close()
+
+
 def test_golden_fixtures_on_gpu(ug, synth, cv2ref):
     """The committed cv2-generated fixtures (tests/golden), replayed through the C ABI."""
     import hashlib
