@@ -148,6 +148,14 @@ int  ugd_detect_batch(ugd_detector* d, const void* frames, int is_device, int is
                       ugd_rect* out, int cap, int* counts);
 
 /* ---- observability / parity hooks ------------------------------------------------------------- */
+/* Prefetching form of ugd_detect_batch: submit enqueues the copies, kernels and result copies of the
+ * whole batch and returns at once, so the host tracker (face_tracker.cc:140-210, sequential, stateful) can consume
+ * batch k while the GPU detects batch k+1; wait blocks until the submitted batch is done and delivers its lists in
+ * frame order (out: nframes * cap rects, counts: nframes).  One batch in flight per detector; the frame memory passed
+ * to submit must stay valid and unchanged until wait returns. */
+int  ugd_submit_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h, int cap);
+int  ugd_wait_batch(ugd_detector* d, ugd_rect* out, int* counts);
+
 /* The step right before detectFaces in the tracker: cv::resize(orig, scan.frame_size, INTER_AREA)
  * (src/tracker/face_tracker.cc:112-114, cfg key scan.frame_size, src/structure.cc:63-67), fused in front of
  * the detector: full-size BGR frames in, rects in SCAN-frame coordinates out (what track_frame works in).

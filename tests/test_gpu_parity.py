@@ -138,6 +138,27 @@ def test_pipelined_host_batches(dets, synth):
         assert rectset(got[f]) == rectset(det.detect_bgr(bgr[f]))
 
 
+def test_submit_wait_prefetch(dets, synth, ug):
+    """8(f) N2: submit returns before the batch is done, the host does other work, wait delivers the same lists as the
+    blocking call; a second submit (or a blocking call) while one is pending is refused."""
+    _, det = dets["alt"]
+    a = synth.gray_batch(640, 360, 7, seed0=600, nfaces=5)
+    b = synth.gray_batch(640, 360, 3, seed0=700, nfaces=5)
+    want_a, want_b = det.detect_batch(a), det.detect_batch(b)
+    det.submit_batch(a)
+    with pytest.raises(ug.UgdError):
+        det.detect_gray(b[0])
+    host_work = sum(int(x.sum()) for x in b)                                   # the tracker's share, overlapped
+    got_a = det.wait_batch()
+    det.submit_batch(b)
+    got_b = det.wait_batch()
+    assert host_work > 0
+    for w_, g_ in zip(want_a + want_b, got_a + got_b):
+        assert np.array_equal(w_, g_)
+    with pytest.raises(ug.UgdError):
+        lib_rc = det._ck(ug.lib().ugd_wait_batch(det._h, None, None))
+
+
 def test_inter_area_decimation_bit_exact(dets, synth, orc):
     """SURVEY 8(f) N1: cv::resize(orig, scan.frame_size, INTER_AREA) (face_tracker.cc:112-114) on the device,
     bit-exact with cv2 and the oracle: the shipped cfg's 2x case, other integral factors, rational factors, gray."""

@@ -210,6 +210,23 @@ class Detector:
         n, h, w = frames.shape[:3]
         return self._batch(_p(frames), 0, frames.ndim == 4, n, w, h, cap)
 
+    def submit_batch(self, frames: np.ndarray, cap: int = 256) -> None:
+        """Prefetching form (8(f) N2): enqueue a host batch and return at once; wait_batch() delivers the lists."""
+        assert frames.dtype == np.uint8 and frames.ndim in (3, 4)
+        self._pending = (np.ascontiguousarray(frames), cap)            # the frames must stay alive until wait_batch
+        f = self._pending[0]
+        n, h, w = f.shape[:3]
+        self._ck(lib().ugd_submit_batch(self._h, _p(f), 0, int(f.ndim == 4), n, w, h, cap))
+
+    def wait_batch(self):
+        f, cap = self._pending
+        n = f.shape[0]
+        out = np.zeros((n, cap, 4), np.int32)
+        cnt = np.zeros(n, np.int32)
+        self._ck(lib().ugd_wait_batch(self._h, _p(out), _p(cnt)))
+        self._pending = None
+        return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(n)]
+
     def detect_batch_scaled(self, frames: np.ndarray, scan_size, cap: int = 256):
         """frames: [N,H,W,3] full-size BGR host array; scan_size = (w, h) as cfg scan.frame_size.  INTER_AREA
         decimation (face_tracker.cc:112-114) + detectFaces on the device; rects in scan-frame coordinates."""

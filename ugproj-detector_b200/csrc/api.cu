@@ -73,6 +73,7 @@ struct ugd_detector {
     const DevPlan* last_plan = nullptr;
     bool last_was_bgr = false;
     ugd_counters ctr{};
+    struct { bool active = false; int nframes = 0, cap = 0; DevPlan* plan = nullptr; } pending;   // ugd_submit_batch ... ugd_wait_batch
     bool profiling = false, want_map = false;
     float ktime[UGD_K_COUNT] = {0}; int64_t klaunch[UGD_K_COUNT] = {0};
     cudaEvent_t ev[UGD_K_COUNT + 1] = {nullptr};
@@ -369,9 +370,15 @@ AreaArgs area_args(const DevAreaPlan& ap, const uint8_t* src, size_t row_stride,
     return a;
 }
 
+int wait_pending(ugd_detector* d, ugd_rect* out, int* counts);
+
+// async_submit: enqueue everything (copies, kernels, result copies to pinned memory) and return without waiting;
+// ugd_wait_batch finishes the call.  out/counts are not touched until then.
 int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
-                  size_t host_row_stride, ugd_rect* out, int cap, int* counts) {
-    if (!d || !frames || !out || !counts || nframes < 0 || cap <= 0 || w <= 0 || h <= 0) return UGD_ERR_ARG;
+                  size_t host_row_stride, ugd_rect* out, int cap, int* counts, bool async_submit = false) {
+    if (!d || !frames || nframes < 0 || cap <= 0 || w <= 0 || h <= 0) return UGD_ERR_ARG;
+    if (!async_submit && (!out || !counts)) return UGD_ERR_ARG;
+    if (d->pending.active) { d->err = "a submitted batch is still pending: call ugd_wait_batch first"; return UGD_ERR_ARG; }
     if (w > d->max_w || h > d->max_h) { d->err = "frame larger than the detector was created for"; return UGD_ERR_CAPACITY; }
     CK(cudaSetDevice(d->device));
     DevPlan* dp = nullptr;
@@ -385,6 +392,7 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
     // Host frames in more than one group: copies of group g+1 (copy stream) overlap the kernels of group g.
     const bool tight_host = !is_device && host_row_stride == (size_t)w * ch;
     const bool pipelined = tight_host && !d->profiling && nframes > d->max_batch;
+    const bool defer = pipelined || async_submit;
     if (pipelined) CK(d->stage2.reserve((size_t)d->max_batch * st_stride + 256));
     int g = 0;
     for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
@@ -414,16 +422,25 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
             }
             dev = staging; stride = st_stride;
         }
-        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, pipelined))) return rc;
+        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, defer ? nullptr : out + (size_t)f0 * cap, cap, defer ? nullptr : counts + f0, f0, defer))) return rc;
         if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));
     }
-    if (pipelined) {
-        CK(cudaStreamSynchronize(d->stream));
-        bool overflow = false;
-        for (int f0 = 0; f0 < nframes; f0 += d->max_batch)
-            finish_group(d, dp->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
-        if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
+    if (defer) {
+        d->pending.active = true; d->pending.nframes = nframes; d->pending.cap = cap; d->pending.plan = dp;
+        if (!async_submit) return wait_pending(d, out, counts);
     }
+    return UGD_OK;
+}
+
+int wait_pending(ugd_detector* d, ugd_rect* out, int* counts) {
+    if (!d->pending.active) { d->err = "no submitted batch to wait for"; return UGD_ERR_ARG; }
+    d->pending.active = false;
+    CK(cudaStreamSynchronize(d->stream));
+    const int nframes = d->pending.nframes, cap = d->pending.cap;
+    bool overflow = false;
+    for (int f0 = 0; f0 < nframes; f0 += d->max_batch)
+        finish_group(d, d->pending.plan->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
+    if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     return UGD_OK;
 }
 
@@ -591,6 +608,7 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
     if (!d || !frames || !out || !counts || nframes < 0 || cap <= 0 || src_w <= 0 || src_h <= 0) return UGD_ERR_ARG;
     if (scan_w <= 0 || scan_h <= 0) { scan_w = src_w; scan_h = src_h; }           // scan.frame_size absent: structure.cc:64-65
     if (scan_w == src_w && scan_h == src_h) return ugd_detect_batch(d, frames, is_device, 1, nframes, src_w, src_h, out, cap, counts);
+    if (d->pending.active) { d->err = "a submitted batch is still pending: call ugd_wait_batch first"; return UGD_ERR_ARG; }
     if (scan_w > d->max_w || scan_h > d->max_h) { d->err = "scan size larger than the detector was created for"; return UGD_ERR_CAPACITY; }
     CK(cudaSetDevice(d->device));
     DevAreaPlan* ap = nullptr;
@@ -642,6 +660,16 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
         if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     }
     return UGD_OK;
+}
+
+int ugd_submit_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h, int cap) {
+    return detect_common(d, frames, is_device != 0, is_bgr != 0, nframes, w, h, (size_t)w * (is_bgr ? 3 : 1), nullptr, cap, nullptr, true);
+}
+
+int ugd_wait_batch(ugd_detector* d, ugd_rect* out, int* counts) {
+    if (!d || !out || !counts) return UGD_ERR_ARG;
+    CK(cudaSetDevice(d->device));
+    return wait_pending(d, out, counts);
 }
 
 int ugd_get_counters(const ugd_detector* d, ugd_counters* c) {
