@@ -337,7 +337,7 @@ def main():
             roof = {"kernel": dominant, "bound": v.get("bound", "hbm"), "achieved": v.get("achieved"), "peak": hbm_peak,
                     "unit": "GB/s", "frac": v.get("frac"), "traffic": None}
         hi = kern.get("k_integral", {})
-        roof_hbm = {"kernel": "k_integral (one-pass k_integral_bands)", "bound": "hbm", "achieved": hi.get("achieved"), "peak": hbm_peak,
+        roof_hbm = {"kernel": "k_integral_bands (main pass of the integral)", "bound": "hbm", "achieved": hi.get("achieved"), "peak": hbm_peak,
                     "unit": "GB/s", "frac": hi.get("frac"),
                     # ncu r01 (profiles/r01_ncu_resize_integral_bands_summary.txt): dram read 191.1 MB + write 1030.5 MB per launch
                     "traffic": 1221.6e6 if (w, h, GROUP) == (1280, 720, 64) else None, "peak_source": peak_src}
@@ -361,7 +361,7 @@ def main():
                    "sample": f"{cn} of the step's {nF} frames in {cdt:.1f} s, cv2 detectMultiScale, "
                              f"{os.cpu_count()} host cpus"}
         groups = (nF + GROUP - 1) // GROUP
-        launches_per_step = groups * 7                          # resize, colsum, carry, integral, scan x2 (grid step 2 / step 1 levels), group
+        launches_per_step = groups * (9 + (3 if scan else 0))   # resize, colsum, carry, integral, scan x2 (grid step 2 / step 1 levels), group init/link/finish (+ area, preprocess, equalize on the BGR path)
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
