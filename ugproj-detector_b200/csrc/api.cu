@@ -31,9 +31,9 @@ struct DevPtr {                       // grow-only device allocation
 
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
-    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_integral, wk_bands, wk_scan;
+    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_bands, wk_scan;
     void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release(); wk_colsum.release();
-                     wk_carry.release(); wk_integral.release(); wk_bands.release(); wk_scan.release(); }
+                     wk_carry.release(); wk_bands.release(); wk_scan.release(); }
 };
 
 struct DevAreaPlan {                  // INTER_AREA tables for one (source size -> scan size) pair
@@ -112,7 +112,6 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_resize, dp->host.wk_resize))) return rc;
     if ((rc = upload(d, dp->wk_colsum, dp->host.wk_colsum))) return rc;
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
-    if ((rc = upload(d, dp->wk_integral, dp->host.wk_integral))) return rc;
     if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
@@ -304,13 +303,11 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 2);
     launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), st);
     mark(d, 3);
-    static const bool old_integral = getenv("UGD_INTEGRAL_3PASS") != nullptr;     // A/B switch: colsum + carry + integral
     launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
     mark(d, 4);
     launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
     mark(d, 5);
-    if (old_integral) launch_integral(b, dp->wk_integral.as<WorkItem>(), (int)p.wk_integral.size(), st);
-    else launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
+    launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
     mark(d, 6);
     {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)

@@ -1,4 +1,4 @@
-// Host-side cascade model (immutable after load) and the packed device layout derived from it.
+// Host-side cascade model (immutable after load) and the corner-list form the device layouts are built from.
 // Replaces the cv::CascadeClassifier object the reference loads at src/file_io.cc:11.
 #pragma once
 #include <cstdint>
@@ -14,17 +14,6 @@ struct HostNode {
     int32_t left, right;    // > 0: child node index inside the tree, 0: leaf
     float   left_val, right_val;
 };
-
-// Packed node, 48 bytes, the unit both evaluators read.
-//   q0 = { rect0, rect1, rect2, thr_bits }         rect = x | y<<8 | w<<16 | h<<24
-//   q1 = { left_val (f64), right_val (f64) }       leaves pre-widened: stage sums are fp64
-//   q2 = { meta, 0, 0, 0 }  meta = left | right<<8 | (w0&0xff)<<16 | (w1&0xff)<<24 ; q2.y = w2 | last<<8
-struct alignas(16) PackedNode {
-    uint32_t r0, r1, r2, thr_bits;
-    double   lval, rval;
-    uint32_t meta, meta2, pad0, pad1;
-};
-static_assert(sizeof(PackedNode) == 48, "PackedNode layout");
 
 // Corner-list form of a node: feature = sum_j coef[j] * S[corner j], duplicates merged
 // (6, 8 or 9 distinct corners for the shipped cascades instead of 8 / 12).  Exact in int32.
@@ -45,7 +34,6 @@ struct Cascade {
     std::vector<int32_t> tree_first_node, tree_nnodes;
     std::vector<HostNode> nodes;
     // derived
-    std::vector<PackedNode> packed;              // one per node, same order
     std::vector<CornerNode> corners;             // one per node, same order
     std::vector<int32_t> stage_first_node;       // [nstages+1]
     int nstages() const { return (int)stage_thr.size(); }

@@ -233,13 +233,12 @@ int lsb_exponent(float f) {
     return e - 24 + tz;
 }
 
-int validate_and_pack(Cascade& c, std::string& err) {
+int validate_and_derive(Cascade& c, std::string& err) {
     if (c.win_w < 4 || c.win_h < 4 || c.win_w > 64 || c.win_h > 64) { err = "window size outside 4..64"; return UGD_ERR_UNSUPPORTED; }
     if (c.nstages() == 0 || c.nstages() > 32000) { err = "cascade has no stages"; return UGD_ERR_PARSE; }
     c.max_tree_nodes = 0;
     int min_lsb = 1000; double max_bound = 0;
     c.stage_first_node.assign(c.nstages() + 1, 0);
-    c.packed.resize(c.nodes.size());
     c.corners.resize(c.nodes.size());
     for (int s = 0; s < c.nstages(); ++s) {
         double bound = 0;
@@ -269,14 +268,6 @@ int validate_and_pack(Cascade& c, std::string& err) {
                 if (n.weight[0] == 0.f || n.weight[1] == 0.f) { err = "feature needs at least two rects"; return UGD_ERR_UNSUPPORTED; }
                 // int32 evaluation is exact iff every partial sum stays below 2^24 (float mantissa)
                 if ((double)sumw * c.win_w * c.win_h * 255.0 >= 16777216.0) { err = "feature weights too large for exact evaluation"; return UGD_ERR_UNSUPPORTED; }
-                PackedNode& p = c.packed[base + k];
-                auto pk = [](const int32_t* q) { return (uint32_t)q[0] | (uint32_t)q[1] << 8 | (uint32_t)q[2] << 16 | (uint32_t)q[3] << 24; };
-                p.r0 = pk(n.rect[0]); p.r1 = pk(n.rect[1]); p.r2 = n.weight[2] != 0.f ? pk(n.rect[2]) : 0u;
-                memcpy(&p.thr_bits, &n.thr, 4);
-                p.lval = (double)n.left_val; p.rval = (double)n.right_val;
-                p.meta = (uint32_t)n.left | (uint32_t)n.right << 8 | ((uint32_t)(int)n.weight[0] & 0xffu) << 16 | ((uint32_t)(int)n.weight[1] & 0xffu) << 24;
-                p.meta2 = ((uint32_t)(int)n.weight[2] & 0xffu) | (k == nn - 1 ? 0x100u : 0u);
-                p.pad0 = p.pad1 = 0;
                 {   // corner list: merge duplicate corners, drop zero coefficients
                     CornerNode cn{};
                     int m = 0;
@@ -348,7 +339,7 @@ int load_cascade_xml(const std::string& path, Cascade& out, std::string& err) {
         if (k->type_id == "opencv-cascade-classifier") { err.clear(); rc = load_new(*k, out, err); break; }
     }
     if (rc != UGD_OK) return rc;
-    return validate_and_pack(out, err);
+    return validate_and_derive(out, err);
 }
 
 }  // namespace ugd

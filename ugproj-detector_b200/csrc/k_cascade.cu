@@ -184,29 +184,9 @@ __device__ __forceinline__ int node_resp(const DNode& d, int si, const char* __r
 }
 #undef TILE_AT
 
-// FAST: stump cascade whose leaf sums are exact in fp64 (Cascade::delta_exact).  The stage sum is
-// formed as base + sum over the nodes that go LEFT of (left - right): one predicated DADD per node.
-// It equals the oracle's sum of leaves bit for bit because every partial sum is exact.
-template <bool FAST>
-__device__ __forceinline__ double tile_stage(int s, int si, const char* __restrict__ t, float vnf) {
+// Generic evaluator (any tree shape, plain fp64 sum of leaves in file order), one window per lane.
+__device__ __forceinline__ double tile_stage_generic(int s, int si, const char* __restrict__ t, float vnf) {
     const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
-    if (FAST) {
-        // two nodes per trip, separate accumulators: twice the independent work in flight per warp
-        double s0 = c_stage_base[s], s1 = 0.0;
-        int n = n0;
-        for (; n + 1 < n1; n += 2) {
-            const DNode& d0 = c_dn[n];
-            const DNode& d1 = c_dn[n + 1];
-            const int r0 = node_resp(d0, si, t), r1 = node_resp(d1, si, t);
-            if (__fmul_rn(__int2float_rn(r0), vnf) < d0.thr) s0 += d0.delta;
-            if (__fmul_rn(__int2float_rn(r1), vnf) < d1.thr) s1 += d1.delta;
-        }
-        if (n < n1) {
-            const DNode& d0 = c_dn[n];
-            if (__fmul_rn(__int2float_rn(node_resp(d0, si, t)), vnf) < d0.thr) s0 += d0.delta;
-        }
-        return s0 + s1;
-    }
     double sum = 0.0;
     float leaf = 0.f;
     int at = 0, k = 0;
@@ -455,7 +435,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                     const char* t1[1] = {t}; const float v1[1] = {vnf}; double s1[1];
                     stage_eval<MODE, 1>(0, si, t1, v1, s1);
                     sum = s1[0];
-                } else sum = tile_stage<false>(0, si, t, vnf);
+                } else sum = tile_stage_generic(0, si, t, vnf);
                 const bool pass0 = !(sum < (double)thr0);
                 // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
                 // ending at i-1 has even length (a failure is only seen at evaluated positions)
@@ -575,7 +555,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                 const int bit = act ? __ffs((int)mm) - 1 : 0;
                 const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
                 const char* tw = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
-                const double sum = tile_stage<false>(s, si, tw, s_vnf[rl * C + c]);
+                const double sum = tile_stage_generic(s, si, tw, s_vnf[rl * C + c]);
                 bool pass = act && !(sum < (double)thr);
                 const unsigned am = __ballot_sync(0xffffffffu, act);
                 const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));

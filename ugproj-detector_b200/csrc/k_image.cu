@@ -181,12 +181,10 @@ void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 }
 
 // ------------------------------------------------------------------------------------------------
-// K4  integral images S and SQ (a8), three phases so that every output element is written once
-// and every level pixel is read twice (second read is an L2 hit):
-//   colsum   : per 32-row strip, column sums of pixel and pixel^2            (1 B/px read)
-//   carry    : exclusive scan of those sums down the strips (tiny)
-//   integral : per strip, 128-column chunks: warp-shuffle row scans into shared memory, then a
-//              column pass that adds the strip carry and stores coalesced rows (8 B/px written)
+// K4  integral images S and SQ (a8).  Two small passes give every 32-row strip its starting column sums:
+//   colsum : per 32-row strip, column sums of pixel and pixel^2            (1 B/px read)
+//   carry  : exclusive scan of those sums down the strips (tiny)
+// and k_integral_bands (below) then writes both planes in one sweep, each output element once.
 // Arithmetic is uint32 modular, which reproduces cv2's wrapping int32 SQ plane bit for bit.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_colsum(DevBufs b, const WorkItem* __restrict__ wk) {
@@ -240,84 +238,9 @@ __global__ void __launch_bounds__(256) k_carry(DevBufs b, const WorkItem* __rest
     }
 }
 
-__global__ void __launch_bounds__(256) k_integral(DevBufs b, const WorkItem* __restrict__ wk) {
-    __shared__ __align__(16) uint32_t ES[kStripRows][kChunkCols];
-    __shared__ __align__(16) uint32_t EQ[kStripRows][kChunkCols];
-    __shared__ uint32_t leftS[kStripRows], leftQ[kStripRows];
-    const WorkItem it = wk[blockIdx.x];
-    const LevelInfo& L = b.levels[it.level];
-    const int strip = it.first, frame = blockIdx.y;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
-    const size_t co = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * L.img_pitch;
-    const uint32_t* cS = b.carryS + co;
-    const uint32_t* cQ = b.carryQ + co;
-    uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off);
-    uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off);
-    if (tid < kStripRows) { leftS[tid] = 0; leftQ[tid] = 0; }
-    __syncthreads();
-    const int nchunks = (L.sw + 1 + kChunkCols - 1) / kChunkCols;
-    const int Y0 = strip * kStripRows;
-    for (int c = 0; c < nchunks; ++c) {
-        // ---- row pass: exclusive prefix along x of (carry row, then 31 pixel rows) ----
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int k = warp * 4 + r;
-            const int u = c * kChunkCols + lane * 4;
-            uint32_t v[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
-            if (u < L.img_pitch) {
-                if (k == 0) {
-                    uint4 a = *reinterpret_cast<const uint4*>(cS + u), d = *reinterpret_cast<const uint4*>(cQ + u);
-                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-                    q[0] = d.x; q[1] = d.y; q[2] = d.z; q[3] = d.w;
-                } else {
-                    const int row = Y0 + k - 1;
-                    if (row < L.sh) {
-                        uint32_t p = *reinterpret_cast<const uint32_t*>(img + (size_t)row * L.img_pitch + u);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) { uint32_t t = (p >> (8 * j)) & 255u; v[j] = t; q[j] = t * t; }
-                    }
-                }
-            }
-            uint32_t ts = v[0] + v[1] + v[2] + v[3], tq = q[0] + q[1] + q[2] + q[3];
-            uint32_t is = ts, iq = tq;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                uint32_t a = __shfl_up_sync(0xffffffffu, is, d), e = __shfl_up_sync(0xffffffffu, iq, d);
-                if (lane >= d) { is += a; iq += e; }
-            }
-            uint32_t es = is - ts + leftS[k], eq = iq - tq + leftQ[k];
-            *reinterpret_cast<uint4*>(&ES[k][lane * 4]) = make_uint4(es, es + v[0], es + v[0] + v[1], es + v[0] + v[1] + v[2]);
-            *reinterpret_cast<uint4*>(&EQ[k][lane * 4]) = make_uint4(eq, eq + q[0], eq + q[0] + q[1], eq + q[0] + q[1] + q[2]);
-            uint32_t tots = __shfl_sync(0xffffffffu, is, 31), totq = __shfl_sync(0xffffffffu, iq, 31);
-            __syncwarp();
-            if (lane == 0) { leftS[k] += tots; leftQ[k] += totq; }
-        }
-        __syncthreads();
-        // ---- column pass: running sum down the strip, coalesced stores ----
-        {
-            const int col = tid & (kChunkCols - 1);
-            const int X = c * kChunkCols + col;
-            const uint32_t(*E)[kChunkCols] = (tid >> 7) ? EQ : ES;
-            uint32_t* out = (tid >> 7) ? outQ : outS;
-            if (X <= L.sw) {
-                uint32_t acc = E[0][col];
-                const int kmax = min(kStripRows, L.sh + 1 - Y0);
-                uint32_t* o = out + (size_t)Y0 * L.P + X;
-#pragma unroll 8
-                for (int k = 0; k < kmax; ++k) {
-                    o[(size_t)k * L.P] = acc;
-                    if (k + 1 < kStripRows) acc += E[k + 1][col];
-                }
-            }
-        }
-        __syncthreads();
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
-// K4'  integral images in ONE pass (replaces colsum + carry + integral): one warp owns a band of 512
-// output columns of one level of one frame and walks it top to bottom.  Lane l holds 16 consecutive columns:
+// K4'  the integral main pass: one warp owns a band of 512 output columns x a segment of 64 pixel rows of
+// one level of one frame, seeded from the strip carries, and walks it top to bottom.  Lane l holds 16 consecutive columns:
 // per row it loads 16 pixels (one 16-byte load), forms their exclusive prefix (and that of their squares),
 // a warp shuffle scan supplies the offset of the lanes to its left, and the running column sums live in
 // registers from the first row to the last, so nothing is ever re-read and every output element is written
@@ -467,9 +390,6 @@ void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 }
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
     if (nblocks) k_carry<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
-}
-void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
-    if (nblocks) k_integral<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
 }
 
 }  // namespace ugd

@@ -112,7 +112,6 @@ void launch_equalize(const DevBufs& b, cudaStream_t st);
 void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
-void launch_integral(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);

@@ -87,7 +87,6 @@ void build_plan(int w, int h, int win_w, int win_h, double scale_factor, int min
         add_work(p.wk_resize, level, (int64_t)quads * L.sh, 256);
         add_work(p.wk_colsum, level, (int64_t)quads * L.nstrips, 256);
         add_work(p.wk_carry, level, quads, 256);
-        add_work(p.wk_integral, level, L.nstrips, 1);
         for (int seg = 0; seg * kIntSegRows < L.sh; ++seg)                         // one warp per (segment of 64 rows, band of 512 integral columns)
             for (int bnd = 0; bnd * kIntBand < L.sw + 1; ++bnd) p.wk_bands.push_back({level, bnd | seg << 8});
         add_work(p.wk_scan, level, L.nyg, kScanRows);      // one block per kScanRows grid rows

@@ -9,7 +9,6 @@
 namespace ugd {
 
 constexpr int kStripRows = 32;       // integral strips: 32 output rows each
-constexpr int kChunkCols = 128;      // integral chunk: 128 output columns
 constexpr int kIntBand = 512;        // band integral: output columns per warp
 constexpr int kIntSegRows = 64;      // band integral: pixel rows per warp (a multiple of kStripRows)
 constexpr int kMaxLevels = 256;
@@ -42,7 +41,7 @@ struct Plan {
     int w = 0, h = 0;
     std::vector<LevelInfo> levels;
     std::vector<uint32_t> xtab, ytab;           // entry = i0 | c1 << 16  (c1 in 0..256)
-    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_integral, wk_bands, wk_scan;
+    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_bands, wk_scan;
     // per-frame sizes
     size_t pyr_bytes = 0, int_ints = 0, pos_entries = 0, carry_ints = 0, map_entries = 0;
     int64_t level_pixels = 0, grid_windows = 0;
