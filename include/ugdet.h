@@ -32,8 +32,8 @@ extern "C" {
 #define UGD_ERR_ARG          1   /* bad argument (null pointer, size out of range)                  */
 #define UGD_ERR_IO           2   /* file cannot be opened / read                                    */
 #define UGD_ERR_PARSE        3   /* malformed XML / INI                                             */
-#define UGD_ERR_UNSUPPORTED  4   /* cascade uses something the engine does not implement (tilted,
-                                    LBP/HOG, non-integer rect weights, > 255 tree nodes ...)        */
+#define UGD_ERR_UNSUPPORTED  4   /* cascade uses something the engine does not implement (LBP/HOG
+                                    features, non-integer rect weights, > 255 tree nodes ...)       */
 #define UGD_ERR_CUDA         5   /* CUDA runtime error; text via ugd_last_error()                   */
 #define UGD_ERR_CAPACITY     6   /* frame larger than the detector was created for, or an internal
                                     per-frame candidate buffer overflowed                           */
@@ -68,6 +68,8 @@ typedef struct {
     int32_t old_format;       /* 1 = type_id "opencv-haar-classifier" (the reference data XMLs)         */
     int32_t sum_exact;        /* 1 = every stage sum is exactly representable in fp64, so the
                                  engine's parallel summation order cannot change a decision         */
+    int32_t has_tilted;       /* 1 = some features are 45-degree tilted: the engine also builds the
+                                 tilted integral of every pyramid level            */
 } ugd_cascade_info;
 
 /* Work counters of the most recent detect call (summed over its frames). */
@@ -95,9 +97,10 @@ enum { UGD_K_PREPROCESS = 0,    /* BGR -> gray + skin mask + histogram          
        UGD_K_COLSUM,            /* integral phase 1: per-strip column sums            (a8)           */
        UGD_K_CARRY,             /* integral phase 2: scan of strip sums               (a8)           */
        UGD_K_INTEGRAL,          /* integral phase 3: S and SQ planes                  (a8)           */
-       UGD_K_SCAN,              /* tiled window scan: variance norm, x-skip, in-tile
-                                   stages with block-wide compaction                  (a9)           */
-       UGD_K_TAIL,              /* slot kept for ABI stability: never launched (the scan finishes every window) */
+       UGD_K_TILTED,            /* tilted integral plane; launched only for cascades with tilted
+                                   features                                           (8(f) N4)      */
+       UGD_K_SCAN,              /* tiled window scan: variance norm, x-skip, in-tile stages on
+                                   per-bank-class survivor masks, block-local queue   (a9)           */
        UGD_K_GROUP,             /* groupRectangles + clip + skin post-filter          (a10-a12)      */
        UGD_K_AREA,              /* INTER_AREA decimation to the scan size (ugd_detect_batch_scaled)  (8(f) N1) */
        UGD_K_COUNT };
@@ -117,11 +120,12 @@ int  ugd_cascade_load_xml(const char* path, ugd_cascade** out);
 int  ugd_cascade_get_info(const ugd_cascade* c, ugd_cascade_info* info);
 /* Copies the parsed model out as flat arrays (any pointer may be NULL).  Sizes: stage_* [nstages],
  * tree_* [ntrees], node_rects [nnodes*12] (3 x (x,y,w,h)), node_weights [nnodes*3], others [nnodes].
- * stage_thr already holds f32(xml) - 1e-5f.  Used by the loader parity tests. */
+ * stage_thr already holds f32(xml) - 1e-5f; node_tilted is 1 for nodes whose rects are 45-degree tilted.
+ * Used by the loader parity tests. */
 int  ugd_cascade_dump(const ugd_cascade* c, int32_t* stage_first_tree, int32_t* stage_ntrees, float* stage_thr,
                       int32_t* tree_first_node, int32_t* tree_nnodes, int32_t* node_rects, float* node_weights,
                       float* node_thr, int32_t* node_left, int32_t* node_right, float* node_left_val,
-                      float* node_right_val);
+                      float* node_right_val, int32_t* node_tilted);
 void ugd_cascade_free(ugd_cascade* c);
 
 /* ---- detector: replaces ugproj::FaceDetector (detector.h:10-19) ------------------------------- */
@@ -191,9 +195,11 @@ int  ugd_set_stage_map(ugd_detector* d, int on);
 int  ugd_get_stage_map(ugd_detector* d, int16_t* map, size_t cap, size_t* n);
 /* Intermediate images of frame 0 of the most recent call, for per-subsystem parity tests:
  *   ugd_get_preprocessed: equalised+masked gray (w*h) and skin mask (w*h) after a BGR call;
- *   ugd_get_level: level image (lw*lh, tight) and integral planes S, SQ ((lh+1)*(lw+1), tight). */
+ *   ugd_get_level: level image (lw*lh, tight) and integral planes S, SQ ((lh+1)*(lw+1), tight);
+ *   ugd_get_level_tilted: the tilted integral plane of that level (cascades with tilted features only). */
 int  ugd_get_preprocessed(ugd_detector* d, uint8_t* gray_eq, uint8_t* mask);
 int  ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t* SQ);
+int  ugd_get_level_tilted(ugd_detector* d, int level, int32_t* T);
 
 const char* ugd_strerror(int code);
 const char* ugd_last_error(const ugd_detector* d);   /* detail of the detector's last failure */

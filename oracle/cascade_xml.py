@@ -39,6 +39,7 @@ class FlatCascade:
     node_right: np.ndarray         # int32 [nnodes]
     node_left_val: np.ndarray      # float32 [nnodes]  leaf value when node_left == 0
     node_right_val: np.ndarray     # float32 [nnodes]
+    node_tilted: np.ndarray = None  # int32 [nnodes]  1: the node's rects are 45-degree tilted (read the tilted integral)
     tilted: bool = False
 
     @property
@@ -67,7 +68,9 @@ def _finish(win, stages, trees, nodes, tilted):
     right = np.zeros(n, np.int32)
     lval = np.zeros(n, np.float32)
     rval = np.zeros(n, np.float32)
+    tl = np.zeros(n, np.int32)
     for i, nd in enumerate(nodes):
+        tl[i] = int(bool(nd.get("tilted", False)))
         for k, (x, y, w, h, wt) in enumerate(nd["rects"]):
             rects[i, k] = (x, y, w, h)
             weights[i, k] = wt
@@ -83,7 +86,7 @@ def _finish(win, stages, trees, nodes, tilted):
         tree_nnodes=np.array([t[1] for t in trees], np.int32),
         node_rects=rects, node_weights=weights, node_thr=thr,
         node_left=left, node_right=right, node_left_val=lval, node_right_val=rval,
-        tilted=tilted)
+        node_tilted=tl, tilted=bool(tl.any()))
 
 
 def _parse_rect(txt):
@@ -103,9 +106,9 @@ def _load_old(root_el):
             for nd in tnodes:
                 feat = nd.find("feature")
                 rects = [_parse_rect(r.text) for r in feat.find("rects")]
-                if int(feat.find("tilted").text) != 0:
-                    tilted = True
+                t = feat.find("tilted")
                 d = {"rects": rects, "thr": _f32(nd.find("threshold").text),
+                     "tilted": t is not None and int(t.text) != 0,
                      "left": 0, "right": 0, "lval": np.float32(0), "rval": np.float32(0)}
                 if nd.find("left_val") is not None:
                     d["lval"] = _f32(nd.find("left_val").text)
@@ -131,9 +134,7 @@ def _load_new(root_el):
     for f in root_el.find("features"):
         rects = [_parse_rect(r.text) for r in f.find("rects")]
         t = f.find("tilted")
-        if t is not None and int(t.text) != 0:
-            tilted = True
-        feats.append(rects)
+        feats.append((rects, t is not None and int(t.text) != 0))
     stages, trees, nodes = [], [], []
     for st in root_el.find("stages"):
         first_tree = len(trees)
@@ -144,7 +145,7 @@ def _load_new(root_el):
             first_node = len(nodes)
             for k in range(nn):
                 l, r, fi = int(inodes[4 * k]), int(inodes[4 * k + 1]), int(inodes[4 * k + 2])
-                d = {"rects": feats[fi], "thr": _f32(inodes[4 * k + 3]),
+                d = {"rects": feats[fi][0], "tilted": feats[fi][1], "thr": _f32(inodes[4 * k + 3]),
                      "left": max(l, 0), "right": max(r, 0),
                      "lval": leaves[-l] if l <= 0 else np.float32(0),
                      "rval": leaves[-r] if r <= 0 else np.float32(0)}
@@ -161,6 +162,6 @@ def load_cascade(path: str) -> FlatCascade:
         tid = el.get("type_id")
         if tid == "opencv-haar-classifier":
             return _load_old(el)
-        if tid == "opencv-cascade-classifier":
-            return _load_new(el)
+        if tid == "opencv-cascade-classifier" or (tid is None and el.find("stageType") is not None):
+            return _load_new(el)          # some shipped files (frontalcatface*) carry no type_id
     raise ValueError(f"{path}: no Haar cascade node found")

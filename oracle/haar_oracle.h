@@ -25,6 +25,8 @@ typedef struct {
     const int32_t* node_right;
     const float*   node_left_val;
     const float*   node_right_val;
+    const int32_t* node_tilted;      /* 1 = rects are 45-degree tilted: read the tilted integral */
+    int32_t has_tilted;              /* any node tilted -> the tilted plane is built per level   */
 } orc_cascade;
 
 typedef struct {
@@ -38,10 +40,13 @@ void orc_equalize_hist(const uint8_t* src, int n, uint8_t* dst);
 int  orc_resize_area(const uint8_t* src, int sw, int sh, int cn, size_t sstride, uint8_t* dst, int dw, int dh);
 void orc_resize_exact(const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw, int dh);
 void orc_integral(const uint8_t* img, int w, int h, int32_t* S, int32_t* SQ);
+void orc_integral_tilted(const uint8_t* img, int w, int h, int32_t* T);
 int  orc_scale_list(int W, int H, int ow, int oh, double scale_factor, int min_w, int min_h, int max_w,
                     int max_h, float* scales, int cap);
 void orc_level_size(int W, int H, float s, int* sw, int* sh);
-int  orc_run_at(const orc_cascade* c, const int32_t* S, const int32_t* SQ, int pitch, int x, int y,
+int  orc_stripe_count(int W, int H, int ow, float first_scale);
+int  orc_grid_rows(int ny, int step, int ns);
+int  orc_run_at(const orc_cascade* c, const int32_t* S, const int32_t* SQ, const int32_t* T, int pitch, int x, int y,
                 double* last_sum, int64_t* weak_evals);
 int  orc_detect_raw(const orc_cascade* c, const uint8_t* gray, int W, int H, size_t stride, double scale_factor,
                     int min_w, int min_h, int max_w, int max_h, orc_rect* out, double* out_sum, int cap,

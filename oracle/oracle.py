@@ -27,7 +27,7 @@ class _Cascade(C.Structure):
                 ("nnodes", C.c_int32)] + [(n, C.c_void_p) for n in (
                     "stage_first_tree", "stage_ntrees", "stage_thr", "tree_first_node", "tree_nnodes",
                     "node_rects", "node_weights", "node_thr", "node_left", "node_right", "node_left_val",
-                    "node_right_val")]
+                    "node_right_val", "node_tilted")] + [("has_tilted", C.c_int32)]
 
 
 class Counters(C.Structure):
@@ -68,8 +68,9 @@ class OracleCascade:
         self._keep = [np.ascontiguousarray(a) for a in (
             f.stage_first_tree, f.stage_ntrees, f.stage_thr, f.tree_first_node, f.tree_nnodes,
             f.node_rects.reshape(-1), f.node_weights.reshape(-1), f.node_thr, f.node_left, f.node_right,
-            f.node_left_val, f.node_right_val)]
-        self.c = _Cascade(f.win_w, f.win_h, f.nstages, f.ntrees, f.nnodes, *[_p(a) for a in self._keep])
+            f.node_left_val, f.node_right_val, f.node_tilted)]
+        self.c = _Cascade(f.win_w, f.win_h, f.nstages, f.ntrees, f.nnodes, *[_p(a) for a in self._keep],
+                          int(f.tilted))
 
     @classmethod
     def load(cls, path):
@@ -140,6 +141,15 @@ def integral(gray):
     SQ = np.empty((h + 1, w + 1), np.int32)
     lib().orc_integral(_p(gray), w, h, _p(S), _p(SQ))
     return S, SQ
+
+
+def integral_tilted(gray):
+    """Third output of cv2.integral3 (CV_32S): the 45-degree rotated integral tilted cascades read."""
+    gray = np.ascontiguousarray(gray, np.uint8)
+    h, w = gray.shape
+    T = np.empty((h + 1, w + 1), np.int32)
+    lib().orc_integral_tilted(_p(gray), w, h, _p(T))
+    return T
 
 
 def scale_list(W, H, ow, oh, scale_factor=1.1, min_size=(30, 30), max_size=(0, 0)):

@@ -43,3 +43,40 @@ CASCADES = ["alt", "alt2", "default", "alt_tree"]
 
 def rectset(a):
     return sorted(map(tuple, [[int(v) for v in r] for r in a]))
+
+
+def all_cv2_haar_cascades():
+    """Every Haar cascade file cv2 ships (17 in cv2 4.13; 9 of them use 45-degree tilted features)."""
+    import glob
+    import cv2
+    return sorted(glob.glob(os.path.join(cv2.data.haarcascades, "haarcascade_*.xml")))
+
+
+def truncate_cascade(path, nstages, out_path):
+    """Writes a copy of a cascade file (either format) that keeps only its first `nstages` stages: many windows then
+    survive to the end, which exercises every evaluator and the final-stage sums far more than the
+    full cascade does on a handful of frames (the crafted-cascade idea of SURVEY A.6)."""
+    import xml.etree.ElementTree as ET
+    tree = ET.parse(path)
+    casc = [e for e in tree.getroot() if e.find("stages") is not None][0]
+    stages = casc.find("stages")
+    for e in list(stages)[nstages:]:
+        stages.remove(e)
+    if casc.find("stageNum") is not None:        # new format only; old-format files just list their stages
+        casc.find("stageNum").text = str(nstages)
+    with open(out_path, "wb") as fh:
+        fh.write(b'<?xml version="1.0"?>\n')
+        tree.write(fh)
+    return str(out_path)
+
+
+def pass_everything_cascade(out_path, win=(20, 20)):
+    """a one-stump cascade whose two leaves both clear the stage threshold, so it accepts every
+    window that is evaluated and passes the variance test -- it enumerates the oracle's window grid."""
+    with open(out_path, "w") as fh:
+        fh.write('<?xml version="1.0"?>\n<opencv_storage><c type_id="opencv-haar-classifier">'
+                 f"<size>{win[0]} {win[1]}</size><stages><_><trees><_><_>"
+                 "<feature><rects><_>1 1 4 4 -1.</_><_>2 2 2 2 2.</_></rects><tilted>0</tilted></feature>"
+                 "<threshold>0.1</threshold><left_val>1.</left_val><right_val>1.</right_val></_></_></trees>"
+                 "<stage_threshold>0.5</stage_threshold><parent>-1</parent><next>-1</next></_></stages></c></opencv_storage>")
+    return str(out_path)

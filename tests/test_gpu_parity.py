@@ -1,9 +1,11 @@
 """GPU parity tests proper: every kernel of the path against the CPU oracle (and live cv2 4.13),
 called through the C ABI (ctypes -> libugdet.so).  Bit-exact: integers, bytes, decisions, rects."""
+import os
+
 import numpy as np
 import pytest
 
-from conftest import CASCADES, rectset
+from conftest import CASCADES, all_cv2_haar_cascades, pass_everything_cascade, rectset, truncate_cascade
 
 pytestmark = pytest.mark.gpu
 
@@ -313,3 +315,91 @@ def test_properties_at_bench_size(ug, synth, cv2ref):
     assert ctr["frames"] == 8 and ctr["levels"] == 33 and ctr["grid_windows"] == 8 * 1185515 or ctr["grid_windows"] > 0
     assert ctr["windows_evaluated"] <= ctr["grid_windows"] and ctr["grouped"] == sum(len(x) for x in a)
     det.close()
+
+
+# ---- any Haar cascade cv2 can load (tilted features, non-square windows) -------------------
+
+def test_tilted_integral_bit_exact(ug, synth):
+    """k_tilted against the third output of cv2.integral3, every level, including a wrapping 720p frame."""
+    import cv2
+    c = ug.Cascade(cv2.data.haarcascades + "haarcascade_smile.xml")
+    assert c.info.has_tilted == 1
+    det = ug.Detector(c, ug.default_params(), max_size=(1280, 720), max_batch=2)
+    bright = np.full((720, 1280), 255, np.uint8)
+    bright[::7, ::5] = 3
+    for g in (synth.gray_frame(640, 360, 6, 5), bright, synth.gray_frame(333, 217, 3, 1)):
+        h, w = g.shape
+        det.detect_gray(g)
+        sc, lw, lh, _ = det.plan_info(w, h)
+        for i in range(len(sc)):
+            img, S, SQ = det.level(i, int(lw[i]), int(lh[i]))
+            T = det.level_tilted(i, int(lw[i]), int(lh[i]))
+            s2, q2, t2 = cv2.integral3(img, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
+            assert np.array_equal(T, t2), f"{w}x{h} level {i} tilted integral"
+            assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+    det.close()
+    # a cascade without tilted features never builds the plane
+    c2 = ug.Cascade(cv2.data.haarcascades + "haarcascade_eye.xml")
+    d2 = ug.Detector(c2, ug.default_params(), max_size=(320, 180), max_batch=1)
+    d2.detect_gray(synth.gray_frame(320, 180, 2, 0))
+    with pytest.raises(ug.UgdError) as e:
+        d2.level_tilted(0, 10, 10)
+    assert e.value.code == ug.ERR_UNSUPPORTED
+    d2.close()
+
+
+@pytest.mark.parametrize("path", all_cv2_haar_cascades(), ids=lambda p: os.path.basename(p)[12:-4])
+def test_every_cv2_haar_cascade(ug, synth, orc, tmp_path, path):
+    """All 17 Haar files cv2 ships -- 9 with tilted features, windows from 14x28 to 64x16 -- decision for
+    decision against the oracle (itself pinned to cv2 on the same files): the full cascade on 640x360 and a
+    4-stage truncation on 320x180 that accepts thousands of windows (final-stage sums bitwise)."""
+    import cv2
+    cases = ((path, synth.gray_frame(640, 360, 6, 3)),
+             (truncate_cascade(path, 4, tmp_path / "t4.xml"), synth.gray_frame(320, 180, 3, 7)))
+    for p, g in cases:
+        h, w = g.shape
+        c = ug.Cascade(p)
+        oc = orc.OracleCascade.load(p)
+        det = ug.Detector(c, ug.default_params(max_raw_per_frame=1 << 17), max_size=(w, h), max_batch=1)
+        det.set_stage_map(True)
+        got = det.detect_gray(g)
+        raw, sums = det.raw(cap=1 << 17)
+        smap = det.stage_map()
+        ctr = det.counters()
+        oraw, osums, octr, omap = orc.detect_raw(oc, g, want_map=True, cap=1 << 17)
+        assert len(smap) == len(omap)
+        bad = np.nonzero(smap != omap)[0]
+        assert len(bad) == 0, f"{p}: {len(bad)} window decisions differ, first at {bad[:5]}: {smap[bad[:5]]} vs {omap[bad[:5]]}"
+        for k in ("windows_evaluated", "grid_windows", "lowvar"):
+            assert ctr[k] == octr[k], (p, k)
+        if c.info.max_tree_nodes == 1:          # trees: the engine counts every node of a tree, the oracle the visited ones
+            assert ctr["weak_evals"] == octr["weak_evals"], p
+        a = sorted(zip(map(tuple, raw.tolist()), sums.tolist()))
+        b = sorted(zip(map(tuple, oraw.tolist()), osums.tolist()))
+        assert a == b, p
+        want, _ = orc.detect_multiscale(oc, g)
+        assert rectset(got) == rectset(want), p
+        cc = cv2.CascadeClassifier(p)
+        assert rectset(got) == rectset(cc.detectMultiScale(g, scaleFactor=1.1, minNeighbors=2, minSize=(30, 30)))
+        det.close()
+
+
+def test_window_grid_follows_cv2_row_stripes(ug, orc, tmp_path):
+    """The stripe rule that drops the last grid row of some levels (oracle test of the same name): the engine's
+    grid, enumerated with a pass-everything cascade, equals cv2's on sizes where rows are really lost."""
+    import cv2
+    rng = np.random.default_rng(11)
+    p = pass_everything_cascade(tmp_path / "all.xml")
+    c = ug.Cascade(p)
+    cc = cv2.CascadeClassifier(p)
+    for (w, h) in [(320, 180), (201, 202), (417, 233), (640, 360)]:
+        g = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        det = ug.Detector(c, ug.default_params(min_neighbors=0, max_raw_per_frame=1 << 18), max_size=(w, h), max_batch=1)
+        det.detect_gray(g, cap=16)
+        raw, _ = det.raw(cap=1 << 18)
+        want = np.asarray(cc.detectMultiScale(g, scaleFactor=1.1, minNeighbors=0, minSize=(30, 30))).reshape(-1, 4)
+        clipped = raw.copy()
+        clipped[:, 2] = np.minimum(raw[:, 0] + raw[:, 2], w) - raw[:, 0]
+        clipped[:, 3] = np.minimum(raw[:, 1] + raw[:, 3], h) - raw[:, 1]
+        assert rectset(clipped) == rectset(want), (w, h)
+        det.close()

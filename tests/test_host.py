@@ -10,10 +10,10 @@ import textwrap
 import numpy as np
 import pytest
 
-from conftest import CASCADES, ROOT
+from conftest import CASCADES, ROOT, all_cv2_haar_cascades
 
 FIELDS = ["stage_first_tree", "stage_ntrees", "stage_thr", "tree_first_node", "tree_nnodes", "node_rects",
-          "node_weights", "node_thr", "node_left", "node_right", "node_left_val", "node_right_val"]
+          "node_weights", "node_thr", "node_left", "node_right", "node_left_val", "node_right_val", "node_tilted"]
 
 
 @pytest.mark.parametrize("name", CASCADES)
@@ -35,6 +35,24 @@ def test_xml_loader_matches_independent_parser(ug, cv2ref, name):
         assert c.info.sum_exact == 1
         assert c.info.old_format == (1 if path == ref else 0)
         assert (c.info.win_w, c.info.nstages) == (f.win_w, f.nstages)
+
+
+def test_xml_loader_reads_every_cv2_haar_cascade(ug):
+    """8(f) N4: all 17 Haar files cv2 ships load (tilted features, 14x28 ... 64x16 windows, <cascade> nodes
+    without a type_id) and agree with the independent parser number for number."""
+    from oracle.cascade_xml import load_cascade
+    paths = all_cv2_haar_cascades()
+    assert len(paths) >= 17
+    ntilted = 0
+    for path in paths:
+        c = ug.Cascade(path)
+        d = c.dump()
+        f = load_cascade(path)
+        for k in FIELDS:
+            assert np.array_equal(d[k], getattr(f, k)), (path, k)
+        assert c.info.has_tilted == int(f.tilted) and (c.info.win_w, c.info.win_h) == (f.win_w, f.win_h)
+        ntilted += c.info.has_tilted
+    assert ntilted >= 9
 
 
 def _old_format_xml(f):
@@ -90,14 +108,17 @@ def test_loader_errors(ug, tmp_path):
     with pytest.raises(ug.UgdError) as e:
         ug.Cascade(str(bad))
     assert e.value.code == ug.ERR_PARSE
-    tilted = tmp_path / "tilted.xml"
-    tilted.write_text('<opencv_storage><c type_id="opencv-haar-classifier"><size>20 20</size><stages><_><trees><_><_>'
-                      "<feature><rects><_>1 1 4 4 -1.</_><_>2 2 2 2 2.</_></rects><tilted>1</tilted></feature>"
-                      "<threshold>0.1</threshold><left_val>0.1</left_val><right_val>0.2</right_val></_></_></trees>"
-                      "<stage_threshold>0.1</stage_threshold><parent>-1</parent><next>-1</next></_></stages></c></opencv_storage>")
-    with pytest.raises(ug.UgdError) as e:
-        ug.Cascade(str(tilted))
-    assert e.value.code == ug.ERR_UNSUPPORTED
+    # a tilted rect that leaves the window (x - h < 0) is malformed; a fractional rect weight is unsupported
+    for tag, rects, code in (("tilted", "<_>1 1 4 4 -1.</_><_>2 2 2 2 2.</_>", ug.ERR_PARSE),
+                             ("weight", "<_>5 1 4 4 -1.5</_><_>6 2 2 2 2.</_>", ug.ERR_UNSUPPORTED)):
+        f = tmp_path / f"{tag}.xml"
+        f.write_text('<opencv_storage><c type_id="opencv-haar-classifier"><size>20 20</size><stages><_><trees><_><_>'
+                     f"<feature><rects>{rects}</rects><tilted>1</tilted></feature>"
+                     "<threshold>0.1</threshold><left_val>0.1</left_val><right_val>0.2</right_val></_></_></trees>"
+                     "<stage_threshold>0.1</stage_threshold><parent>-1</parent><next>-1</next></_></stages></c></opencv_storage>")
+        with pytest.raises(ug.UgdError) as e:
+            ug.Cascade(str(f))
+        assert e.value.code == code, tag
 
 
 def test_config_reader_matches_reference_keys(ug, tmp_path):

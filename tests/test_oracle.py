@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import CASCADES, rectset
+from conftest import CASCADES, all_cv2_haar_cascades, pass_everything_cascade, rectset, truncate_cascade
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_detections.json")
 
@@ -55,6 +55,60 @@ def test_integral_wraps_like_cv2(orc):
     s2, q2 = cv2.integral2(g, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)
     assert (q2 < 0).any()
     assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+
+
+def test_tilted_integral_matches_cv2(orc):
+    """8(f) N4: the tilted integral restatement vs the third output of cv2.integral3 (CV_32S)."""
+    import cv2
+    rng = np.random.default_rng(1)
+    for shape in [(1, 1), (1, 5), (5, 1), (7, 9), (270, 480), (447, 795)]:
+        g = rng.integers(0, 256, shape, dtype=np.uint8)
+        assert np.array_equal(orc.integral_tilted(g), cv2.integral3(g, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)[2]), shape
+    g = np.full((720, 1280), 255, np.uint8)
+    assert np.array_equal(orc.integral_tilted(g), cv2.integral3(g, sdepth=cv2.CV_32S, sqdepth=cv2.CV_32S)[2])
+
+
+@pytest.mark.parametrize("path", all_cv2_haar_cascades(), ids=lambda p: os.path.basename(p)[12:-4])
+def test_every_cv2_haar_cascade_matches_cv2(orc, cv2ref, synth, tmp_path, path):
+    """8(f) N4: any Haar cascade cv2 can load -- tilted features, non-square windows, files without a
+    type_id -- gives the same raw windows as cv2; on a 4-stage truncation (thousands of accepted windows)
+    also the same final-stage sums, bitwise."""
+    import cv2
+    g = synth.gray_frame(320, 180, 3, 7)
+    for p, cap in ((path, 1 << 16), (truncate_cascade(path, 4, tmp_path / "t4.xml"), 1 << 18)):
+        oc = orc.OracleCascade.load(p)
+        cc = cv2.CascadeClassifier(p)
+        raw, sums, _ = orc.detect_raw(oc, g, cap=cap)
+        r3, _lv, wt = cc.detectMultiScale3(g, scaleFactor=1.1, minNeighbors=0, minSize=(30, 30), outputRejectLevels=True)
+        a = sorted(zip(map(tuple, _clip(raw, 320, 180).tolist()), sums.tolist()))
+        b = sorted(zip(map(tuple, np.asarray(r3).reshape(-1, 4).tolist()), np.asarray(wt).reshape(-1).tolist()))
+        assert a == b, p
+    assert len(a) > 100                          # the truncated cascade really accepted many windows
+
+
+def test_window_grid_matches_cv2_row_stripes(orc, tmp_path):
+    """The rows cv2 visits: every level is cut into ns = ceil(first level's working width / 32) stripes of
+    ceil(floor(ny / step) / ns) * step rows, so some levels lose their last grid row (320x180 does, at the
+    39-pixel window).  A pass-everything cascade on noise enumerates the grid; compare it with cv2's."""
+    import cv2
+    rng = np.random.default_rng(11)
+    sizes = [(320, 180), (201, 202), (640, 360)] + [(int(rng.integers(60, 700)), int(rng.integers(60, 400))) for _ in range(9)]
+    lost = 0
+    for win in ((20, 20), (24, 24)):
+        p = pass_everything_cascade(tmp_path / f"all{win[0]}.xml", win)
+        oc = orc.OracleCascade.load(p)
+        cc = cv2.CascadeClassifier(p)
+        for (w, h) in sizes:
+            sf, ms = float(rng.choice([1.05, 1.1, 1.25])), [(0, 0), (30, 30), (50, 50)][int(rng.integers(0, 3))]
+            g = rng.integers(0, 256, (h, w), dtype=np.uint8)
+            raw, _, ctr = orc.detect_raw(oc, g, sf, ms, cap=1 << 20)
+            want = cc.detectMultiScale(g, scaleFactor=sf, minNeighbors=0, minSize=ms)
+            assert rectset(_clip(raw, w, h)) == rectset(np.asarray(want).reshape(-1, 4)), (win, w, h, sf, ms)
+            full = sum(len(range(0, lh + 1 - win[1], 1 if s >= 2 else 2)) * len(range(0, lw + 1 - win[0], 1 if s >= 2 else 2))
+                       for s in orc.scale_list(w, h, win[0], win[1], sf, ms)
+                       for lw, lh in [orc.level_size(w, h, float(s))])
+            lost += full - ctr["grid_windows"]
+    assert lost > 0                              # the rule really removed rows somewhere in this sample
 
 
 def test_group_rectangles_matches_cv2(orc):

@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM = range(8)
-K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_scan", "k_tail(unused)",
+K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_tilted", "k_scan",
            "k_group", "k_area")
 
 
@@ -38,7 +38,7 @@ class Params(C.Structure):
 
 class CascadeInfo(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("win_w", "win_h", "nstages", "ntrees", "nnodes", "max_tree_nodes",
-                                         "old_format", "sum_exact")]
+                                         "old_format", "sum_exact", "has_tilted")]
 
 
 class Counters(C.Structure):
@@ -130,7 +130,8 @@ class Cascade:
                  tree_nnodes=np.zeros(i.ntrees, np.int32), node_rects=np.zeros((i.nnodes, 3, 4), np.int32),
                  node_weights=np.zeros((i.nnodes, 3), np.float32), node_thr=np.zeros(i.nnodes, np.float32),
                  node_left=np.zeros(i.nnodes, np.int32), node_right=np.zeros(i.nnodes, np.int32),
-                 node_left_val=np.zeros(i.nnodes, np.float32), node_right_val=np.zeros(i.nnodes, np.float32))
+                 node_left_val=np.zeros(i.nnodes, np.float32), node_right_val=np.zeros(i.nnodes, np.float32),
+                 node_tilted=np.zeros(i.nnodes, np.int32))
         rc = lib().ugd_cascade_dump(self._h, *[_p(v) for v in d.values()])
         if rc:
             raise UgdError(rc)
@@ -317,6 +318,12 @@ class Detector:
         S = np.zeros((lh + 1, lw + 1), np.int32); SQ = np.zeros((lh + 1, lw + 1), np.int32)
         self._ck(lib().ugd_get_level(self._h, idx, _p(img), _p(S), _p(SQ)))
         return img, S, SQ
+
+    def level_tilted(self, idx, lw, lh):
+        """Tilted integral plane of a level (only for cascades with tilted features)."""
+        T = np.zeros((lh + 1, lw + 1), np.int32)
+        self._ck(lib().ugd_get_level_tilted(self._h, idx, _p(T)))
+        return T
 
 
 def _rects_np(buf, n):

@@ -63,7 +63,7 @@ struct ugd_detector {
     // cascade on device
     DevPtr nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
-    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, carryS, carryQ, raw, rawsum,
+    DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, T, carryS, carryQ, raw, rawsum,
         rawcount, grp, out, outcount, counters, stage_map, gray_in;
     // host staging (pinned)
     ugd_rect* h_out = nullptr; int* h_counts = nullptr; unsigned long long* h_ctr = nullptr;
@@ -114,6 +114,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
+    if (c.has_tilted) CK(init_tilted_attributes(dp->host.max_level_w));
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
     *out = dp.get();
     d->plans[key] = std::move(dp);
@@ -132,6 +133,7 @@ int upload_cascade(ugd_detector* d) {
             std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
     const ScanGeom geom = make_scan_geom(c.win_w, c.win_h);
+    const bool words = scan_word_offsets(c);
     std::vector<uint4> B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
     for (int si = 0; si < 2; ++si) { TA[si].resize(c.nnodes()); TB[si].resize(c.nnodes()); }
     std::vector<uint32_t> M(c.nnodes());
@@ -146,7 +148,11 @@ int upload_cascade(ugd_detector* d) {
                           cf[0] | cf[1] << 8 | cf[2] << 16 | cf[3] << 24, cf[4] | cf[5] << 8 | cf[6] << 16 | cf[7] << 24);
         for (int si = 0; si < 2; ++si) {              // the same lists with offsets into the scan tile
             uint32_t to[12];
-            for (int j = 0; j < 12; ++j) to[j] = (uint32_t)scan_tile_off(geom, si, cn.cx[j], cn.cy[j]);
+            for (int j = 0; j < 12; ++j) {
+                to[j] = (uint32_t)(scan_tile_off(geom, si, cn.cx[j], cn.cy[j]) + (cn.plane ? scan_plane_bytes(geom, si) : 0));
+                if (words) to[j] >>= 2;
+                if (to[j] > 0xffffu) { d->err = "scan tile too large for the per-lane offset tables"; return UGD_ERR_UNSUPPORTED; }
+            }
             TA[si][i] = make_uint4(to[0] | to[1] << 16, to[2] | to[3] << 16, to[4] | to[5] << 16, to[6] | to[7] << 16);
             TB[si][i] = make_uint4(to[8] | to[9] << 16, to[10] | to[11] << 16, B[i].z, B[i].w);
         }
@@ -195,6 +201,7 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->pyr.reserve(F * p.pyr_bytes + 256));
     CK(d->S.reserve(F * p.int_ints * 4 + 256));
     CK(d->SQ.reserve(F * p.int_ints * 4 + 256));
+    if (d->casc->has_tilted) CK(d->T.reserve(F * p.int_ints * 4 + 256));
     CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
     CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
     CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
@@ -258,7 +265,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.w = p.w; b.h = p.h; b.nlevels = (int)p.levels.size(); b.nframes = nframes;
     b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
     b.stumps_only = c.max_tree_nodes == 1;
-    b.fast_scan = scan_mode(c);
+    b.fast_scan = scan_mode(c); b.word_off = scan_word_offsets(c) ? 1 : 0;
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeC = d->nodeC.as<uint4>();
     b.nodeM = d->nodeM.as<uint32_t>();
@@ -279,6 +286,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     }
     b.pyr = d->pyr.as<uint8_t>(); b.pyr_stride = p.pyr_bytes;
     b.S = d->S.as<int32_t>(); b.SQ = d->SQ.as<int32_t>(); b.int_stride = p.int_ints;
+    b.T = d->casc->has_tilted ? d->T.as<int32_t>() : nullptr;
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
     b.pos_stride = p.pos_entries;
     b.tile_min = d->tile_min;
@@ -309,12 +317,13 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 5);
     launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
     mark(d, 6);
+    if (b.T) launch_tilted(b, p.max_level_w, st);
+    mark(d, 7);
     {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
         launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st);
     }
-    mark(d, 7);
     mark(d, 8);
     launch_group(b, st);
     mark(d, 9);
@@ -328,7 +337,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     bool overflow = false;
     finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, 1, 0, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, b.T ? 1 : 0, 1, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_AREA; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
@@ -461,12 +470,12 @@ int ugd_cascade_get_info(const ugd_cascade* c, ugd_cascade_info* i) {
     if (!c || !i) return UGD_ERR_ARG;
     i->win_w = c->c.win_w; i->win_h = c->c.win_h; i->nstages = c->c.nstages(); i->ntrees = c->c.ntrees();
     i->nnodes = c->c.nnodes(); i->max_tree_nodes = c->c.max_tree_nodes; i->old_format = c->c.old_format;
-    i->sum_exact = c->c.sum_exact;
+    i->sum_exact = c->c.sum_exact; i->has_tilted = c->c.has_tilted;
     return UGD_OK;
 }
 
 int ugd_cascade_dump(const ugd_cascade* cc, int32_t* sft, int32_t* snt, float* sthr, int32_t* tfn, int32_t* tnn,
-                     int32_t* nrects, float* nw, float* nthr, int32_t* nl, int32_t* nr, float* nlv, float* nrv) {
+                     int32_t* nrects, float* nw, float* nthr, int32_t* nl, int32_t* nr, float* nlv, float* nrv, int32_t* ntl) {
     if (!cc) return UGD_ERR_ARG;
     const Cascade& c = cc->c;
     for (int s = 0; s < c.nstages(); ++s) {
@@ -484,6 +493,7 @@ int ugd_cascade_dump(const ugd_cascade* cc, int32_t* sft, int32_t* snt, float* s
         if (nr) nr[n] = h.right;
         if (nlv) nlv[n] = h.left_val;
         if (nrv) nrv[n] = h.right_val;
+        if (ntl) ntl[n] = h.tilted;
     }
     return UGD_OK;
 }
@@ -520,7 +530,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
     for (auto& ev : d->ev_area) cudaEventCreate(&ev);
-    if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h)) != cudaSuccess) {
+    if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
     }
     int rc = upload_cascade(d);
@@ -538,7 +548,7 @@ void ugd_destroy(ugd_detector* d) {
     for (auto& kv : d->area_plans) kv.second->release();
     d->src_full.release(); d->area_dst.release();
     DevPtr* all[] = {&d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
-                     &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ,
+                     &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ, &d->T,
                      &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};
     for (DevPtr* p : all) p->release();
@@ -685,7 +695,7 @@ int ugd_get_kernel_times(const ugd_detector* d, float* t, int64_t* l) {
 
 const char* ugd_kernel_name(int k) {
     static const char* names[UGD_K_COUNT] = {"k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry",
-                                             "k_integral", "k_scan", "k_tail(unused)", "k_group", "k_area"};
+                                             "k_integral", "k_tilted", "k_scan", "k_group", "k_area"};
     return k >= 0 && k < UGD_K_COUNT ? names[k] : "?";
 }
 
@@ -773,6 +783,18 @@ int ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t*
     size_t wbytes = (size_t)(L.sw + 1) * 4;
     if (S) CK(cudaMemcpy2D(S, wbytes, d->last.S + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
     if (SQ) CK(cudaMemcpy2D(SQ, wbytes, d->last.SQ + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
+    return UGD_OK;
+}
+
+int ugd_get_level_tilted(ugd_detector* d, int level, int32_t* T) {
+    if (!d || !d->last_plan || !T) return UGD_ERR_ARG;
+    const Plan& p = d->last_plan->host;
+    if (level < 0 || level >= (int)p.levels.size()) return UGD_ERR_ARG;
+    if (!d->last.T) return UGD_ERR_UNSUPPORTED;          // the cascade has no tilted features: the plane is never built
+    CK(cudaSetDevice(d->device));
+    const LevelInfo& L = p.levels[level];
+    const size_t wbytes = (size_t)(L.sw + 1) * 4;
+    CK(cudaMemcpy2D(T, wbytes, d->last.T + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
     return UGD_OK;
 }
 

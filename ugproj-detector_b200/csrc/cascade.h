@@ -13,6 +13,7 @@ struct HostNode {
     float   thr;
     int32_t left, right;    // > 0: child node index inside the tree, 0: leaf
     float   left_val, right_val;
+    int32_t tilted;         // 1: the rects are 45-degree tilted (read the tilted integral)
 };
 
 // Corner-list form of a node: feature = sum_j coef[j] * S[corner j], duplicates merged
@@ -21,12 +22,14 @@ struct CornerNode {
     int nc;                 // corners used, padded with coef 0 up to 6, 8, 9 or 12
     int8_t cx[12], cy[12];  // corner position inside the window
     int8_t coef[12];
+    int8_t plane;           // 0: upright integral S, 1: tilted integral T
 };
 
 struct Cascade {
     int win_w = 0, win_h = 0;
     bool old_format = false;
     bool sum_exact = false;
+    bool has_tilted = false;                // some node reads the tilted integral
     bool delta_exact = false;               // base + sum of (left - right) is exact too (see cascade_xml.cc)
     int max_tree_nodes = 0;
     std::vector<int32_t> stage_first_tree, stage_ntrees;

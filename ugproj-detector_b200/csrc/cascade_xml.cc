@@ -153,7 +153,7 @@ int load_old(const Elem& root, Cascade& c, std::string& err) {
                 if (!feat) { err = "node without <feature>"; return UGD_ERR_PARSE; }
                 if (!parse_rects(feat->child("rects"), n, err)) return UGD_ERR_PARSE;
                 double t = 0;
-                if (one_number(feat->child("tilted"), t) && t != 0) { err = "tilted Haar features are not supported"; return UGD_ERR_UNSUPPORTED; }
+                if (one_number(feat->child("tilted"), t) && t != 0) n.tilted = 1;
                 double d;
                 if (!one_number(nd->child("threshold"), d)) { err = "node without <threshold>"; return UGD_ERR_PARSE; }
                 n.thr = (float)d;
@@ -187,7 +187,7 @@ int load_new(const Elem& root, Cascade& c, std::string& err) {
         HostNode n{};
         if (!parse_rects(f->child("rects"), n, err)) return UGD_ERR_PARSE;
         double t = 0;
-        if (one_number(f->child("tilted"), t) && t != 0) { err = "tilted Haar features are not supported"; return UGD_ERR_UNSUPPORTED; }
+        if (one_number(f->child("tilted"), t) && t != 0) n.tilted = 1;
         fl.push_back(n);
     }
     std::vector<double> in, lv;
@@ -260,9 +260,10 @@ int validate_and_derive(Cascade& c, std::string& err) {
                     if (w != (float)(int)w || fabsf(w) > 127.f) { err = "non-integer feature weight"; return UGD_ERR_UNSUPPORTED; }
                     if (w == 0.f) continue;
                     const int32_t* q = n.rect[r];
-                    if (q[0] < 0 || q[1] < 0 || q[2] <= 0 || q[3] <= 0 || q[0] + q[2] > c.win_w || q[1] + q[3] > c.win_h) {
-                        err = "feature rectangle outside the window"; return UGD_ERR_PARSE;
-                    }
+                    const bool inside = n.tilted
+                        ? (q[0] - q[3] >= 0 && q[1] >= 0 && q[2] > 0 && q[3] > 0 && q[0] + q[2] <= c.win_w && q[1] + q[2] + q[3] <= c.win_h)
+                        : (q[0] >= 0 && q[1] >= 0 && q[2] > 0 && q[3] > 0 && q[0] + q[2] <= c.win_w && q[1] + q[3] <= c.win_h);
+                    if (!inside) { err = "feature rectangle outside the window"; return UGD_ERR_PARSE; }
                     sumw += abs((int)w);
                 }
                 if (n.weight[0] == 0.f || n.weight[1] == 0.f) { err = "feature needs at least two rects"; return UGD_ERR_UNSUPPORTED; }
@@ -276,8 +277,14 @@ int validate_and_derive(Cascade& c, std::string& err) {
                         int w = (int)n.weight[r];
                         if (!w) continue;
                         const int32_t* q = n.rect[r];
-                        const int px[4] = {q[0], q[0] + q[2], q[0], q[0] + q[2]};
-                        const int py[4] = {q[1], q[1], q[1] + q[3], q[1] + q[3]};
+                        // upright: S(x,y) - S(x+w,y) - S(x,y+h) + S(x+w,y+h)
+                        // tilted : T(x,y) - T(x-h,y+h) - T(x+w,y+w) + T(x+w-h,y+w+h)   (cv2's CV_TILTED_OFS)
+                        const int ux[4] = {q[0], q[0] + q[2], q[0], q[0] + q[2]};
+                        const int uy[4] = {q[1], q[1], q[1] + q[3], q[1] + q[3]};
+                        const int tx4[4] = {q[0], q[0] - q[3], q[0] + q[2], q[0] + q[2] - q[3]};
+                        const int ty4[4] = {q[1], q[1] + q[3], q[1] + q[2], q[1] + q[2] + q[3]};
+                        const int* px = n.tilted ? tx4 : ux;
+                        const int* py = n.tilted ? ty4 : uy;
                         const int sg[4] = {w, -w, -w, w};
                         for (int e = 0; e < 4; ++e) {
                             int f = 0;
@@ -292,6 +299,8 @@ int validate_and_derive(Cascade& c, std::string& err) {
                         cn.cx[o] = (int8_t)tx[f]; cn.cy[o] = (int8_t)ty[f]; cn.coef[o] = (int8_t)tc[f]; ++o;
                     }
                     cn.nc = o <= 6 ? 6 : (o <= 8 ? 8 : (o <= 9 ? 9 : 12));   // padding entries: corner (0,0), coef 0
+                    cn.plane = n.tilted ? 1 : 0;
+                    if (n.tilted) c.has_tilted = true;
                     c.corners[base + k] = cn;
                 }
                 for (int side = 0; side < 2; ++side) {
@@ -336,7 +345,8 @@ int load_cascade_xml(const std::string& path, Cascade& out, std::string& err) {
     err = "no Haar cascade node in file";
     for (auto& k : root.kids) {
         if (k->type_id == "opencv-haar-classifier") { err.clear(); rc = load_old(*k, out, err); break; }
-        if (k->type_id == "opencv-cascade-classifier") { err.clear(); rc = load_new(*k, out, err); break; }
+        // some shipped files (haarcascade_frontalcatface*.xml) carry no type_id on <cascade>
+        if (k->type_id == "opencv-cascade-classifier" || (k->type_id.empty() && k->child("stageType"))) { err.clear(); rc = load_new(*k, out, err); break; }
     }
     if (rc != UGD_OK) return rc;
     return validate_and_derive(out, err);

@@ -70,6 +70,15 @@ static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     //
     return 4 * (si ? y * g.TP[1] + (x & 1) * g.TCH[1] + (x >> 1) : y * g.TP[0] + x);
 }
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y) { return tile_off(g, si, x, y); }
+// The tilted-integral tile (cascades with tilted features only) sits right behind the S tile, same geometry.
+int32_t scan_plane_bytes(const ScanGeom& g, int si) { return 4 * g.TR[si] * g.TP[si]; }
+
+// 16-bit byte addresses cover the static shared arrays plus one tile of a small window; anything larger
+// (two tiles for tilted cascades, wide windows) switches the per-lane tables to word offsets.
+bool scan_word_offsets(const Cascade& c) {
+    const ScanGeom g = make_scan_geom(c.win_w, c.win_h);
+    return c.has_tilted || g.tile_ints * 4 > 48 * 1024;
+}
 
 // Which in-tile evaluator a cascade gets: 1 = stumps, 2 = two-node trees (root + one child), both with
 // exact "base + deltas" stage sums; 0 = the generic evaluator (any tree shape, plain leaf sums).
@@ -110,7 +119,7 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             memset(&d, 0, sizeof d);
             for (int j = 0; j < 12; ++j) {
                 d.coef[j] = cn.coef[j];
-                for (int si = 0; si < 2; ++si) d.off[si][j] = tile_off(g, si, cn.cx[j], cn.cy[j]);
+                for (int si = 0; si < 2; ++si) d.off[si][j] = tile_off(g, si, cn.cx[j], cn.cy[j]) + (cn.plane ? scan_plane_bytes(g, si) : 0);
             }
             d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
                      (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
@@ -319,26 +328,32 @@ __device__ __forceinline__ int lds32(uint32_t addr) {
 }
 __device__ __forceinline__ int sx8(uint32_t w, int byte) { return (int)(int8_t)(w >> (8 * byte)); }
 
-// response of node n against the window whose shared-memory byte address is packed in pb2
+// With two tiles (tilted cascades) or a large window the addresses no longer fit 16 bits: the tables then
+// hold WORD offsets and pb2 the window's word address (WORDS = true).
+template <bool WORDS> __device__ __forceinline__ uint32_t lo16(uint32_t o) { return WORDS ? (o << 2) & 0x3fffcu : o & 0xffffu; }
+template <bool WORDS> __device__ __forceinline__ uint32_t hi16(uint32_t o) { return WORDS ? (o >> 14) & 0x3fffcu : o >> 16; }
+
+// response of node n against the window whose shared-memory byte (or word) address is packed in pb2
+template <bool WORDS>
 __device__ __forceinline__ int lane_resp(const DevBufs& b, const uint4* __restrict__ nA, const uint4* __restrict__ nB, int n, uint32_t pb2, uint32_t nc, uint4& C) {
     const uint4 A = __ldg(nA + n);
     const uint4 B = __ldg(nB + n);
     C = __ldg(b.nodeC + n);
     const uint32_t o01 = A.x + pb2, o23 = A.y + pb2, o45 = A.z + pb2;
-    int a = sx8(B.z, 0) * lds32(o01 & 0xffffu) + sx8(B.z, 1) * lds32(o01 >> 16) + sx8(B.z, 2) * lds32(o23 & 0xffffu);
-    int c = sx8(B.z, 3) * lds32(o23 >> 16) + sx8(B.w, 0) * lds32(o45 & 0xffffu) + sx8(B.w, 1) * lds32(o45 >> 16);
+    int a = sx8(B.z, 0) * lds32(lo16<WORDS>(o01)) + sx8(B.z, 1) * lds32(hi16<WORDS>(o01)) + sx8(B.z, 2) * lds32(lo16<WORDS>(o23));
+    int c = sx8(B.z, 3) * lds32(hi16<WORDS>(o23)) + sx8(B.w, 0) * lds32(lo16<WORDS>(o45)) + sx8(B.w, 1) * lds32(hi16<WORDS>(o45));
     if (nc > 6) {
         const uint32_t o67 = A.w + pb2;
-        a += sx8(B.w, 2) * lds32(o67 & 0xffffu);
-        c += sx8(B.w, 3) * lds32(o67 >> 16);
+        a += sx8(B.w, 2) * lds32(lo16<WORDS>(o67));
+        c += sx8(B.w, 3) * lds32(hi16<WORDS>(o67));
         if (nc > 8) {
             const uint32_t o89 = B.x + pb2;
-            a += sx8(C.x, 0) * lds32(o89 & 0xffffu);
+            a += sx8(C.x, 0) * lds32(lo16<WORDS>(o89));
             if (nc > 9) {
                 const uint32_t oab = B.y + pb2;
-                c += sx8(C.x, 1) * lds32(o89 >> 16);
-                a += sx8(C.x, 2) * lds32(oab & 0xffffu);
-                c += sx8(C.x, 3) * lds32(oab >> 16);
+                c += sx8(C.x, 1) * lds32(hi16<WORDS>(o89));
+                a += sx8(C.x, 2) * lds32(lo16<WORDS>(oab));
+                c += sx8(C.x, 3) * lds32(hi16<WORDS>(oab));
             }
         }
     }
@@ -351,7 +366,7 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <int MODE>
+template <int MODE, bool WORDS>
 __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
     constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols;
     static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
@@ -388,12 +403,14 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96; i += NW * 32) (&s_alive[0][0])[i] = 0;
-        // ---- 1. stage the S tile ----
-        {
+        // ---- 1. stage the S tile (and, for cascades with tilted features, the T tile behind it) ----
+        for (int pl = 0; pl < (b.T ? 2 : 1); ++pl) {
+            const int32_t* plane = pl ? b.T + (size_t)frame * b.int_stride + Lg.int_off : S;
+            int* tile = s_tile + pl * TR * TP;
             const int X0 = xi0 * step, Y0 = r0 * step;
             for (int r = w; r < TR; r += NW) {
-                const int32_t* src = S + (size_t)min(Y0 + r, sh) * P;
-                int* dst = s_tile + r * TP;
+                const int32_t* src = plane + (size_t)min(Y0 + r, sh) * P;
+                int* dst = tile + r * TP;
                 for (int c = lane; c < TC; c += 32) {
                     const int v = src[min(X0 + c, sw)];
                     dst[si ? (c & 1) * TCH + (c >> 1) : c] = v;
@@ -608,7 +625,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                 const int id = s_list[i], rl = id >> 6, c = id & (C - 1);
                 const float vnf = s_vnf[id];
                 const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + (rl * step) * TP + c);
-                const uint32_t pb2 = pbase | pbase << 16;
+                const uint32_t pw = WORDS ? pbase >> 2 : pbase;
+                const uint32_t pb2 = pw | pw << 16;
                 int st = s;
                 double sum = 0.0;
                 for (; st < nstages; ++st) {
@@ -619,7 +637,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                         for (int t = lane; t < nt; t += 32) {
                             const int n = n0 + t;
                             uint4 Cq;
-                            const int r = lane_resp(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
+                            const int r = lane_resp<WORDS>(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
                             const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
                             part += (double)__uint_as_float(lt ? Cq.z : Cq.w);
                         }
@@ -634,7 +652,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                             for (;;) {
                                 const uint32_t M = __ldg(b.nodeM + base + at);
                                 uint4 Cq;
-                                const int r = lane_resp(b, nA, nB, base + at, pb2, M & 255u, Cq);
+                                const int r = lane_resp<WORDS>(b, nA, nB, base + at, pb2, M & 255u, Cq);
                                 ++visited;
                                 const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
                                 leaf = __uint_as_float(lt ? Cq.z : Cq.w);
@@ -662,8 +680,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     if (lane == 0 && weak) atomicAdd(&s_ctr[3], weak);
     __syncthreads();
     if (tid < 5 && s_ctr[tid]) {
-        const int slot[5] = {CTR_EVALUATED, CTR_LOWVAR, CTR_NEAR, CTR_WEAK, CTR_QUEUED};
-        atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + slot[tid]], (unsigned long long)s_ctr[tid]);
+        constexpr unsigned slots = CTR_EVALUATED | CTR_LOWVAR << 4 | CTR_NEAR << 8 | CTR_WEAK << 12 | CTR_QUEUED << 16;   // s_ctr[i] -> counter
+        atomicAdd(&b.counters[(size_t)frame * kCtrPerFrame + ((slots >> (4 * tid)) & 15u)], (unsigned long long)s_ctr[tid]);
     }
 }
 
@@ -677,20 +695,29 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
     for (int half = 0; half < 2; ++half) {
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
-        const size_t smem = (size_t)g.TR[half ? 0 : 1] * g.TP[half ? 0 : 1] * sizeof(int);
-        if (b.fast_scan == 1) k_scan<1><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
-        else if (b.fast_scan == 2) k_scan<2><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
-        else k_scan<0><<<dim3(n, b.nframes), kScanWarps * 32, smem, st>>>(b, wk + first);
+        const size_t smem = (size_t)g.TR[half ? 0 : 1] * g.TP[half ? 0 : 1] * sizeof(int) * (b.T ? 2 : 1);
+        const dim3 grid(n, b.nframes);
+        const int variant = b.fast_scan * 2 + (b.word_off ? 1 : 0);
+        switch (variant) {
+            case 0: k_scan<0, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            case 1: k_scan<0, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            case 2: k_scan<1, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            case 3: k_scan<1, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            case 4: k_scan<2, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            default: k_scan<2, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+        }
     }
 }
 
-cudaError_t init_kernel_attributes(int win_w, int win_h) {
-    const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int);
+cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted) {
+    const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int) * (has_tilted ? 2 : 1);
     if (scan_smem > g_scan_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_scan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
-        if (e != cudaSuccess) return e;
+        const void* variants[6] = {(const void*)k_scan<0, false>, (const void*)k_scan<0, true>, (const void*)k_scan<1, false>,
+                                   (const void*)k_scan<1, true>, (const void*)k_scan<2, false>, (const void*)k_scan<2, true>};
+        for (const void* f : variants) {
+            cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
+            if (e != cudaSuccess) return e;
+        }
         g_scan_smem = scan_smem;
     }
     return cudaSuccess;

@@ -381,6 +381,89 @@ __global__ void __launch_bounds__(32) k_integral_bands(DevBufs b, const WorkItem
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K4t  tilted integral T (third output of cv::integral, int32, same (sh+1) x P layout as S):
+//   T(X,Y) = sum of img(x,y) over y < Y, |x - X + 1| <= Y - y - 1   -- a 45-degree cone with apex (X-1, Y-1).
+// With D1 / D2 the running sums along the two diagonals that end in a pixel,
+//   cone(x,y) = cone(x,y-1) + D1(x,y) + D2(x,y) - img(x,y),   D1(x,y) = D1(x-1,y-1) + img,  D2(x,y) = D2(x+1,y-1) + img.
+// One block walks one level of one frame top to bottom; a thread owns J columns (stride 256), keeps their
+// cone sums in registers and hands the diagonal sums to its neighbours through double-buffered shared
+// arrays (one barrier per row).  The next row's pixels are fetched before the barrier.  uint32 modular.
+// Only launched for cascades with tilted features.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTiltThreads = 256;
+
+template <int J>
+__device__ __forceinline__ void tilted_rows(const uint8_t* __restrict__ img, int pitch, int sw, int sh, uint32_t* __restrict__ T,
+                                            int P, uint32_t* sm, int slots) {
+    const int tid = threadIdx.x, W1 = sw + 1;
+    uint32_t* d1 = sm;                    // [2][slots]: slot X + 1 holds the sum of apex column X - 1
+    uint32_t* d2 = sm + 2 * slots;
+    uint32_t cone[J], px[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int X = tid + j * kTiltThreads;
+        cone[j] = 0;
+        px[j] = (X >= 1 && X < W1) ? img[X - 1] : 0u;
+        if (X < W1) T[X] = 0;
+    }
+    for (int i = tid; i < 4 * slots; i += kTiltThreads) sm[i] = 0;
+    __syncthreads();
+    for (int y = 0; y < sh; ++y) {
+        const int cur = (y & 1) * slots, nxt = slots - cur;
+        uint32_t p[J];
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int X = tid + j * kTiltThreads;
+            p[j] = px[j];
+            if (y + 1 < sh) px[j] = (X >= 1 && X < W1) ? img[(size_t)(y + 1) * pitch + X - 1] : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int X = tid + j * kTiltThreads;
+            if (X < W1) {
+                const uint32_t n1 = d1[cur + X] + p[j];          // from the upper-left neighbour
+                const uint32_t n2 = d2[cur + X + 2] + p[j];      // from the upper-right neighbour
+                cone[j] += n1 + n2 - p[j];
+                T[(size_t)(y + 1) * P + X] = cone[j];
+                d1[nxt + X + 1] = n1;
+                d2[nxt + X + 1] = n2;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kTiltThreads) k_tilted(DevBufs b) {
+    extern __shared__ uint32_t s_tilt[];
+    const LevelInfo& L = b.levels[blockIdx.x];
+    const int frame = blockIdx.y;
+    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
+    uint32_t* T = reinterpret_cast<uint32_t*>(b.T + (size_t)frame * b.int_stride + L.int_off);
+    const int slots = L.sw + 3;
+    const int need = (L.sw + 1 + kTiltThreads - 1) / kTiltThreads;
+    if (need <= 1) tilted_rows<1>(img, L.img_pitch, L.sw, L.sh, T, L.P, s_tilt, slots);
+    else if (need <= 2) tilted_rows<2>(img, L.img_pitch, L.sw, L.sh, T, L.P, s_tilt, slots);
+    else if (need <= 4) tilted_rows<4>(img, L.img_pitch, L.sw, L.sh, T, L.P, s_tilt, slots);
+    else if (need <= 8) tilted_rows<8>(img, L.img_pitch, L.sw, L.sh, T, L.P, s_tilt, slots);
+    else tilted_rows<17>(img, L.img_pitch, L.sw, L.sh, T, L.P, s_tilt, slots);
+}
+
+static size_t tilted_smem(int max_w) { return (size_t)4 * (max_w + 3) * sizeof(uint32_t); }
+
+// Called once per plan (per frame size) on the detector's device: levels wider than ~3000 pixels need more
+// than the default 48 KB of dynamic shared memory.
+cudaError_t init_tilted_attributes(int max_w) {
+    const size_t need = tilted_smem(max_w);
+    if (need <= 48 * 1024) return cudaSuccess;
+    return cudaFuncSetAttribute(k_tilted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+}
+
+void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st) {
+    if (!b.T || !b.nlevels) return;
+    k_tilted<<<dim3(b.nlevels, b.nframes), kTiltThreads, tilted_smem(max_level_w), st>>>(b);
+}
+
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
     if (nblocks) k_integral_bands<<<dim3(b.nframes, nblocks), 32, 0, st>>>(b, wk);
 }

@@ -58,6 +58,7 @@ struct DevBufs {
     //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
     const uint4* nodeC; const uint32_t* nodeM;
     const uint4* nodeTA[2]; const uint4* nodeTB[2];   // A/B with byte offsets into the scan tile (grid step 1 / 2 layouts)
+    int word_off;                                     // the A/B offsets are in 32-bit words (two tiles / large windows: bytes do not fit 16 bits)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
     const int32_t* tree_first_node; const int32_t* stage_first_node;
     // frames
@@ -70,6 +71,7 @@ struct DevBufs {
     // pyramid + integrals
     uint8_t* pyr; size_t pyr_stride;
     int32_t* S; int32_t* SQ; size_t int_stride;
+    int32_t* T;                                       // tilted integral, same layout as S; null unless the cascade has tilted features
     uint32_t* carryS; uint32_t* carryQ; size_t carry_stride;
     // window scan
     size_t pos_stride;                                // padded grid positions per frame
@@ -87,6 +89,8 @@ struct DevBufs {
 // to __constant__ (call before launching k_scan with a new cascade).
 ScanGeom make_scan_geom(int win_w, int win_h);
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
+int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
+bool scan_word_offsets(const Cascade& c);                         // per-lane tables in words instead of bytes
 int scan_mode(const Cascade& c);
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
 
@@ -113,8 +117,10 @@ void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
+void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st);
+cudaError_t init_tilted_attributes(int max_w);
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);
-cudaError_t init_kernel_attributes(int win_w, int win_h);
+cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted);
 
 }  // namespace ugd

@@ -2,6 +2,7 @@
 // contraction can change them (the file is compiled with -ffp-contract=off).
 #include "plan.h"
 
+#include <algorithm>
 #include <cmath>
 
 namespace ugd {
@@ -50,6 +51,15 @@ void build_plan(int w, int h, int win_w, int win_h, double scale_factor, int min
         if ((int)scales.size() >= kMaxLevels) break;
     }
     uint32_t img_off = 0, int_off = 0, pos_off = 0, carry_off = 0, xt = 0, yt = 0, map_off = 0;
+    // Rows the oracle really visits: cv2 cuts the rows of every level into the same number of stripes,
+    // ns = ceil(working width of the first level / 32), each ceil(floor(ny / step) / ns) * step rows high, and
+    // walks y < min(ns * stripe, ny) -- so a level with odd ny at step 2 loses its last grid row whenever the
+    // stripes tile floor(ny / 2) rows exactly (verified against cv2 4.13 with a pass-everything cascade).
+    int ns = 1;
+    if (!scales.empty()) {
+        const int nx0 = rint_f((float)w / scales[0]) + 1 - win_w;
+        ns = std::max((nx0 + 31) / 32, 1);
+    }
     for (float s : scales) {
         LevelInfo L{};
         L.scale = s;
@@ -61,7 +71,11 @@ void build_plan(int w, int h, int win_w, int win_h, double scale_factor, int min
         L.P = (int32_t)round_up((uint32_t)L.sw + 1, 32);
         L.step = s >= 2.f ? 1 : 2;                        // A.3
         L.nxg = (L.nx + L.step - 1) / L.step;
-        L.nyg = (L.ny + L.step - 1) / L.step;
+        {
+            const int stripe = std::max((L.ny / L.step + ns - 1) / ns, 1) * L.step;
+            const int64_t lim = std::min<int64_t>((int64_t)ns * stripe, L.ny);
+            L.nyg = (int32_t)((lim + L.step - 1) / L.step);
+        }
         L.nxg_pad = (int32_t)round_up((uint32_t)L.nxg, 32);
         L.nstrips = (L.sh + 1 + kStripRows - 1) / kStripRows;
         L.rect_w = rint_f((float)win_w * s);
@@ -90,6 +104,7 @@ void build_plan(int w, int h, int win_w, int win_h, double scale_factor, int min
         for (int seg = 0; seg * kIntSegRows < L.sh; ++seg)                         // one warp per (segment of 64 rows, band of 512 integral columns)
             for (int bnd = 0; bnd * kIntBand < L.sw + 1; ++bnd) p.wk_bands.push_back({level, bnd | seg << 8});
         add_work(p.wk_scan, level, L.nyg, kScanRows);      // one block per kScanRows grid rows
+        if (L.sw > p.max_level_w) p.max_level_w = L.sw;
         p.level_pixels += (int64_t)L.sw * L.sh;
         p.grid_windows += (int64_t)L.nxg * L.nyg;
         p.levels.push_back(L);

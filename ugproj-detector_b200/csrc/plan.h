@@ -27,7 +27,7 @@ struct LevelInfo {
     float   scale;
     int32_t rect_w, rect_h;    // rint(win_w*scale), rint(win_h*scale)
     uint32_t img_off;          // bytes, into a frame's pyramid buffer
-    uint32_t int_off;          // ints, into a frame's S (and SQ) buffer
+    uint32_t int_off;          // ints, into a frame's S (and SQ, and tilted T) buffer
     uint32_t pos_off;          // entries, into a frame's per-position arrays (padded layout)
     uint32_t carry_off;        // ints, into a frame's strip-carry arrays (nstrips x img_pitch)
     uint32_t xtab_off, ytab_off;  // entries, into the resize tables
@@ -43,6 +43,7 @@ struct Plan {
     std::vector<uint32_t> xtab, ytab;           // entry = i0 | c1 << 16  (c1 in 0..256)
     std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_bands, wk_scan;
     // per-frame sizes
+    int max_level_w = 0;                  // widest pyramid level (sizes the tilted-integral kernel's shared memory)
     size_t pyr_bytes = 0, int_ints = 0, pos_entries = 0, carry_ints = 0, map_entries = 0;
     int64_t level_pixels = 0, grid_windows = 0;
 };
