@@ -161,7 +161,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
-        "config": {"workload": f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, "
+        "config": {"workload": f"{os.path.basename(cv2_ref.cascade_path(args.cascade))} on synthetic {w}x{h} gray frames, "
                                f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}", "frames_per_step": per_step},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cv2.getNumThreads(), "kind": "reference",
                          "sample": f"{per_step} frames/step x {args.steps} steps, cv2 {cv2.__version__} "
@@ -367,8 +367,8 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
             "config": {"workload": (f"tracker front end: synthetic {w}x{h} BGR frames -> INTER_AREA to {scan[0]}x{scan[1]} -> detectFaces "
-                                    f"(skin mask), haarcascade_frontalface_{args.cascade}.xml, " if scan else
-                                    f"haarcascade_frontalface_{args.cascade}.xml on synthetic {w}x{h} gray frames, ")
+                                    f"(skin mask), {os.path.basename(cv2_ref.cascade_path(args.cascade))}, " if scan else
+                                    f"{os.path.basename(cv2_ref.cascade_path(args.cascade))} on synthetic {w}x{h} gray frames, ")
                                    + f"scale {sf}, minNeighbors 2, minSize {ms[0]}x{ms[1]}"
                                    + (" (BASELINE configs[0]/[1] frame+params)" if (w, h, sf, ms[0]) == (1280, 720, 1.1, 30) and not scan else ""),
                        "frames_per_step_per_gpu": nF, "launch_group": GROUP, "levels": plan_levels,

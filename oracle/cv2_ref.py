@@ -22,8 +22,15 @@ def cascade_dir() -> str:
 
 
 def cascade_path(name: str) -> str:
+    """"alt" -> haarcascade_frontalface_alt.xml (the reference's four); any other cv2 Haar cascade by its
+    short name ("smile", "upperbody", ...) or an explicit file path."""
     import os
-    return os.path.join(cascade_dir(), f"haarcascade_frontalface_{name}.xml")
+    if os.path.isfile(name):
+        return name
+    p = os.path.join(cascade_dir(), f"haarcascade_frontalface_{name}.xml")
+    if os.path.isfile(p):
+        return p
+    return os.path.join(cv2.data.haarcascades, f"haarcascade_{name}.xml")
 
 
 def load(path: str) -> "cv2.CascadeClassifier":
