@@ -266,6 +266,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
     b.stumps_only = c.max_tree_nodes == 1;
     b.fast_scan = scan_mode(c); b.word_off = scan_word_offsets(c) ? 1 : 0;
+    { static const int kmin = getenv("UGD_SCAN_KMIN") ? atoi(getenv("UGD_SCAN_KMIN")) : 2; b.scan_kmin = std::max(kmin, 1); }   // 2: measured optimum (1: -2 %, 3: -3 %, 4: -8 %)
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeC = d->nodeC.as<uint4>();
     b.nodeM = d->nodeM.as<uint32_t>();

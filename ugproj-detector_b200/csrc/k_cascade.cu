@@ -275,10 +275,7 @@ __device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* 
 }
 
 template <int K>
-__device__ __forceinline__ void tile_trees_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-    const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
-#pragma unroll
-    for (int k = 0; k < K; ++k) sum[k] = c_stage_base[s];
+__device__ __forceinline__ void tree_pairs(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
 #pragma unroll 1
     for (int n = n0; n < n1; n += 2) {
         const DNode& root = c_dn[n];
@@ -298,6 +295,13 @@ __device__ __forceinline__ void tile_trees_k(int s, int si, const char* const (&
             else if (lt_k) sum[k] += d_k;
         }
     }
+}
+
+template <int K>
+__device__ __forceinline__ void tile_trees_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) sum[k] = c_stage_base[s];
+    tree_pairs<K>(c_stage_first_node[s], c_stage_first_node[s + 1], si, t, vnf, sum);
 }
 
 template <int MODE, int K>
@@ -366,11 +370,42 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// ---- tile staging: asynchronous global -> shared copies (LDGSTS), 4 bytes per element because the source
+// index is clamped per element and the grid-step-2 layout de-interleaves even / odd columns ----
+__device__ __forceinline__ void cp_async4(int* dst, const int32_t* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_wait() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// Copies the patch of one integral plane under the tile whose first window is (xi0, r0) (grid units).
+__device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict__ plane, int P, int sw, int sh, int X0, int Y0,
+                                           int TR, int TC, int TP, int TCH, int si, int w, int lane) {
+    for (int r = w; r < TR; r += kScanWarps) {
+        const int32_t* src = plane + (size_t)min(Y0 + r, sh) * P;
+        int* dst = tile + r * TP;
+        for (int c = lane; c < TC; c += 32) cp_async4(dst + (si ? (c & 1) * TCH + (c >> 1) : c), src + min(X0 + c, sw));
+    }
+}
+
+// Windows per lane that share a node fetch in the exact evaluators, and resident blocks per SM the register
+// budget is cut for.  Measured on B200 (alt, 720p, ms per 64 frames): K=4 / 4 blocks (64 regs) 10.7, K=4 / 5 blocks 11.2,
+// K=3 / 5 blocks 11.8, K=2 / 5 blocks 10.2, K=2 / 6 blocks (40 regs) 9.9, K=2 / 8 blocks (32 regs, spills) 10.8,
+// K=1 / 6 blocks 11.3: two windows per fetch already buy most of the amortisation (24.5 vs 22 instructions per
+// window and node), and the 12 extra warps per SM fill the issue slots the stage barriers leave empty.
+#ifndef UGD_SCAN_KMAX
+#define UGD_SCAN_KMAX 2
+#endif
+#ifndef UGD_SCAN_MINBLOCKS
+#define UGD_SCAN_MINBLOCKS 6
+#endif
+
 template <int MODE, bool WORDS>
-__global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 32) : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk) {
-    constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols;
+__global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
+    constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols, KMAX = UGD_SCAN_KMAX;
     static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
-    extern __shared__ int s_tile[];
+    extern __shared__ int s_tiles[];
     __shared__ float s_vnf[R * C];
     __shared__ unsigned s_alive[3][32];                // rotating survivor masks, one word per bank class
     __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
@@ -400,24 +435,30 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
     const int nw0 = c_stage_first_node[1] - c_stage_first_node[0];
     const float thr0 = c_stage_thr[0];
 
+    // The tile buffer is double (dbl = 1) when shared memory allows: the next tile's patch is then copied
+    // asynchronously while this tile is being evaluated, and its latency disappears behind the stages.
+    const int planes = b.T ? 2 : 1, buf_ints = planes * TR * TP;
+    const int32_t* Tp = b.T ? b.T + (size_t)frame * b.int_stride + Lg.int_off : nullptr;
+    int* s_tile = s_tiles;
+    if (dbl) {
+        stage_tile(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        if (Tp) stage_tile(s_tile + TR * TP, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
+    }
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96; i += NW * 32) (&s_alive[0][0])[i] = 0;
-        // ---- 1. stage the S tile (and, for cascades with tilted features, the T tile behind it) ----
-        for (int pl = 0; pl < (b.T ? 2 : 1); ++pl) {
-            const int32_t* plane = pl ? b.T + (size_t)frame * b.int_stride + Lg.int_off : S;
-            int* tile = s_tile + pl * TR * TP;
-            const int X0 = xi0 * step, Y0 = r0 * step;
-            for (int r = w; r < TR; r += NW) {
-                const int32_t* src = plane + (size_t)min(Y0 + r, sh) * P;
-                int* dst = tile + r * TP;
-                for (int c = lane; c < TC; c += 32) {
-                    const int v = src[min(X0 + c, sw)];
-                    dst[si ? (c & 1) * TCH + (c >> 1) : c] = v;
-                }
-            }
+        // ---- 1. the S tile (and, for cascades with tilted features, the T tile behind it) ----
+        if (!dbl) {
+            stage_tile(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            if (Tp) stage_tile(s_tile + TR * TP, Tp, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
         }
+        cp_async_commit_wait();
         __syncthreads();
+        if (dbl && xi0 + C < nxg) {                    // prefetch the next tile into the other buffer
+            int* nxt = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
+            stage_tile(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            if (Tp) stage_tile(nxt + TR * TP, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        }
         // ---- 2. variance normalisation + stage 0 + x-skip, row segment by row segment ----
 #pragma unroll 1
         for (int seg = 0; seg < (R / NW) * (C / 32); ++seg) {
@@ -507,17 +548,18 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
             const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
             if (MODE) {
-                // exact evaluators: the rounds are dealt evenly to the warps (warp w takes rounds
-                // [w*rounds/NW, (w+1)*rounds/NW)), up to 4 consecutive rounds at once: the windows a lane
-                // holds share every node fetch
+                // exact evaluators: the rounds are dealt to the warps in runs of `per` (at least scan_kmin, so that
+                // late stages with fewer rounds than warps still pair windows up), KMAX consecutive rounds at
+                // once: the windows a lane holds share every node fetch
                 unsigned mm = m;
-                const int g_end = ((w + 1) * rounds) / NW;
-                for (int i = 0; i < (w * rounds) / NW; ++i) mm &= mm - 1;
-                for (int g = (w * rounds) / NW; g < g_end; g += 4) {
-                    const int K = min(4, g_end - g);
+                const int per = max((rounds + NW - 1) / NW, b.scan_kmin);
+                const int g_beg = min(w * per, rounds), g_end = min(g_beg + per, rounds);
+                for (int i = 0; i < g_beg; ++i) mm &= mm - 1;
+                for (int g = g_beg; g < g_end; g += KMAX) {
+                    const int K = min(KMAX, g_end - g);
                     int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < KMAX; ++k) {
                         act[k] = mm != 0;
                         bit[k] = act[k] ? __ffs((int)mm) - 1 : 0;
                         mm &= mm - 1;
@@ -525,24 +567,24 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                         tw[k] = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
                         vn[k] = s_vnf[rl * C + c];
                     }
-                    if (K == 1) {
+                    if (K == 1 || KMAX == 1) {
                         const char* t1[1] = {tw[0]}; float v1[1] = {vn[0]}; double s1[1];
                         stage_eval<MODE, 1>(s, si, t1, v1, s1);
-                        sum[0] = s1[0]; sum[1] = sum[2] = sum[3] = 0.0;
-                    } else if (K == 2) {
+                        sum[0] = s1[0];
+                    } else if (K == 2 || KMAX == 2) {
                         const char* t2[2] = {tw[0], tw[1]}; float v2[2] = {vn[0], vn[1]}; double s2[2];
                         stage_eval<MODE, 2>(s, si, t2, v2, s2);
-                        sum[0] = s2[0]; sum[1] = s2[1]; sum[2] = sum[3] = 0.0;
-                    } else if (K == 3) {
+                        sum[0] = s2[0]; sum[1] = s2[1];
+                    } else if (K == 3 || KMAX == 3) {
                         const char* t3[3] = {tw[0], tw[1], tw[2]}; float v3[3] = {vn[0], vn[1], vn[2]}; double s3[3];
                         stage_eval<MODE, 3>(s, si, t3, v3, s3);
-                        sum[0] = s3[0]; sum[1] = s3[1]; sum[2] = s3[2]; sum[3] = 0.0;
+                        sum[0] = s3[0]; sum[1] = s3[1]; sum[2] = s3[2];
                     } else {
                         stage_eval<MODE, 4>(s, si, tw, vn, sum);
                     }
                     unsigned passbits = 0;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < KMAX; ++k) {
                         if (k < K) {                    // warp-uniform
                             bool pass = act[k] && !(sum[k] < (double)thr);
                             const unsigned am = __ballot_sync(0xffffffffu, act[k]);
@@ -676,6 +718,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
                 }
             }
         }
+        if (dbl) s_tile = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
     }
     if (lane == 0 && weak) atomicAdd(&s_ctr[3], weak);
     __syncthreads();
@@ -687,6 +730,15 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? 1024 / (kScanWarps * 3
 
 static int g_scan_smem = 0;
 
+// Shared memory of one launch: the tile (x2 planes for tilted cascades), doubled when two buffers still leave
+// room for six blocks per SM next to the static arrays (the asynchronous prefetch of the next tile).
+static size_t scan_smem_bytes(const ScanGeom& g, int si, bool tilted, int* dbl) {
+    const size_t one = (size_t)g.TR[si] * g.TP[si] * sizeof(int) * (tilted ? 2 : 1);
+    *dbl = 2 * one + 7 * 1024 <= 37 * 1024 ? 1 : 0;          // 6 blocks x 37 KB < 228 KB
+    if (getenv("UGD_SCAN_SINGLE")) *dbl = 0;
+    return one * (*dbl ? 2 : 1);
+}
+
 // The work table is ordered by level and the grid-step-2 levels (scale < 2) come first, so the launch is
 // split in two: each half asks only for the shared memory its own tile layout needs.
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
@@ -695,22 +747,25 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
     for (int half = 0; half < 2; ++half) {
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
-        const size_t smem = (size_t)g.TR[half ? 0 : 1] * g.TP[half ? 0 : 1] * sizeof(int) * (b.T ? 2 : 1);
+        int dbl = 0;
+        const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
         const dim3 grid(n, b.nframes);
         const int variant = b.fast_scan * 2 + (b.word_off ? 1 : 0);
         switch (variant) {
-            case 0: k_scan<0, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
-            case 1: k_scan<0, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
-            case 2: k_scan<1, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
-            case 3: k_scan<1, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
-            case 4: k_scan<2, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
-            default: k_scan<2, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first); break;
+            case 0: k_scan<0, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 1: k_scan<0, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 2: k_scan<1, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 3: k_scan<1, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 4: k_scan<2, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            default: k_scan<2, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
         }
     }
 }
 
 cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted) {
-    const int scan_smem = make_scan_geom(win_w, win_h).tile_ints * (int)sizeof(int) * (has_tilted ? 2 : 1);
+    const ScanGeom g = make_scan_geom(win_w, win_h);
+    int dbl;
+    const int scan_smem = (int)std::max(scan_smem_bytes(g, 0, has_tilted, &dbl), scan_smem_bytes(g, 1, has_tilted, &dbl));
     if (scan_smem > g_scan_smem) {
         const void* variants[6] = {(const void*)k_scan<0, false>, (const void*)k_scan<0, true>, (const void*)k_scan<1, false>,
                                    (const void*)k_scan<1, true>, (const void*)k_scan<2, false>, (const void*)k_scan<2, true>};

@@ -75,6 +75,7 @@ struct DevBufs {
     uint32_t* carryS; uint32_t* carryQ; size_t carry_stride;
     // window scan
     size_t pos_stride;                                // padded grid positions per frame
+    int scan_kmin;                                    // a warp takes at least this many rounds of a stage at once (they share the node fetches)
     int tile_min;                                     // hand a tile's survivors to the per-warp evaluator once fewer than this remain
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
     int16_t* stage_map;                               // frame 0 only, padded layout; may be null
