@@ -185,8 +185,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"               # keep stdout to the one JSON line
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"               # keep stdout to the one JSON line (an nccl.conf may ask for VERSION)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ug = ge.load_package()
