@@ -207,7 +207,7 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
     CK(d->rawsum.reserve(F * d->rawcap * sizeof(double)));
     CK(d->rawcount.reserve(F * 4));
-    CK(d->grp.reserve(F * 10 * (size_t)d->rawcap * 4));
+    CK(d->grp.reserve(F * 11 * (size_t)d->rawcap * 4));
     CK(d->out.reserve(F * (size_t)outcap * sizeof(ugd_rect)));
     CK(d->outcount.reserve(F * 4));
     CK(d->counters.reserve(F * kCtrPerFrame * 8));
@@ -293,7 +293,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.tile_min = d->tile_min;
     b.raw = d->raw.as<ugd_rect>(); b.rawsum = d->rawsum.as<double>(); b.rawcap = d->rawcap; b.rawcount = d->rawcount.as<int>();
     b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
-    b.grp_scratch = d->grp.as<int>(); b.grp_stride = 10 * (size_t)d->rawcap;
+    b.grp_scratch = d->grp.as<int>(); b.grp_stride = 11 * (size_t)d->rawcap;
     b.out = d->out.as<ugd_rect>(); b.outcap = cap; b.outcount = d->outcount.as<int>();
     b.min_neighbors = d->prm.min_neighbors;
     b.counters = d->counters.as<unsigned long long>();

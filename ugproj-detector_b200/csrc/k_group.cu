@@ -51,8 +51,14 @@ __global__ void __launch_bounds__(kLinkI) k_group_link(DevBufs b) {
     const int j0 = max(blockIdx.y * chunk, blockIdx.x * kLinkI + 1), j1 = min((blockIdx.y + 1) * chunk, n);
     if (i >= n) return;
     const ugd_rect ri = raw[i];
+    // integer pre-filter: SimilarRects needs |dx|, |dy| <= 0.1 * (min widths + min heights) <= 0.1 * (w_i + h_i), so a
+    // pair with 10 * |dx| > w_i + h_i can never be similar (exact superset; the fp64 test decides the rest)
+    const int lim = ri.width + ri.height;
     for (int j = max(j0, i + 1); j < j1; ++j) {
-        if (!similar_rects(ri, raw[j])) continue;
+        const int4 q = __ldg(reinterpret_cast<const int4*>(raw + j));
+        if (abs(ri.x - q.x) * 10 > lim || abs(ri.y - q.y) * 10 > lim) continue;
+        ugd_rect rj; rj.x = q.x; rj.y = q.y; rj.width = q.z; rj.height = q.w;
+        if (!similar_rects(ri, rj)) continue;
         int a = i, c = j;
         for (;;) {                                           // unite: the larger root is hung under the smaller one
             a = uf_find(parent, a); c = uf_find(parent, c);
@@ -64,7 +70,7 @@ __global__ void __launch_bounds__(kLinkI) k_group_link(DevBufs b) {
 }
 
 __global__ void __launch_bounds__(256) k_group(DevBufs b) {
-    __shared__ int s_nkept, s_nfinal;
+    __shared__ int s_nkept, s_nfinal, s_ncls;
     __shared__ unsigned long long s_red[8];
     const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = b.rawcount[frame];
@@ -76,9 +82,10 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
     int* acc = scratch + b.rawcap;           // [rawcap][4] class sums -> class mean rect
     int* cnt = scratch + 5 * b.rawcap;       // [rawcap]
     ugd_rect* kept = reinterpret_cast<ugd_rect*>(scratch + 6 * b.rawcap);   // [rawcap]
+    int* clist = scratch + 10 * b.rawcap;    // [rawcap] roots of the classes with more than g members
     const int g = b.min_neighbors;
     if (tid == 0) {
-        s_nkept = 0; s_nfinal = 0;
+        s_nkept = 0; s_nfinal = 0; s_ncls = 0;
         ctr[CTR_RAW] = (unsigned long long)total;
         if (total > b.rawcap) ctr[CTR_RAW_OVERFLOW] = 1ull;
     }
@@ -116,17 +123,22 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
             for (int k = 0; k < 4; ++k) acc[4 * i + k] = __float2int_rn(__fmul_rn((float)acc[4 * i + k], s));
         }
         __syncthreads();
-        // ---- keep classes with more than g members that are not nested in a stronger class ----
-        for (int i = tid; i < n; i += 256) {
-            if (label[i] != i) continue;
+        // ---- keep classes with more than g members that are not nested in a stronger class.  The classes that
+        //      qualify are first gathered into a list, so the all-pairs test runs over them and not over every
+        //      candidate (thousands of candidates give a few hundred classes) ----
+        for (int i = tid; i < n; i += 256)
+            if (label[i] == i && cnt[i] > g) clist[atomicAdd(&s_ncls, 1)] = i;
+        __syncthreads();
+        const int nc = s_ncls;
+        for (int a = tid; a < nc; a += 256) {
+            const int i = clist[a];
             const int n1 = cnt[i];
-            if (n1 <= g) continue;
             const int x1 = acc[4 * i], y1 = acc[4 * i + 1], w1 = acc[4 * i + 2], h1 = acc[4 * i + 3];
             bool drop = false;
-            for (int j = 0; j < n && !drop; ++j) {
-                if (j == i || label[j] != j) continue;
+            for (int c = 0; c < nc && !drop; ++c) {
+                const int j = clist[c];
+                if (j == i) continue;
                 const int n2 = cnt[j];
-                if (n2 <= g) continue;
                 const int x2 = acc[4 * j], y2 = acc[4 * j + 1], w2 = acc[4 * j + 2], h2 = acc[4 * j + 3];
                 const int dx = __double2int_rn(__dmul_rn((double)w2, 0.2)), dy = __double2int_rn(__dmul_rn((double)h2, 0.2));
                 if (x1 >= x2 - dx && y1 >= y2 - dy && x1 + w1 <= x2 + w2 + dx && y1 + h1 <= y2 + h2 + dy &&

@@ -80,7 +80,7 @@ struct DevBufs {
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
     int16_t* stage_map;                               // frame 0 only, padded layout; may be null
     // grouping / output
-    int* grp_scratch; size_t grp_stride;              // per frame: 6*rawcap ints
+    int* grp_scratch; size_t grp_stride;              // per frame: 11*rawcap ints (labels, class sums, counts, kept rects, class list)
     ugd_rect* out; int outcap; int* outcount;
     int min_neighbors;
     unsigned long long* counters;                     // [nframes][kCtrPerFrame]
