@@ -132,7 +132,7 @@ int upload_cascade(ugd_detector* d) {
         for (int s = 0; s < c.nstages(); ++s)
             std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
-    const ScanGeom geom = make_scan_geom(c.win_w, c.win_h);
+    const ScanGeom geom = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
     const bool words = scan_word_offsets(c);
     std::vector<uint4> B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
     for (int si = 0; si < 2; ++si) { TA[si].resize(c.nnodes()); TB[si].resize(c.nnodes()); }

@@ -46,11 +46,21 @@ __constant__ ScanGeom c_geom;
 // of surviving windows over many classes (tools/sim_compaction3.py).
 static bool good_shift(int sh) { return sh == 8 || sh == 12 || sh == 20 || sh == 24; }
 
-ScanGeom make_scan_geom(int win_w, int win_h) {
+// Tile width in windows.  Grid-step-1 levels get 128-column tiles (64 windows per bank class instead of 32: the
+// per-class survivor counts even out, tools/sim_stage_util.py) when the wider S tile still leaves room for six
+// blocks per SM; grid-step-2 tiles (twice the pixels per window) and two-plane tiles (tilted cascades) stay at 64.
+static int tile_cols(int si, int win_w, int win_h, bool tilted) {
+    if (si != 0 || tilted || getenv("UGD_SCAN_NARROW")) return kTileCols;
+    const int tc = (2 * kTileCols - 1) + win_w + 1, tr = (kTileRows - 1) + win_h + 1;
+    return (tc + 7) * tr * 4 <= 25 * 1024 ? 2 * kTileCols : kTileCols;
+}
+
+ScanGeom make_scan_geom(int win_w, int win_h, bool tilted) {
     ScanGeom g{};
     for (int si = 0; si < 2; ++si) {
         const int step = si + 1;
-        g.TC[si] = (kTileCols - 1) * step + win_w + 1;
+        g.cols[si] = tile_cols(si, win_w, win_h, tilted);
+        g.TC[si] = (g.cols[si] - 1) * step + win_w + 1;
         g.TR[si] = (kTileRows - 1) * step + win_h + 1;
         if (si == 0) {
             int tp = g.TC[0];
@@ -76,7 +86,7 @@ int32_t scan_plane_bytes(const ScanGeom& g, int si) { return 4 * g.TR[si] * g.TP
 // 16-bit byte addresses cover the static shared arrays plus one tile of a small window; anything larger
 // (two tiles for tilted cascades, wide windows) switches the per-lane tables to word offsets.
 bool scan_word_offsets(const Cascade& c) {
-    const ScanGeom g = make_scan_geom(c.win_w, c.win_h);
+    const ScanGeom g = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
     return c.has_tilted || g.tile_ints * 4 > 48 * 1024;
 }
 
@@ -98,7 +108,7 @@ int scan_mode(const Cascade& c) {
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
     const int nn = c.stage_first_node[dense_stages];
     if (nn > kMaxDenseNodes || dense_stages > kMaxDenseStages) return cudaErrorInvalidValue;
-    ScanGeom g = make_scan_geom(c.win_w, c.win_h);
+    ScanGeom g = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
     for (int si = 0; si < 2; ++si) {
         g.norm_off[si][0] = tile_off(g, si, 1, 1);
         g.norm_off[si][1] = tile_off(g, si, c.win_w - 1, 1);
@@ -124,7 +134,7 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
                      (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
             d.thr = h.thr;
-            if (mode == 1) d.delta = (double)h.left_val - (double)h.right_val;
+            if (mode == 1) d.delta = ((double)h.left_val - (double)h.right_val) * 128.0;   // see add_if_lt
             else if (mode == 2) {
                 // tree value = cr + [root takes its leaf](root leaf - cr) + [root takes the child and child goes left](cl - cr)
                 const HostNode& kid = c.nodes[base + 1];
@@ -216,26 +226,43 @@ __device__ __forceinline__ double tile_stage_generic(int s, int si, const char* 
 // Exact stump evaluator for K windows per lane (the same node is applied to the K windows, so its
 // constant-bank fetches are paid once per K feature evaluations).  Nodes of a stage are sorted by corner
 // count at upload time (sums are exact, hence order-independent), so NC is a compile-time constant.
+// sum += delta where val < thr, in two instructions: FSET.BF writes 1.0f / 0.0f, and those bits read as the HIGH word
+// of a double (low word 0) are 2^-7 / 0.0, so one DFMA with delta * 128 (stored that way at upload, exact) adds
+// delta or nothing -- rounded once, exactly like the DADD it replaces (the compiler's own choice for the
+// conditional add is DADD + two FSEL behind an FSETP).
+__device__ __forceinline__ void add_if_lt(double& sum, float val, float thr, double delta128) {
+    asm("{\n\t.reg .f32 m;\n\t.reg .b32 z;\n\t.reg .f64 md;\n\tset.lt.f32.f32 m, %1, %2;\n\tmov.b32 z, 0;\n\t"
+        "mov.b64 md, {z, m};\n\tfma.rn.f64 %0, md, %3, %0;\n\t}" : "+d"(sum) : "f"(val), "f"(thr), "d"(delta128));
+}
+
 template <int NC, int K>
 __device__ __forceinline__ void stage_nodes(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
 #pragma unroll 1
     for (int n = n0; n < n1; ++n) {
         const DNode& d = c_dn[n];
-        const int32_t* o = d.off[si];
+        // 16-byte fetches (LDCU.128): four offsets / four coefficients / {thr, meta, delta} per instruction
+        const int4* o4 = reinterpret_cast<const int4*>(d.off[si]);
+        const int4* c4 = reinterpret_cast<const int4*>(d.coef);
+        int o[12], cf[12];
+#pragma unroll
+        for (int q = 0; q < (NC + 3) / 4; ++q) {
+            const int4 ov = o4[q], cv = c4[q];
+            o[4 * q] = ov.x; o[4 * q + 1] = ov.y; o[4 * q + 2] = ov.z; o[4 * q + 3] = ov.w;
+            cf[4 * q] = cv.x; cf[4 * q + 1] = cv.y; cf[4 * q + 2] = cv.z; cf[4 * q + 3] = cv.w;
+        }
         int acc[K];
 #pragma unroll
         for (int k = 0; k < K; ++k) acc[k] = 0;
 #pragma unroll
         for (int j = 0; j < NC; ++j) {                  // corner by corner: offset and coefficient fetched once for the K windows
-            const int oj = o[j], cj = d.coef[j];
 #pragma unroll
-            for (int k = 0; k < K; ++k) acc[k] += cj * *reinterpret_cast<const int*>(t[k] + oj);
+            for (int k = 0; k < K; ++k) acc[k] += cf[j] * *reinterpret_cast<const int*>(t[k] + o[j]);
         }
-        const float thr = d.thr;
-        const double delta = d.delta;
+        const int4 tail = *reinterpret_cast<const int4*>(&d.thr);
+        const float thr = __int_as_float(tail.x);
+        const double delta = __hiloint2double(tail.w, tail.z);
 #pragma unroll
-        for (int k = 0; k < K; ++k)
-            if (__fmul_rn(__int2float_rn(acc[k]), vnf[k]) < thr) sum[k] += delta;
+        for (int k = 0; k < K; ++k) add_if_lt(sum[k], __fmul_rn(__int2float_rn(acc[k]), vnf[k]), thr, delta);
     }
 }
 
@@ -401,13 +428,43 @@ __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict_
 #define UGD_SCAN_MINBLOCKS 6
 #endif
 
-template <int MODE, bool WORDS>
+// The survivors of one bank class: bit rl * (C / 32) + h of the mask is the window in tile row rl, column segment h
+// (32 bits for 64-column tiles, 64 bits as two words for 128-column tiles).
+template <int NMW>
+struct Live {
+    unsigned w[NMW];
+    __device__ __forceinline__ int count() const { return NMW == 1 ? __popc(w[0]) : __popc(w[0]) + __popc(w[1]); }
+    __device__ __forceinline__ bool any() const { return NMW == 1 ? w[0] != 0 : (w[0] | w[1]) != 0; }
+    __device__ __forceinline__ void skip(int n) {      // drop the n lowest live windows
+        if (NMW == 2) {
+            const int p = __popc(w[0]);
+            const bool over = n >= p;
+            unsigned v = over ? w[1] : w[0];
+            for (int i = over ? n - p : n; i > 0 && v; --i) v &= v - 1;
+            if (over) { w[0] = 0; w[1] = v; } else w[0] = v;
+        } else {
+            for (int i = 0; i < n; ++i) w[0] &= w[0] - 1;
+        }
+    }
+    __device__ __forceinline__ bool pop(int& bit) {    // take the lowest live window; bit = 0 when none is left
+        const bool lo = NMW == 1 || w[0] != 0;
+        unsigned v = lo ? w[0] : w[NMW - 1];
+        const bool act = v != 0;
+        bit = act ? __ffs((int)v) - 1 + (lo ? 0 : 32) : 0;
+        v &= v - 1;
+        if (lo) w[0] = v; else w[NMW - 1] = v;
+        return act;
+    }
+};
+
+template <int MODE, bool WORDS, int C>
 __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
-    constexpr int NW = kScanWarps, R = kTileRows, C = kTileCols, KMAX = UGD_SCAN_KMAX;
-    static_assert(R * C == 32 * 32 && C == 64, "one 32-bit survivor mask per bank class");
+    constexpr int NW = kScanWarps, R = kTileRows, KMAX = UGD_SCAN_KMAX;
+    constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
+    static_assert((C == 64 || C == 128) && R == 16 && R % NW == 0, "32 or 64 windows per bank class");
     extern __shared__ int s_tiles[];
     __shared__ float s_vnf[R * C];
-    __shared__ unsigned s_alive[3][32];                // rotating survivor masks, one word per bank class
+    __shared__ unsigned s_alive[3][NMW][32];           // rotating survivor masks, NMW words per bank class
     __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
     __shared__ int s_pop;
     __shared__ unsigned int s_ctr[5];                  // evaluated, lowvar, near, weak, queued
@@ -446,7 +503,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
     }
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
-        for (int i = tid; i < 96; i += NW * 32) (&s_alive[0][0])[i] = 0;
+        for (int i = tid; i < 96 * NMW; i += NW * 32) (&s_alive[0][0][0])[i] = 0;
         // ---- 1. the S tile (and, for cascades with tilted features, the T tile behind it) ----
         if (!dbl) {
             stage_tile(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
@@ -461,8 +518,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
         }
         // ---- 2. variance normalisation + stage 0 + x-skip, row segment by row segment ----
 #pragma unroll 1
-        for (int seg = 0; seg < (R / NW) * (C / 32); ++seg) {
-            const int k = seg >> 1, h = seg & 1;
+        for (int seg = 0; seg < (R / NW) * SEG; ++seg) {
+            const int k = seg >> LSEG, h = seg & (SEG - 1);
             const int rl = w + k * NW, row = r0 + rl;
             const bool row_valid = row < nyg;
             {
@@ -528,7 +585,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                         emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
                         if (map) map[row * nxg_pad + xi] = 1;
                     } else {
-                        atomicOr(&s_alive[0][(c + SH * rl) & 31], 1u << (rl * (C / 32) + h));
+                        atomicOr(&s_alive[0][(rl * SEG + h) >> 5][(c + SH * rl) & 31], 1u << ((rl * SEG + h) & 31));
                     }
                 }
             }
@@ -536,34 +593,35 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
         __syncthreads();
         // ---- 3. stage by stage on the per-class survivor masks ----
         int cur = 0, s = 1, total;
-        unsigned m;
+        Live<NMW> m;
         for (;;) {
-            m = s_alive[cur][lane];
-            const int cnt = __popc(m);
+#pragma unroll
+            for (int i = 0; i < NMW; ++i) m.w[i] = s_alive[cur][i][lane];
+            const int cnt = m.count();
             total = __reduce_add_sync(0xffffffffu, cnt);
             if (s >= D || total == 0 || (total < b.tile_min && s >= 2)) break;   // block-uniform
             const int rounds = __reduce_max_sync(0xffffffffu, cnt);
             const int nxt = cur == 2 ? 0 : cur + 1, nxt2 = nxt == 2 ? 0 : nxt + 1;
-            if (w == 0) s_alive[nxt2][lane] = 0;        // masks of the stage before: nobody reads them any more
+            if (w == 0)                                 // masks of the stage before: nobody reads them any more
+#pragma unroll
+                for (int i = 0; i < NMW; ++i) s_alive[nxt2][i][lane] = 0;
             const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
             if (MODE) {
                 // exact evaluators: the rounds are dealt to the warps in runs of `per` (at least scan_kmin, so that
                 // late stages with fewer rounds than warps still pair windows up), KMAX consecutive rounds at
                 // once: the windows a lane holds share every node fetch
-                unsigned mm = m;
+                Live<NMW> mm = m;
                 const int per = max((rounds + NW - 1) / NW, b.scan_kmin);
                 const int g_beg = min(w * per, rounds), g_end = min(g_beg + per, rounds);
-                for (int i = 0; i < g_beg; ++i) mm &= mm - 1;
+                mm.skip(g_beg);
                 for (int g = g_beg; g < g_end; g += KMAX) {
                     const int K = min(KMAX, g_end - g);
                     int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
 #pragma unroll
                     for (int k = 0; k < KMAX; ++k) {
-                        act[k] = mm != 0;
-                        bit[k] = act[k] ? __ffs((int)mm) - 1 : 0;
-                        mm &= mm - 1;
-                        const int rl = bit[k] >> 1, c = ((lane - SH * rl) & 31) + ((bit[k] & 1) << 5);
+                        act[k] = mm.pop(bit[k]);
+                        const int rl = bit[k] >> LSEG, c = ((lane - SH * rl) & 31) + ((bit[k] & (SEG - 1)) << 5);
                         tw[k] = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
                         vn[k] = s_vnf[rl * C + c];
                     }
@@ -582,7 +640,9 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                     } else {
                         stage_eval<MODE, 4>(s, si, tw, vn, sum);
                     }
-                    unsigned passbits = 0;
+                    unsigned passbits[NMW];
+#pragma unroll
+                    for (int i = 0; i < NMW; ++i) passbits[i] = 0;
 #pragma unroll
                     for (int k = 0; k < KMAX; ++k) {
                         if (k < K) {                    // warp-uniform
@@ -593,7 +653,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                                 weak += (unsigned)__popc(am) * (unsigned)nws;
                                 if (nm) atomicAdd(&s_ctr[2], __popc(nm));
                             }
-                            const int rl = bit[k] >> 1, c = ((lane - SH * rl) & 31) + ((bit[k] & 1) << 5);
+                            const int rl = bit[k] >> LSEG, c = ((lane - SH * rl) & 31) + ((bit[k] & (SEG - 1)) << 5);
                             const int mpos = (r0 + rl) * nxg_pad + xi0 + c;
                             if (act[k] && !pass && map) map[mpos] = (int16_t)s;
                             if (pass && s + 1 == nstages) {
@@ -601,18 +661,23 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                                 if (map) map[mpos] = (int16_t)nstages;
                                 pass = false;           // accepted: nothing left to do for it
                             }
-                            if (pass) passbits |= 1u << bit[k];
+                            if (pass) {
+                                if (NMW == 1 || bit[k] < 32) passbits[0] |= 1u << bit[k];
+                                else passbits[NMW - 1] |= 1u << (bit[k] - 32);
+                            }
                         }
                     }
-                    if (passbits) atomicOr(&s_alive[nxt][lane], passbits);
+#pragma unroll
+                    for (int i = 0; i < NMW; ++i)
+                        if (passbits[i]) atomicOr(&s_alive[nxt][i][lane], passbits[i]);
                 }
             } else {
-            unsigned mm = m;
-            for (int i = 0; i < w; ++i) mm &= mm - 1;   // this warp takes rounds w, w+8, ...
+            Live<NMW> mm = m;
+            mm.skip(w);                                 // this warp takes rounds w, w+8, ...
             for (int j = w; j < rounds; j += NW) {
-                const bool act = mm != 0;
-                const int bit = act ? __ffs((int)mm) - 1 : 0;
-                const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
+                int bit;
+                const bool act = mm.pop(bit);
+                const int rl = bit >> LSEG, c = ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
                 const char* tw = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
                 const double sum = tile_stage_generic(s, si, tw, s_vnf[rl * C + c]);
                 bool pass = act && !(sum < (double)thr);
@@ -629,9 +694,8 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                     if (map) map[mpos] = (int16_t)nstages;
                     pass = false;                       // accepted: nothing left to do for it
                 }
-                if (pass) atomicOr(&s_alive[nxt][lane], 1u << bit);
-#pragma unroll
-                for (int i = 0; i < NW; ++i) mm &= mm - 1;
+                if (pass) atomicOr(&s_alive[nxt][bit >> 5][lane], 1u << (bit & 31));
+                mm.skip(NW - 1);
             }
             }
             __syncthreads();
@@ -641,7 +705,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
         //         time, the 32 lanes evaluate 32 weak classifiers of a stage against the tile in shared memory ----
         if (total > 0 && s < nstages) {
             if (w == 0) {
-                const int cnt = __popc(m);
+                const int cnt = m.count();
                 int incl = cnt;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
@@ -649,9 +713,10 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                     if (lane >= d) incl += v;
                 }
                 int pos = incl - cnt;
-                for (unsigned mm = m; mm; mm &= mm - 1) {
-                    const int bit = __ffs((int)mm) - 1;
-                    const int rl = bit >> 1, c = ((lane - SH * rl) & 31) + ((bit & 1) << 5);
+                Live<NMW> mm = m;
+                int bit;
+                while (mm.pop(bit)) {
+                    const int rl = bit >> LSEG, c = ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
                     s_list[pos++] = (uint16_t)(rl * C + c);
                 }
                 if (lane == 0) { s_pop = 0; s_ctr[4] += (unsigned)total; }
@@ -664,7 +729,7 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
                 if (lane == 0) i = atomicAdd(&s_pop, 1);
                 i = __shfl_sync(0xffffffffu, i, 0);
                 if (i >= total) break;
-                const int id = s_list[i], rl = id >> 6, c = id & (C - 1);
+                const int id = s_list[i], rl = id / C, c = id & (C - 1);
                 const float vnf = s_vnf[id];
                 const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + (rl * step) * TP + c);
                 const uint32_t pw = WORDS ? pbase >> 2 : pbase;
@@ -743,32 +808,37 @@ static size_t scan_smem_bytes(const ScanGeom& g, int si, bool tilted, int* dbl) 
 // split in two: each half asks only for the shared memory its own tile layout needs.
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
     if (!nblocks) return;
-    const ScanGeom g = make_scan_geom(b.win_w, b.win_h);
+    const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr);
     for (int half = 0; half < 2; ++half) {
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
         int dbl = 0;
         const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
         const dim3 grid(n, b.nframes);
-        const int variant = b.fast_scan * 2 + (b.word_off ? 1 : 0);
+        const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
+        const int variant = wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
         switch (variant) {
-            case 0: k_scan<0, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 1: k_scan<0, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 2: k_scan<1, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 3: k_scan<1, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 4: k_scan<2, false><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            default: k_scan<2, true><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
         }
     }
 }
 
 cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted) {
-    const ScanGeom g = make_scan_geom(win_w, win_h);
+    const ScanGeom g = make_scan_geom(win_w, win_h, has_tilted);
     int dbl;
     const int scan_smem = (int)std::max(scan_smem_bytes(g, 0, has_tilted, &dbl), scan_smem_bytes(g, 1, has_tilted, &dbl));
     if (scan_smem > g_scan_smem) {
-        const void* variants[6] = {(const void*)k_scan<0, false>, (const void*)k_scan<0, true>, (const void*)k_scan<1, false>,
-                                   (const void*)k_scan<1, true>, (const void*)k_scan<2, false>, (const void*)k_scan<2, true>};
+        const void* variants[9] = {(const void*)k_scan<0, false, 64>, (const void*)k_scan<0, true, 64>, (const void*)k_scan<1, false, 64>,
+                                   (const void*)k_scan<1, true, 64>, (const void*)k_scan<2, false, 64>, (const void*)k_scan<2, true, 64>,
+                                   (const void*)k_scan<0, false, 128>, (const void*)k_scan<1, false, 128>, (const void*)k_scan<2, false, 128>};
         for (const void* f : variants) {
             cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
             if (e != cudaSuccess) return e;

@@ -26,15 +26,16 @@ struct alignas(16) DNode {
     uint32_t meta;                        // nc | lnode << 8 | rnode << 16 | last << 24
     union {
         struct { float lval, rval; };     // generic evaluator: the two leaves
-        double delta;                     // exact stump evaluator: (double)left - (double)right
+        double delta;                     // exact evaluators: leaf difference (stumps: times 128, see add_if_lt)
     };
 };
 static_assert(sizeof(DNode) == 160, "DNode layout");
 
 constexpr int kTileRows = 16;             // scan tile: kTileRows x kTileCols windows = 32 per bank class
-constexpr int kTileCols = 64;
+constexpr int kTileCols = 64;             // (grid-step-1 levels: 128 columns, 64 per class, when shared memory allows)
 constexpr int kScanWarps = 8;              // warps per scan block
 struct ScanGeom {                          // per layout (step 1 / step 2)
+    int cols[2];                           // tile width in windows (kTileCols, or twice that: see tile_cols)
     int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
     int SH[2];                             // bank shift between consecutive window rows: (step * TP) mod 32
     int32_t norm_off[2][4];                // tile BYTE offsets of the 4 variance-normalisation corners
@@ -88,7 +89,7 @@ struct DevBufs {
 
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
-ScanGeom make_scan_geom(int win_w, int win_h);
+ScanGeom make_scan_geom(int win_w, int win_h, bool tilted);
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
 bool scan_word_offsets(const Cascade& c);                         // per-lane tables in words instead of bytes
