@@ -407,9 +407,10 @@ __device__ __forceinline__ void cp_async_commit_wait() {
 }
 
 // Copies the patch of one integral plane under the tile whose first window is (xi0, r0) (grid units).
+template <int NW>
 __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict__ plane, int P, int sw, int sh, int X0, int Y0,
                                            int TR, int TC, int TP, int TCH, int si, int w, int lane) {
-    for (int r = w; r < TR; r += kScanWarps) {
+    for (int r = w; r < TR; r += NW) {
         const int32_t* src = plane + (size_t)min(Y0 + r, sh) * P;
         int* dst = tile + r * TP;
         for (int c = lane; c < TC; c += 32) cp_async4(dst + (si ? (c & 1) * TCH + (c >> 1) : c), src + min(X0 + c, sw));
@@ -421,6 +422,9 @@ __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict_
 // K=3 / 5 blocks 11.8, K=2 / 5 blocks 10.2, K=2 / 6 blocks (40 regs) 9.9, K=2 / 8 blocks (32 regs, spills) 10.8,
 // K=1 / 6 blocks 11.3: two windows per fetch already buy most of the amortisation (24.5 vs 22 instructions per
 // window and node), and the 12 extra warps per SM fill the issue slots the stage barriers leave empty.
+// Warps per block (NW): 16 warps on the same 16 x 128 tile (three blocks per SM, same 48 resident warps) measured 9.5 %
+// slower than 8 (9.78 vs 8.93 ms): half as many rounds per warp leaves fewer window pairs, and twice as many warps
+// wait at every end-of-stage barrier.
 #ifndef UGD_SCAN_KMAX
 #define UGD_SCAN_KMAX 2
 #endif
@@ -457,9 +461,9 @@ struct Live {
     }
 };
 
-template <int MODE, bool WORDS, int C>
-__global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1536 / (kScanWarps * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
-    constexpr int NW = kScanWarps, R = kTileRows, KMAX = UGD_SCAN_KMAX;
+template <int MODE, bool WORDS, int C, int NW = kScanWarps>
+__global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarps / NW : 1536 / (NW * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
+    constexpr int R = kTileRows, KMAX = UGD_SCAN_KMAX;
     constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
     static_assert((C == 64 || C == 128) && R == 16 && R % NW == 0, "32 or 64 windows per bank class");
     extern __shared__ int s_tiles[];
@@ -498,23 +502,23 @@ __global__ void __launch_bounds__(kScanWarps * 32, MODE ? UGD_SCAN_MINBLOCKS : 1
     const int32_t* Tp = b.T ? b.T + (size_t)frame * b.int_stride + Lg.int_off : nullptr;
     int* s_tile = s_tiles;
     if (dbl) {
-        stage_tile(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
-        if (Tp) stage_tile(s_tile + TR * TP, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        stage_tile<NW>(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        if (Tp) stage_tile<NW>(s_tile + TR * TP, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
     }
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96 * NMW; i += NW * 32) (&s_alive[0][0][0])[i] = 0;
         // ---- 1. the S tile (and, for cascades with tilted features, the T tile behind it) ----
         if (!dbl) {
-            stage_tile(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
-            if (Tp) stage_tile(s_tile + TR * TP, Tp, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            stage_tile<NW>(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            if (Tp) stage_tile<NW>(s_tile + TR * TP, Tp, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
         }
         cp_async_commit_wait();
         __syncthreads();
         if (dbl && xi0 + C < nxg) {                    // prefetch the next tile into the other buffer
             int* nxt = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
-            stage_tile(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
-            if (Tp) stage_tile(nxt + TR * TP, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            stage_tile<NW>(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            if (Tp) stage_tile<NW>(nxt + TR * TP, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
         }
         // ---- 2. variance normalisation + stage 0 + x-skip, row segment by row segment ----
 #pragma unroll 1
