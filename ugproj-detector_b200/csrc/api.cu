@@ -57,6 +57,12 @@ struct ugd_detector {
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};   // host-input pipeline
     DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
+    // group pipeline of multi-group calls: the image stage (preprocess .. integrals, HBM-bound) of group g+1 runs on
+    // img_stream next to the scan stage (k_scan + grouping, issue-bound) of group g; S / SQ / T / mask exist twice
+    cudaStream_t img_stream = nullptr;
+    cudaEvent_t ev_img_done[2] = {nullptr, nullptr}, ev_scan_done[2] = {nullptr, nullptr}, ev_call = nullptr;
+    bool set_used[2] = {false, false};
+    DevPtr S2, SQ2, T2, mask2;
     std::map<std::pair<int, int>, std::unique_ptr<DevPlan>> plans;
     std::map<std::vector<int>, std::unique_ptr<DevAreaPlan>> area_plans;
     DevPtr src_full, area_dst;                        // full-size input frames / standalone resize output
@@ -187,7 +193,7 @@ int bind_constants(ugd_detector* d) {
     return UGD_OK;
 }
 
-int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, int outcap, int total_frames) {
+int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, int outcap, int total_frames, bool two_sets = false) {
     const size_t F = (size_t)nframes;
     const size_t px = round_up((size_t)p.w * p.h, 256);
     if (need_bgr) {
@@ -202,6 +208,12 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
     CK(d->S.reserve(F * p.int_ints * 4 + 256));
     CK(d->SQ.reserve(F * p.int_ints * 4 + 256));
     if (d->casc->has_tilted) CK(d->T.reserve(F * p.int_ints * 4 + 256));
+    if (two_sets) {
+        CK(d->mask2.reserve(F * px + 256));
+        CK(d->S2.reserve(F * p.int_ints * 4 + 256));
+        CK(d->SQ2.reserve(F * p.int_ints * 4 + 256));
+        if (d->casc->has_tilted) CK(d->T2.reserve(F * p.int_ints * 4 + 256));
+    }
     CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
     CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
     CK(d->raw.reserve(F * d->rawcap * sizeof(ugd_rect)));
@@ -255,8 +267,12 @@ void finish_group(ugd_detector* d, const Plan& p, int f0, int nframes, ugd_rect*
 
 // One group of <= max_batch frames already resident on the device (frames f0.. of the call).  With `defer` the
 // function only enqueues (kernels + result copies to pinned memory); the caller synchronises and calls finish_group.
+// `set` >= 0 (deferred calls only): the group uses buffer set `set` and its image stage goes to img_stream, so that it
+// overlaps the scan stage of the group before it (which works on the other set).
 int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t frame_stride, bool is_bgr, int nframes,
-              ugd_rect* out, int cap, int* counts, int f0, bool defer) {
+              ugd_rect* out, int cap, int* counts, int f0, bool defer, int set = -1) {
+    const bool ovl = set >= 0 && defer;
+    const bool second = ovl && set == 1;
     const Plan& p = dp->host;
     const Cascade& c = *d->casc;
     int rc;
@@ -275,7 +291,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.stage_thr = d->st_thr.as<float>(); b.tree_first_node = d->tree_first_node.as<int32_t>();
     b.stage_first_node = d->st_first_node.as<int32_t>();
     b.px_stride = round_up((size_t)p.w * p.h, 256);
-    b.gray_raw = d->gray_raw.as<uint8_t>(); b.gray_eq = d->gray_eq.as<uint8_t>(); b.mask = d->mask.as<uint8_t>();
+    b.gray_raw = d->gray_raw.as<uint8_t>(); b.gray_eq = d->gray_eq.as<uint8_t>(); b.mask = (second ? d->mask2 : d->mask).as<uint8_t>();
     b.hist = d->hist.as<uint32_t>();
     memcpy(b.skin_lo, d->prm.skin_lower, 3); memcpy(b.skin_hi, d->prm.skin_upper, 3);
     b.use_skin = is_bgr ? 1 : 0;
@@ -286,8 +302,8 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
         b.src_gray = dev_frames; b.src_stride = frame_stride; b.src_pitch = p.w;
     }
     b.pyr = d->pyr.as<uint8_t>(); b.pyr_stride = p.pyr_bytes;
-    b.S = d->S.as<int32_t>(); b.SQ = d->SQ.as<int32_t>(); b.int_stride = p.int_ints;
-    b.T = d->casc->has_tilted ? d->T.as<int32_t>() : nullptr;
+    b.S = (second ? d->S2 : d->S).as<int32_t>(); b.SQ = (second ? d->SQ2 : d->SQ).as<int32_t>(); b.int_stride = p.int_ints;
+    b.T = d->casc->has_tilted ? (second ? d->T2 : d->T).as<int32_t>() : nullptr;
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
     b.pos_stride = p.pos_entries;
     b.tile_min = d->tile_min;
@@ -297,29 +313,35 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.out = d->out.as<ugd_rect>(); b.outcap = cap; b.outcount = d->outcount.as<int>();
     b.min_neighbors = d->prm.min_neighbors;
     b.counters = d->counters.as<unsigned long long>();
-    cudaStream_t st = d->stream;
+    cudaStream_t st = d->stream;                      // scan stage (and everything, without the group pipeline)
+    cudaStream_t si = ovl ? d->img_stream : st;       // image stage
 
+    if (ovl && d->set_used[set]) CK(cudaStreamWaitEvent(si, d->ev_scan_done[set], 0));   // the set's last reader (group g-2) is done
+    mark(d, 0);
+    if (is_bgr) {
+        CK(cudaMemsetAsync(b.hist, 0, (size_t)nframes * 256 * 4, si));
+        launch_preprocess(b, si);
+    }
+    mark(d, 1);
+    if (is_bgr) launch_equalize(b, si);
+    mark(d, 2);
+    launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), si);
+    mark(d, 3);
+    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), si);
+    mark(d, 4);
+    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), si);
+    mark(d, 5);
+    launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), si);
+    mark(d, 6);
+    if (b.T) launch_tilted(b, p.max_level_w, si);
+    mark(d, 7);
+    if (ovl) {
+        CK(cudaEventRecord(d->ev_img_done[set], si));
+        CK(cudaStreamWaitEvent(st, d->ev_img_done[set], 0));
+    }
     CK(cudaMemsetAsync(b.rawcount, 0, (size_t)nframes * 4, st));
     CK(cudaMemsetAsync(b.counters, 0, (size_t)nframes * kCtrPerFrame * 8, st));
     if (b.stage_map) CK(cudaMemsetAsync(b.stage_map, 0x80, p.pos_entries * 2, st));
-    mark(d, 0);
-    if (is_bgr) {
-        CK(cudaMemsetAsync(b.hist, 0, (size_t)nframes * 256 * 4, st));
-        launch_preprocess(b, st);
-    }
-    mark(d, 1);
-    if (is_bgr) launch_equalize(b, st);
-    mark(d, 2);
-    launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), st);
-    mark(d, 3);
-    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), st);
-    mark(d, 4);
-    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), st);
-    mark(d, 5);
-    launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), st);
-    mark(d, 6);
-    if (b.T) launch_tilted(b, p.max_level_w, st);
-    mark(d, 7);
     {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
@@ -333,6 +355,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     CK(cudaMemcpyAsync(d->h_counts + f0, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(d->h_ctr + (size_t)f0 * kCtrPerFrame, b.counters, (size_t)nframes * kCtrPerFrame * 8, cudaMemcpyDeviceToHost, st));
     d->last = b; d->last_plan = dp; d->last_was_bgr = is_bgr;
+    if (ovl) { CK(cudaEventRecord(d->ev_scan_done[set], st)); d->set_used[set] = true; }
     if (defer) return UGD_OK;
     CK(cudaStreamSynchronize(st));
     bool overflow = false;
@@ -399,19 +422,28 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
     // Host frames in more than one group: copies of group g+1 (copy stream) overlap the kernels of group g.
     const bool tight_host = !is_device && host_row_stride == (size_t)w * ch;
     const bool pipelined = tight_host && !d->profiling && nframes > d->max_batch;
-    const bool defer = pipelined || async_submit;
+    // More than one group: the image stage of group g+1 overlaps the scan stage of group g (two buffer sets, two streams).
+    static const bool no_overlap = getenv("UGD_NO_OVERLAP") != nullptr;
+    const bool overlap = !no_overlap && !d->profiling && !d->want_map && nframes > d->max_batch;
+    const bool defer = pipelined || async_submit || overlap;
     if (pipelined) CK(d->stage2.reserve((size_t)d->max_batch * st_stride + 256));
+    cudaStream_t in_stream = overlap ? d->img_stream : d->stream;      // the stream that consumes the input frames
+    if (overlap) {
+        d->set_used[0] = d->set_used[1] = false;
+        CK(cudaEventRecord(d->ev_call, d->stream));                   // the image stream starts after whatever the caller queued before
+        CK(cudaStreamWaitEvent(d->img_stream, d->ev_call, 0));
+    }
     int g = 0;
     for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
         const int nf = std::min(d->max_batch, nframes - f0);
-        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap, nframes))) return rc;
+        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap, nframes, overlap))) return rc;
         const uint8_t* dev; size_t stride;
         uint8_t* staging = is_bgr ? d->bgr.as<uint8_t>() : d->gray_in.as<uint8_t>();
         if (pipelined && (g & 1)) staging = d->stage2.as<uint8_t>();
         if (is_device) {
             const uint8_t* src = static_cast<const uint8_t*>(frames) + (size_t)f0 * tight;
             if (is_bgr && (((uintptr_t)src & 3) || (tight & 3))) {   // K1 reads 32-bit words: realign
-                CK(cudaMemcpy2DAsync(staging, st_stride, src, tight, tight, nf, cudaMemcpyDeviceToDevice, d->stream));
+                CK(cudaMemcpy2DAsync(staging, st_stride, src, tight, tight, nf, cudaMemcpyDeviceToDevice, in_stream));
                 dev = staging; stride = st_stride;
             } else { dev = src; stride = tight; }
         } else {
@@ -421,7 +453,7 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
                 if (g >= 2) CK(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[bi], 0));   // staging[bi] free again
                 CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->copy_stream));
                 CK(cudaEventRecord(d->ev_copied[bi], d->copy_stream));
-                CK(cudaStreamWaitEvent(d->stream, d->ev_copied[bi], 0));
+                CK(cudaStreamWaitEvent(in_stream, d->ev_copied[bi], 0));
             } else if (tight_host) {
                 CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->stream));
             } else {                                                   // single strided frame (cv::Mat with step)
@@ -429,8 +461,9 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
             }
             dev = staging; stride = st_stride;
         }
-        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, defer ? nullptr : out + (size_t)f0 * cap, cap, defer ? nullptr : counts + f0, f0, defer))) return rc;
-        if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));
+        if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, defer ? nullptr : out + (size_t)f0 * cap, cap, defer ? nullptr : counts + f0, f0, defer,
+                            overlap ? (g & 1) : -1))) return rc;
+        if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], in_stream));      // the image stage was the last reader of the staging buffer
     }
     if (defer) {
         d->pending.active = true; d->pending.nframes = nframes; d->pending.cap = cap; d->pending.plan = dp;
@@ -527,6 +560,16 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     }
     d->stream = d->own_stream;
     cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+    {
+        // UGD_IMG_PRIO=low|normal|high (default low): low lets the image stage of the next group fill the tail of the running scan launches
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        const char* pr = getenv("UGD_IMG_PRIO");
+        const int prio = pr && !strcmp(pr, "high") ? hi : pr && !strcmp(pr, "normal") ? 0 : lo;      // measured (alt, 720p, 4 groups): low +2.1 %, normal +1.8 %, high +0.2 %
+        cudaStreamCreateWithPriority(&d->img_stream, cudaStreamNonBlocking, prio);
+        for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&d->ev_img_done[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&d->ev_scan_done[i], cudaEventDisableTiming); }
+        cudaEventCreateWithFlags(&d->ev_call, cudaEventDisableTiming);
+    }
     for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&d->ev_copied[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&d->ev_consumed[i], cudaEventDisableTiming); }
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
@@ -544,6 +587,7 @@ void ugd_destroy(ugd_detector* d) {
     if (!d) return;
     cudaSetDevice(d->device);
     if (d->stream) cudaStreamSynchronize(d->stream);
+    if (d->img_stream) cudaStreamSynchronize(d->img_stream);
     { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     for (auto& kv : d->plans) kv.second->release();
     for (auto& kv : d->area_plans) kv.second->release();
@@ -551,7 +595,7 @@ void ugd_destroy(ugd_detector* d) {
     DevPtr* all[] = {&d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ, &d->T,
                      &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
-                     &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in};
+                     &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in, &d->S2, &d->SQ2, &d->T2, &d->mask2};
     for (DevPtr* p : all) p->release();
     if (d->h_out) cudaFreeHost(d->h_out);
     if (d->h_counts) cudaFreeHost(d->h_counts);
@@ -560,6 +604,9 @@ void ugd_destroy(ugd_detector* d) {
     for (auto& ev : d->ev_area) if (ev) cudaEventDestroy(ev);
     for (int i = 0; i < 2; ++i) { if (d->ev_copied[i]) cudaEventDestroy(d->ev_copied[i]); if (d->ev_consumed[i]) cudaEventDestroy(d->ev_consumed[i]); }
     if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
+    if (d->img_stream) cudaStreamDestroy(d->img_stream);
+    for (int i = 0; i < 2; ++i) { if (d->ev_img_done[i]) cudaEventDestroy(d->ev_img_done[i]); if (d->ev_scan_done[i]) cudaEventDestroy(d->ev_scan_done[i]); }
+    if (d->ev_call) cudaEventDestroy(d->ev_call);
     d->stage2.release();
     if (d->own_stream) cudaStreamDestroy(d->own_stream);
     delete d;
