@@ -38,7 +38,7 @@ __constant__ DNode c_dn[kMaxDenseNodes];
 __constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[kMaxDenseStages];
 __constant__ double c_stage_base[kMaxDenseStages];
-__constant__ int c_stage_nc_first[kMaxDenseStages][5];      // exact stump evaluator: first node with 6 / 8 / 9 / 12 corners, end          // exact stump evaluator: sum of the right leaves of stage s
+__constant__ int c_stage_nc_first[kMaxDenseStages][9];      // exact stump evaluator: first node with 6 / 8 / 9 / 12 corners, end          // exact stump evaluator: sum of the right leaves of stage s
 __constant__ ScanGeom c_geom;
 
 // Tile pitches are chosen so that the bank shift between consecutive window rows, (step * pitch) mod 32,
@@ -88,6 +88,17 @@ int32_t scan_plane_bytes(const ScanGeom& g, int si) { return 4 * g.TR[si] * g.TP
 bool scan_word_offsets(const Cascade& c) {
     const ScanGeom g = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
     return c.has_tilted || g.tile_ints * 4 > 48 * 1024;
+}
+
+// Coefficient patterns of the exact stump evaluator.  With a node's merged corners sorted by coefficient, every node of
+// the four frontalface cascades is one of four vectors (two-rect features: P0; three-rect: P1; centre-surround and its
+// complement: P2, P3).  A node that matches gets an evaluator with the coefficients as compile-time constants: no
+// coefficient fetches, and the +-1 terms fold into three-input adds.  Packed as nibbles, coefficient + 8, corner 0 lowest.
+constexpr int kPatterns = 4;
+__host__ __device__ constexpr int pat_nc(int p) { return p == 0 ? 6 : p == 1 ? 8 : 9; }
+__host__ __device__ constexpr int pat_coef(int p, int j) {
+    const unsigned long long v = p == 0 ? 0xA99776ULL : p == 1 ? 0xBB997755ULL : p == 2 ? 0xAAAA77774ULL : 0xC99996666ULL;
+    return (int)((v >> (4 * j)) & 15ULL) - 8;
 }
 
 // Which in-tile evaluator a cascade gets: 1 = stumps, 2 = two-node trees (root + one child), both with
@@ -147,7 +158,7 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         }
     }
     std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
-    std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 5, 0);
+    std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 9, 0);
     if (mode == 2)
         for (int s = 0; s < dense_stages; ++s)
             for (int t = c.stage_first_tree[s]; t < c.stage_first_tree[s] + c.stage_ntrees[s]; ++t)
@@ -156,15 +167,29 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         for (int s = 0; s < dense_stages; ++s) {
             const int a = c.stage_first_node[s], z = c.stage_first_node[s + 1];
             for (int n = a; n < z; ++n) base[s] += (double)c.nodes[n].right_val;
-            std::stable_sort(dn.begin() + a, dn.begin() + z, [](const DNode& x, const DNode& y) { return (x.meta & 255u) < (y.meta & 255u); });
-            const int cls[4] = {6, 8, 9, 12};
+            // evaluator class of a node: 0..3 = coefficient pattern (corners sorted by coefficient), 4..7 = generic with 6 / 8 / 9 / 12 corners
+            auto klass = [](DNode& d) {
+                const int nc = (int)(d.meta & 255u);
+                for (int i = 1; i < nc; ++i)                                   // insertion sort of the corners by coefficient
+                    for (int j = i; j > 0 && d.coef[j - 1] > d.coef[j]; --j) {
+                        std::swap(d.coef[j - 1], d.coef[j]); std::swap(d.off[0][j - 1], d.off[0][j]); std::swap(d.off[1][j - 1], d.off[1][j]);
+                    }
+                for (int p = 0; p < kPatterns; ++p) {
+                    bool same = pat_nc(p) == nc;
+                    for (int j = 0; same && j < nc; ++j) same = d.coef[j] == pat_coef(p, j);
+                    if (same) return p;
+                }
+                return nc == 6 ? 4 : nc == 8 ? 5 : nc == 9 ? 6 : nc == 12 ? 7 : 8;
+            };
+            std::vector<std::pair<int, DNode>> keyed;
+            for (int n = a; n < z; ++n) { const int k = klass(dn[n]); if (k > 7) return cudaErrorInvalidValue; keyed.push_back({k, dn[n]}); }   // a corner count outside {6, 8, 9, 12}
+            std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<int, DNode>& x, const std::pair<int, DNode>& y) { return x.first < y.first; });
             int n = a;
-            for (int k = 0; k < 4; ++k) {
-                ncf[s * 5 + k] = n;
-                while (n < z && (int)(dn[n].meta & 255u) == cls[k]) ++n;
+            for (int k = 0; k < 8; ++k) {
+                ncf[s * 9 + k] = n;
+                while (n < z && keyed[n - a].first == k) { dn[n] = keyed[n - a].second; ++n; }
             }
-            ncf[s * 5 + 4] = n;
-            if (n != z) return cudaErrorInvalidValue;      // a corner count outside {6, 8, 9, 12}
+            ncf[s * 9 + 8] = n;
         }
     cudaError_t e;
     if ((e = cudaMemcpyToSymbolAsync(c_dn, dn.data(), sizeof(DNode) * dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
@@ -266,15 +291,45 @@ __device__ __forceinline__ void stage_nodes(int n0, int n1, int si, const char* 
     }
 }
 
+// The same for nodes whose coefficient vector is pattern PAT: coefficients are compile-time constants.
+template <int PAT, int K>
+__device__ __forceinline__ void stage_nodes_pat(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    constexpr int NC = pat_nc(PAT);
+#pragma unroll 1
+    for (int n = n0; n < n1; ++n) {
+        const DNode& d = c_dn[n];
+        const int32_t* o = d.off[si];
+        int acc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) acc[k] = 0;
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+            const int oj = o[j];
+#pragma unroll
+            for (int k = 0; k < K; ++k) acc[k] += pat_coef(PAT, j) * *reinterpret_cast<const int*>(t[k] + oj);
+        }
+        const float thr = d.thr;
+        const double delta = d.delta;
+#pragma unroll
+        for (int k = 0; k < K; ++k) add_if_lt(sum[k], __fmul_rn(__int2float_rn(acc[k]), vnf[k]), thr, delta);
+    }
+}
+
 template <int K>
 __device__ __forceinline__ void tile_stage_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
     const int* f = c_stage_nc_first[s];
 #pragma unroll
     for (int k = 0; k < K; ++k) sum[k] = k == 0 ? c_stage_base[s] : sum[0];
-    stage_nodes<6, K>(f[0], f[1], si, t, vnf, sum);
-    stage_nodes<8, K>(f[1], f[2], si, t, vnf, sum);
-    stage_nodes<9, K>(f[2], f[3], si, t, vnf, sum);
-    stage_nodes<12, K>(f[3], f[4], si, t, vnf, sum);
+    stage_nodes_pat<0, K>(f[0], f[1], si, t, vnf, sum);
+    stage_nodes_pat<1, K>(f[1], f[2], si, t, vnf, sum);
+    stage_nodes_pat<2, K>(f[2], f[3], si, t, vnf, sum);
+    stage_nodes_pat<3, K>(f[3], f[4], si, t, vnf, sum);
+    if (f[4] != f[8]) {                                 // nodes outside the four patterns: coefficients from the table
+        stage_nodes<6, K>(f[4], f[5], si, t, vnf, sum);
+        stage_nodes<8, K>(f[5], f[6], si, t, vnf, sum);
+        stage_nodes<9, K>(f[6], f[7], si, t, vnf, sum);
+        stage_nodes<12, K>(f[7], f[8], si, t, vnf, sum);
+    }
 }
 
 // Exact evaluator for two-node trees (scan_mode 2), K windows per lane.  Corner counts differ from node to
