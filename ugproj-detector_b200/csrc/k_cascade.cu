@@ -38,7 +38,7 @@ __constant__ DNode c_dn[kMaxDenseNodes];
 __constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[kMaxDenseStages];
 __constant__ double c_stage_base[kMaxDenseStages];
-__constant__ int c_stage_nc_first[kMaxDenseStages][9];      // exact stump evaluator: first node with 6 / 8 / 9 / 12 corners, end          // exact stump evaluator: sum of the right leaves of stage s
+__constant__ int c_stage_nc_first[kMaxDenseStages][9];      // exact stump evaluator: first node of each evaluator class (4 patterns, then 6 / 8 / 9 / 12 corners), end
 __constant__ ScanGeom c_geom;
 
 // Tile pitches are chosen so that the bank shift between consecutive window rows, (step * pitch) mod 32,
@@ -94,7 +94,10 @@ bool scan_word_offsets(const Cascade& c) {
 // the four frontalface cascades is one of four vectors (two-rect features: P0; three-rect: P1; centre-surround and its
 // complement: P2, P3).  A node that matches gets an evaluator with the coefficients as compile-time constants: no
 // coefficient fetches, and the +-1 terms fold into three-input adds.  Packed as nibbles, coefficient + 8, corner 0 lowest.
-constexpr int kPatterns = 4;
+#ifndef UGD_NPAT
+#define UGD_NPAT 4
+#endif
+constexpr int kPatterns = UGD_NPAT;
 __host__ __device__ constexpr int pat_nc(int p) { return p == 0 ? 6 : p == 1 ? 8 : 9; }
 __host__ __device__ constexpr int pat_coef(int p, int j) {
     const unsigned long long v = p == 0 ? 0xA99776ULL : p == 1 ? 0xBB997755ULL : p == 2 ? 0xAAAA77774ULL : 0xC99996666ULL;
@@ -114,6 +117,22 @@ int scan_mode(const Cascade& c) {
         if (!one_child || k.left != 0 || k.right != 0) return 0;
     }
     return 2;
+}
+
+// Sorts a node's merged corners by coefficient and returns its evaluator class: 0..3 = coefficient pattern,
+// 4..7 = no pattern, 6 / 8 / 9 / 12 corners (coefficients from the table), 8 = unsupported corner count.
+static int sort_and_classify(DNode& d) {
+    const int nc = (int)(d.meta & 255u);
+    for (int i = 1; i < nc; ++i)                                   // insertion sort of the corners by coefficient
+        for (int j = i; j > 0 && d.coef[j - 1] > d.coef[j]; --j) {
+            std::swap(d.coef[j - 1], d.coef[j]); std::swap(d.off[0][j - 1], d.off[0][j]); std::swap(d.off[1][j - 1], d.off[1][j]);
+        }
+    for (int p = 0; p < kPatterns; ++p) {
+        bool same = pat_nc(p) == nc;
+        for (int j = 0; same && j < nc; ++j) same = d.coef[j] == pat_coef(p, j);
+        if (same) return p;
+    }
+    return nc == 6 ? 4 : nc == 8 ? 5 : nc == 9 ? 6 : nc == 12 ? 7 : 8;
 }
 
 cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
@@ -151,9 +170,9 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
                 const HostNode& kid = c.nodes[base + 1];
                 if (k == 0) {
                     const bool leaf_is_left = h.left == 0;
-                    d.delta = (double)(leaf_is_left ? h.left_val : h.right_val) - (double)kid.right_val;
+                    d.delta = ((double)(leaf_is_left ? h.left_val : h.right_val) - (double)kid.right_val) * 128.0;   // see add_if_lt
                     d.meta |= leaf_is_left ? 0u : 1u << 25;          // bit 25: the root's leaf is on its RIGHT
-                } else d.delta = (double)h.left_val - (double)h.right_val;
+                } else d.delta = ((double)h.left_val - (double)h.right_val) * 128.0;
             } else { d.lval = h.left_val; d.rval = h.right_val; }
         }
     }
@@ -167,22 +186,8 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
         for (int s = 0; s < dense_stages; ++s) {
             const int a = c.stage_first_node[s], z = c.stage_first_node[s + 1];
             for (int n = a; n < z; ++n) base[s] += (double)c.nodes[n].right_val;
-            // evaluator class of a node: 0..3 = coefficient pattern (corners sorted by coefficient), 4..7 = generic with 6 / 8 / 9 / 12 corners
-            auto klass = [](DNode& d) {
-                const int nc = (int)(d.meta & 255u);
-                for (int i = 1; i < nc; ++i)                                   // insertion sort of the corners by coefficient
-                    for (int j = i; j > 0 && d.coef[j - 1] > d.coef[j]; --j) {
-                        std::swap(d.coef[j - 1], d.coef[j]); std::swap(d.off[0][j - 1], d.off[0][j]); std::swap(d.off[1][j - 1], d.off[1][j]);
-                    }
-                for (int p = 0; p < kPatterns; ++p) {
-                    bool same = pat_nc(p) == nc;
-                    for (int j = 0; same && j < nc; ++j) same = d.coef[j] == pat_coef(p, j);
-                    if (same) return p;
-                }
-                return nc == 6 ? 4 : nc == 8 ? 5 : nc == 9 ? 6 : nc == 12 ? 7 : 8;
-            };
             std::vector<std::pair<int, DNode>> keyed;
-            for (int n = a; n < z; ++n) { const int k = klass(dn[n]); if (k > 7) return cudaErrorInvalidValue; keyed.push_back({k, dn[n]}); }   // a corner count outside {6, 8, 9, 12}
+            for (int n = a; n < z; ++n) { const int k = sort_and_classify(dn[n]); if (k > 7) return cudaErrorInvalidValue; keyed.push_back({k, dn[n]}); }   // a corner count outside {6, 8, 9, 12}
             std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<int, DNode>& x, const std::pair<int, DNode>& y) { return x.first < y.first; });
             int n = a;
             for (int k = 0; k < 8; ++k) {
@@ -322,8 +327,10 @@ __device__ __forceinline__ void tile_stage_k(int s, int si, const char* const (&
     for (int k = 0; k < K; ++k) sum[k] = k == 0 ? c_stage_base[s] : sum[0];
     stage_nodes_pat<0, K>(f[0], f[1], si, t, vnf, sum);
     stage_nodes_pat<1, K>(f[1], f[2], si, t, vnf, sum);
-    stage_nodes_pat<2, K>(f[2], f[3], si, t, vnf, sum);
-    stage_nodes_pat<3, K>(f[3], f[4], si, t, vnf, sum);
+    if (kPatterns > 2) {
+        stage_nodes_pat<2, K>(f[2], f[3], si, t, vnf, sum);
+        stage_nodes_pat<3, K>(f[3], f[4], si, t, vnf, sum);
+    }
     if (f[4] != f[8]) {                                 // nodes outside the four patterns: coefficients from the table
         stage_nodes<6, K>(f[4], f[5], si, t, vnf, sum);
         stage_nodes<8, K>(f[5], f[6], si, t, vnf, sum);
@@ -356,6 +363,13 @@ __device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* 
 #undef CORNER
 }
 
+// sum += m * delta128 with m = 2^-7 or 0 given as the high word of a double (see add_if_lt)
+__device__ __forceinline__ void add_masked(double& sum, unsigned m_hi, double delta128) {
+    asm("{\n\t.reg .b32 z;\n\t.reg .f64 md;\n\tmov.b32 z, 0;\n\tmov.b64 md, {z, %1};\n\tfma.rn.f64 %0, md, %2, %0;\n\t}" : "+d"(sum) : "r"(m_hi), "d"(delta128));
+}
+
+// (Pattern classes were tried here too -- pairs ordered by (root, child) pattern, nine loops: alt2 13.7 ms against 11.7
+// for this single loop; its stages hold 3 to 34 trees, too few per class to pay for nine loop set-ups.)
 template <int K>
 __device__ __forceinline__ void tree_pairs(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
 #pragma unroll 1
@@ -365,16 +379,18 @@ __device__ __forceinline__ void tree_pairs(int n0, int n1, int si, const char* c
         int ar[K], ak[K];
         node_resp_k<K>(root, si, t, ar);
         node_resp_k<K>(kid, si, t, ak);
-        const bool leaf_right = (root.meta >> 25) & 1u;
+        const unsigned flip = (root.meta >> 25) & 1u ? 0x3f800000u : 0u;     // the root's leaf is on its right: taken when NOT lt
         const float thr_r = root.thr, thr_k = kid.thr;
         const double d_r = root.delta, d_k = kid.delta;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            const bool lt_r = __fmul_rn(__int2float_rn(ar[k]), vnf[k]) < thr_r;
-            const bool lt_k = __fmul_rn(__int2float_rn(ak[k]), vnf[k]) < thr_k;
-            const bool takes_leaf = lt_r != leaf_right;      // left leaf: taken when lt; right leaf: taken when !lt
-            if (takes_leaf) sum[k] += d_r;
-            else if (lt_k) sum[k] += d_k;
+            // 1.0f / 0.0f masks (FSET.BF): the tree adds the root's leaf difference when the root takes its leaf,
+            // else the child's when the child goes left
+            const unsigned lt_r = __float_as_uint(__fmul_rn(__int2float_rn(ar[k]), vnf[k]) < thr_r ? 1.f : 0.f);
+            const unsigned lt_k = __float_as_uint(__fmul_rn(__int2float_rn(ak[k]), vnf[k]) < thr_k ? 1.f : 0.f);
+            const unsigned takes_leaf = lt_r ^ flip;
+            add_masked(sum[k], takes_leaf, d_r);
+            add_masked(sum[k], lt_k & ~takes_leaf, d_k);
         }
     }
 }
