@@ -321,10 +321,10 @@ def main():
         if dominant == "k_scan":
             roof = {"kernel": "k_scan (window scan + all cascade stages)", "bound": "l1", "achieved": casc_gbs, "peak": l1_peak,
                     "unit": "GB/s", "frac": casc_gbs / l1_peak,
-                    # ncu --set full, r01 (profiles/r01_ncu_k_scan_v6_summary.txt, the two launches of one 64-frame 720p
-                    # launch group): dram read 348.4 + 614.0 MB, write 4.5 + 4.7 MB; the algorithmic HBM bytes are the
+                    # ncu --set full, r01 (profiles/r01_ncu_k_scan_v7_summary.txt, the two launches of one 64-frame 720p
+                    # launch group): dram read 348.1 + 615.5 MB, write 4.1 + 4.5 MB; the algorithmic HBM bytes are the
                     # S and SQ planes read once
-                    "traffic": 971.7e6 if (w, h, GROUP) == (1280, 720, 64) else None,
+                    "traffic": 972.2e6 if (w, h, GROUP) == (1280, 720, 64) else None,
                     "hbm": {"algorithmic_bytes": 8 * int_entries * GROUP,
                             "achieved": 8 * int_entries * GROUP / (casc_ms * 1e-3) / 1e9 if casc_ms else None,
                             "peak": hbm_peak, "unit": "GB/s",
