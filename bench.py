@@ -185,8 +185,11 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"               # keep stdout to the one JSON line (an nccl.conf may ask for VERSION)
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "WARN"):
+        # keep stdout to the one JSON line: NCCL prints "NCCL version ..." to stdout at VERSION *and* at WARN (an nccl.conf
+        # may ask for VERSION); warnings go to stderr instead
+        os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ug = ge.load_package()

@@ -140,6 +140,34 @@ def test_pipelined_host_batches(dets, synth):
         assert rectset(got[f]) == rectset(det.detect_bgr(bgr[f]))
 
 
+def test_group_pipeline_device_batches(ug, synth, cv2ref):
+    """Multi-group calls run as a two-stream pipeline (image stage of group g+1 next to the scan stage of group g, S / SQ /
+    mask double-buffered).  Device-resident batches of 11 frames with max_batch 2 = six groups, gray and BGR (the BGR
+    pointer deliberately misaligned so the realign copy joins the image stream), twice in a row on the same detector:
+    every frame must equal its single-frame call, and the counters must add up."""
+    import torch
+    casc = ug.Cascade(cv2ref.cascade_path("alt2"))
+    det = ug.Detector(casc, ug.default_params(), max_size=(640, 360), max_batch=2)
+    gray = synth.gray_batch(640, 360, 11, seed0=900, nfaces=5)
+    bgr = np.stack([synth.bgr_frame(640, 360, 5, 950 + i) for i in range(11)])
+    want_g = [det.detect_gray(f) for f in gray]
+    want_b = [det.detect_bgr(f) for f in bgr]
+    dg = torch.from_numpy(gray).cuda()
+    pad = torch.zeros(bgr.size + 16, dtype=torch.uint8, device="cuda")
+    pad[1:1 + bgr.size] = torch.from_numpy(bgr).reshape(-1).cuda()          # data_ptr + 1: not 4-byte aligned
+    torch.cuda.synchronize()
+    for _ in range(2):
+        got = det.detect_batch_device(dg.data_ptr(), False, 11, 640, 360)
+        assert det.counters()["frames"] == 11
+        for f in range(11):
+            assert rectset(got[f]) == rectset(want_g[f])
+        got = det.detect_batch_device(pad.data_ptr() + 1, True, 11, 640, 360)
+        for f in range(11):
+            assert rectset(got[f]) == rectset(want_b[f])
+    assert sum(len(x) for x in want_g) > 0 and sum(len(x) for x in want_b) > 0
+    det.close()
+
+
 def test_submit_wait_prefetch(dets, synth, ug):
     """8(f) N2: submit returns before the batch is done, the host does other work, wait delivers the same lists as the
     blocking call; a second submit (or a blocking call) while one is pending is refused."""
