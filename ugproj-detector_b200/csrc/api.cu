@@ -503,9 +503,11 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
         CK(cudaStreamWaitEvent(d->img_stream, d->ev_call, 0));
     }
     int g = 0;
-    for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
-        const int nf = std::min(d->max_batch, nframes - f0);
-        if ((rc = ensure_buffers(d, dp->host, nf, is_bgr, cap, nframes, overlap))) return rc;
+    for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++g) {
+        nf = std::min(d->max_batch, nframes - f0);
+        // host frames: a short first group (a quarter) lets the kernels start after a quarter of the first copy
+        if (pipelined && g == 0) nf = std::max(1, std::min(nf, d->max_batch / 4));
+        if ((rc = ensure_buffers(d, dp->host, std::min(d->max_batch, nframes), is_bgr, cap, nframes, overlap))) return rc;
         const uint8_t* dev; size_t stride;
         uint8_t* staging = is_bgr ? d->bgr.as<uint8_t>() : d->gray_in.as<uint8_t>();
         if (pipelined && (g & 1)) staging = d->stage2.as<uint8_t>();
