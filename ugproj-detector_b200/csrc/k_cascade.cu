@@ -178,10 +178,18 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
     }
     std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
     std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 9, 0);
-    if (mode == 2)
+    if (mode == 2) {
         for (int s = 0; s < dense_stages; ++s)
             for (int t = c.stage_first_tree[s]; t < c.stage_first_tree[s] + c.stage_ntrees[s]; ++t)
                 base[s] += (double)c.nodes[c.tree_first_node[t] + 1].right_val;
+        // corners sorted by coefficient; a node that is pattern 0 or 1 says so in meta bits 26-27 (1 / 2) and the
+        // evaluator takes a warp-uniform branch to compile-time coefficients (pairs stay in file order)
+        for (int n = 0; n < nn; ++n) {
+            const int k = sort_and_classify(dn[n]);
+            if (k > 7) return cudaErrorInvalidValue;
+            if (k < 2) dn[n].meta |= (uint32_t)(k + 1) << 26;
+        }
+    }
     if (fast)
         for (int s = 0; s < dense_stages; ++s) {
             const int a = c.stage_first_node[s], z = c.stage_first_node[s + 1];
@@ -345,8 +353,17 @@ template <int K>
 __device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* const (&t)[K], int (&acc)[K]) {
     const int32_t* o = d.off[si];
     const int nc = d.meta & 255u;
+    const unsigned pat = (d.meta >> 26) & 3u;
 #pragma unroll
     for (int k = 0; k < K; ++k) acc[k] = 0;
+#define PCORNER(P, j)                                                                               \
+    {                                                                                               \
+        const int oj = o[j];                                                                        \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += pat_coef(P, j) * *reinterpret_cast<const int*>(t[k] + oj); \
+    }
+    if (pat == 1) { PCORNER(0, 0) PCORNER(0, 1) PCORNER(0, 2) PCORNER(0, 3) PCORNER(0, 4) PCORNER(0, 5) return; }
+    if (pat == 2) { PCORNER(1, 0) PCORNER(1, 1) PCORNER(1, 2) PCORNER(1, 3) PCORNER(1, 4) PCORNER(1, 5) PCORNER(1, 6) PCORNER(1, 7) return; }
+#undef PCORNER
 #define CORNER(j)                                                                                   \
     {                                                                                               \
         const int oj = o[j], cj = d.coef[j];                                                        \
