@@ -38,6 +38,10 @@ extern "C" {
 #define UGD_ERR_CAPACITY     6   /* frame larger than the detector was created for, or an internal
                                     per-frame candidate buffer overflowed                           */
 #define UGD_ERR_NOMEM        7
+#define UGD_ERR_TRUNCATED    8   /* some frame produced more rectangles than `cap`: out holds the first cap
+                                    of each such frame, counts[] / *n hold the TRUE counts -- call again
+                                    with cap >= the largest count (the reference's std::vector is unbounded) */
+#define UGD_ERR_COMM         9   /* NCCL missing or failed; text via ugd_last_error()               */
 
 /* == cv::Rect (x, y, width, height as int32) -- detector.h:15 std::vector<cv::Rect>& rects */
 typedef struct { int32_t x, y, width, height; } ugd_rect;
@@ -170,6 +174,30 @@ int  ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device,
 int  ugd_resize_area(ugd_detector* d, const uint8_t* src, int src_w, int src_h, int channels, size_t stride_bytes,
                      uint8_t* dst, int dst_w, int dst_h);
 
+/* ---- multi-GPU: one process per GPU, frames sharded, lists gathered to the root ---------------------
+ * detectFaces has no inter-frame state (the tracker does: face_tracker.cc:140-149, and it stays on the root's host), so
+ * rank r of N takes the contiguous frame range ugd_shard_range(F, r, N) and the ONE exchange step of the path is the
+ * gather of the per-frame lists to the root.  The engine does it itself with NCCL send/recv over NVLink, straight from
+ * the device-side result slots, on the detector's stream (libnccl.so.2 is bound at run time with dlopen; without it
+ * these calls return UGD_ERR_COMM and everything else keeps working).
+ *   ugd_comm_unique_id : ncclGetUniqueId -- the root calls it and hands the 128 bytes to every rank by whatever
+ *                        means the host has (a file, MPI, torch.distributed ...);
+ *   ugd_comm_init      : ncclCommInitRank on the detector's device (collective: every rank calls it);
+ *   ugd_comm_attach    : use an ncclComm_t the host already owns instead (not destroyed by ugd_destroy);
+ *   ugd_detect_batch_sharded : ugd_detect_batch on this rank's `nframes` frames (nframes <= slot_frames, the same
+ *                        slot_frames and cap on every rank), then the gather.  On the root, out / counts hold
+ *                        world x slot_frames frames: frame f of rank r at index r * slot_frames + f (out: cap rects
+ *                        each), counts -1 for the slots a rank did not use.  On the other ranks out / counts receive
+ *                        that rank's own nframes lists, as from ugd_detect_batch.  Collective: every rank calls it. */
+#define UGD_COMM_ID_BYTES 128
+int  ugd_comm_unique_id(uint8_t* id /* UGD_COMM_ID_BYTES */);
+int  ugd_comm_init(ugd_detector* d, const uint8_t* id, int rank, int world);
+int  ugd_comm_attach(ugd_detector* d, void* nccl_comm, int rank, int world);
+int  ugd_comm_info(const ugd_detector* d, int* rank, int* world, int* nccl_version);
+void ugd_shard_range(int nframes, int rank, int world, int* lo, int* hi);
+int  ugd_detect_batch_sharded(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h,
+                              int slot_frames, int root, ugd_rect* out, int cap, int* counts);
+
 int  ugd_get_counters(const ugd_detector* d, ugd_counters* c);
 /* Per-kernel device time (ms, CUDA events on the detector's stream) of the most recent detect call;
  * recorded only after ugd_set_profiling(d, 1).  times_ms: UGD_K_COUNT entries. */
@@ -200,6 +228,11 @@ int  ugd_get_stage_map(ugd_detector* d, int16_t* map, size_t cap, size_t* n);
 int  ugd_get_preprocessed(ugd_detector* d, uint8_t* gray_eq, uint8_t* mask);
 int  ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t* SQ);
 int  ugd_get_level_tilted(ugd_detector* d, int level, int32_t* T);
+
+/* Measured roofline denominator of k_scan: sustained GB/s of a conflict-free stream of 32-bit shared-memory loads on
+ * every SM of the device (one probe kernel, CUDA-event timed; takes ~20 ms).  bytes_per_clk_per_sm (may be NULL)
+ * relates it to the nominal 128 B/clk at the device's rated clock. */
+int  ugd_measure_lds_peak(int cuda_device, double* gbytes_per_s, double* bytes_per_clk_per_sm);
 
 const char* ugd_strerror(int code);
 const char* ugd_last_error(const ugd_detector* d);   /* detail of the detector's last failure */

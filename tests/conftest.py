@@ -80,3 +80,35 @@ def pass_everything_cascade(out_path, win=(20, 20)):
                  "<threshold>0.1</threshold><left_val>1.</left_val><right_val>1.</right_val></_></_></trees>"
                  "<stage_threshold>0.5</stage_threshold><parent>-1</parent><next>-1</next></_></stages></c></opencv_storage>")
     return str(out_path)
+
+
+def inexact_cascade(path, out_path, every=4):
+    """A copy of an old-format stump cascade with extra stumps whose leaves are tiny (~1e-9, full 24-bit mantissas)
+    at the head of every stage and after every `every`-th tree: decisions barely move, but the exponent spread of the
+    leaves now exceeds what an fp64 sum holds exactly, so ugd_cascade_info.sum_exact is 0 and the low bits of a stage
+    sum depend on the order of addition -- the engine must add the leaves in file order, like the oracle and cv2."""
+    import re
+    text = open(path).read()
+    k = [0]
+
+    def tiny():
+        k[0] += 1
+        a, b = 1.2345678e-9 * (1.0 + 0.37 * (k[0] % 11)), 2.7182818e-9 * (1.0 + 0.21 * (k[0] % 7))
+        return ("<_><_><feature><rects><_>%d %d 6 4 -1.</_><_>%d %d 3 4 2.</_></rects><tilted>0</tilted></feature>"
+                "<threshold>%.6f</threshold><left_val>%.9e</left_val><right_val>%.9e</right_val></_></_>"
+                % (k[0] % 9, k[0] % 7, k[0] % 9, k[0] % 7, 0.001 * (k[0] % 5 - 2), a, b))
+    out, pos, ntree = [], 0, 0
+    for m in re.finditer(r"<trees>|</_>\s*</_>(?=\s*(?:<!--[^>]*-->\s*)?(?:<_>|</trees>))", text):
+        out.append(text[pos:m.end()])
+        pos = m.end()
+        if m.group(0) == "<trees>":
+            ntree = 0
+            out.append(tiny())
+        else:
+            ntree += 1
+            if ntree % every == 0:
+                out.append(tiny())
+    out.append(text[pos:])
+    with open(out_path, "w") as fh:
+        fh.write("".join(out))
+    return str(out_path)

@@ -1,6 +1,7 @@
 """CPU tests (no GPU): host-side logic of the product -- XML loader, cfg reader, pyramid plan, the
 C ABI surface -- and the multi-rank sharding / gather path on gloo (world size 2)."""
 import ctypes
+import json
 import os
 import re
 import subprocess
@@ -218,7 +219,7 @@ GLOO_WORKER = r'''
 import os, sys, numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, os.environ["UGD_ROOT"])
 import __graft_entry__ as ge
-ge.load_package()
+ug = ge.load_package()
 import importlib
 sh = importlib.import_module("ugproj_detector_b200.sharding")
 dist.init_process_group("gloo")
@@ -229,6 +230,13 @@ def fake_detect(i):                      # deterministic stand-in for a frame's 
 lo, hi = sh.shard_range(F, rank, world)
 local = sh.pack_slots([fake_detect(i) for i in range(lo, hi)], cap)
 maxf = max(b - a for a, b in (sh.shard_range(F, r, world) for r in range(world)))
+assert (lo, hi) == ug.shard_range(F, rank, world)                        # the C ABI's ugd_shard_range: same rule
+# the plumbing of sharding.init_comm: rank 0 draws the NCCL id through the library, every rank ends up with the same 128 bytes
+box = [ug.comm_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(box, src=0)
+ids = [None] * world
+dist.all_gather_object(ids, box[0])
+assert len(box[0]) == 128 and all(i == ids[0] for i in ids)
 bufs = sh.gather_to_rank0(torch.from_numpy(local), world, rank, maxf)
 if rank == 0:
     got = []
@@ -253,3 +261,30 @@ def test_gather_to_rank0_gloo_world2(tmp_path):
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "GATHER_OK" in r.stdout
+
+
+@pytest.mark.parametrize("name,w,h,sf,ms", [("alt", 1280, 720, 1.1, 30), ("default", 1920, 1080, 1.1, 30), ("alt", 3840, 2160, 1.05, 24),
+                                            ("alt2", 640, 360, 1.1, 30)])
+def test_bench_geometry_matches_the_plan(ug, cv2ref, name, w, h, sf, ms):
+    """bench.py prints `config` in both arms from a plain-Python restatement of the scale list (the reference arm must
+    not load the CUDA library): it has to agree with the engine's plan."""
+    import bench
+    c = ug.Cascade(cv2ref.cascade_path(name))
+    q = ug.plan_query(c, ug.default_params(scale_factor=sf, min_size=(ms, ms)), w, h)
+    levels, level_px, int_entries = bench.geometry(w, h, c.info.win_w, sf, ms)
+    assert levels == len(q["scales"]) and level_px == q["level_pixels"]
+    assert int_entries == int(sum((int(a) + 1) * (int(b) + 1) for a, b in zip(q["lw"], q["lh"])))
+
+
+def test_bench_reference_arm_prints_the_same_config(ug, cv2ref):
+    """`bench.py --impl reference` runs cv2 alone (no CUDA library in the process) on rank 0's frames and carries the
+    same `config` object as the repo arm, so the driver's ratio compares like with like."""
+    import bench
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "frames/s" and line["value"] > 0
+    want = bench.workload_config("haarcascade_frontalface_alt.xml", 1280, 720, 1.1, 30, bench.FRAMES_PER_STEP, bench.GROUP, 1, 20)
+    assert line["config"] == want
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "reference"

@@ -175,3 +175,18 @@ def test_oracle_against_golden_fixtures(orc, cv2ref, synth):
             assert hashlib.sha1(f.tobytes()).hexdigest() == c["frame_sha1"]
             got, _ = orc.detect_faces(oc, f, c["scale"], 2, ms)
         assert rectset(got) == rectset(c["rects"]), c
+
+
+def test_inexact_stage_sums_match_cv2_bitwise(orc, cv2ref, synth, tmp_path):
+    """Pins the ORDER of the oracle's stage sums: on a cascade whose sums are not exactly representable
+    (conftest.inexact_cascade) the final-stage sums equal cv2's detectMultiScale3 weights bit for bit."""
+    import cv2
+    from conftest import inexact_cascade
+    p = inexact_cascade(cv2ref.cascade_path("alt"), tmp_path / "inexact.xml")
+    oc = orc.OracleCascade.load(p)
+    cc = cv2.CascadeClassifier(p)
+    g = synth.gray_frame(640, 360, 6, 3)
+    raw, sums, _ = orc.detect_raw(oc, g)
+    r, _, wt = cc.detectMultiScale3(g, scaleFactor=1.1, minNeighbors=0, minSize=(30, 30), outputRejectLevels=True)
+    assert len(raw) == len(r) > 0
+    assert sorted(sums.tolist()) == sorted(np.asarray(wt).reshape(-1).tolist())

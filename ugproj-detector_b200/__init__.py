@@ -20,7 +20,7 @@ from . import _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM = range(8)
+OK, ERR_ARG, ERR_IO, ERR_PARSE, ERR_UNSUPPORTED, ERR_CUDA, ERR_CAPACITY, ERR_NOMEM, ERR_TRUNCATED = range(9)
 K_NAMES = ("k_preprocess", "k_equalize", "k_resize", "k_colsum", "k_carry", "k_integral", "k_tilted", "k_scan",
            "k_group", "k_area")
 
@@ -77,6 +77,7 @@ def lib():
         L.ugd_last_error.argtypes = [C.c_void_p]
         L.ugd_destroy.argtypes = [C.c_void_p]
         L.ugd_cascade_free.argtypes = [C.c_void_p]
+        L.ugd_shard_range.restype = None
         _LIB = L
     return _LIB
 
@@ -109,6 +110,21 @@ def load_config(cfg_path: str):
 
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def comm_unique_id() -> bytes:
+    """ncclGetUniqueId through the library (the root calls it; every rank passes the bytes to Detector.comm_init)."""
+    buf = C.create_string_buffer(128)
+    rc = lib().ugd_comm_unique_id(buf)
+    if rc:
+        raise UgdError(rc, "ugd_comm_unique_id")
+    return buf.raw
+
+
+def shard_range(nframes: int, rank: int, world: int):
+    lo, hi = C.c_int(), C.c_int()
+    lib().ugd_shard_range(nframes, rank, world, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
 
 
 class Cascade:
@@ -189,19 +205,26 @@ class Detector:
         assert bgr.dtype == np.uint8 and bgr.ndim == 3 and bgr.shape[2] == 3
         bgr = np.ascontiguousarray(bgr)
         h, w = bgr.shape[:2]
-        out = (Rect * cap)()
-        n = C.c_int()
-        self._ck(lib().ugd_detect_bgr(self._h, _p(bgr), w, h, C.c_size_t(w * 3), out, cap, C.byref(n)))
-        return _rects_np(out, min(n.value, cap))
+        return self._single(lib().ugd_detect_bgr, bgr, w, h, w * 3, cap)
+
+    def _single(self, fn, frame, w, h, stride, cap):
+        """One frame; a list longer than `cap` (UGD_ERR_TRUNCATED) is fetched again with the true count, so the
+        result is never silently cut -- the reference's std::vector is unbounded (detector.cc:41)."""
+        while True:
+            out = (Rect * cap)()
+            n = C.c_int()
+            rc = fn(self._h, _p(frame), w, h, C.c_size_t(stride), out, cap, C.byref(n))
+            if rc == ERR_TRUNCATED and n.value > cap:
+                cap = n.value
+                continue
+            self._ck(rc)
+            return _rects_np(out, min(n.value, cap))
 
     def detect_gray(self, gray: np.ndarray, cap: int = 1024) -> np.ndarray:
         assert gray.dtype == np.uint8 and gray.ndim == 2
         gray = np.ascontiguousarray(gray)
         h, w = gray.shape
-        out = (Rect * cap)()
-        n = C.c_int()
-        self._ck(lib().ugd_detect_gray(self._h, _p(gray), w, h, C.c_size_t(w), out, cap, C.byref(n)))
-        return _rects_np(out, min(n.value, cap))
+        return self._single(lib().ugd_detect_gray, gray, w, h, w, cap)
 
     # -- batch ------------------------------------------------------------------------------------
     def detect_batch(self, frames: np.ndarray, cap: int = 256):
@@ -258,14 +281,53 @@ class Detector:
         return self._batch(C.c_void_p(dev_ptr), 1, is_bgr, n, w, h, cap)
 
     def _batch(self, ptr, is_device, is_bgr, n, w, h, cap):
-        key = (n, cap)
-        if getattr(self, "_bkey", None) != key:
-            self._bout = np.zeros((n, cap, 4), np.int32)
-            self._bcnt = np.zeros(n, np.int32)
-            self._bkey = key
-        self._ck(lib().ugd_detect_batch(self._h, ptr, is_device, int(is_bgr), n, w, h, _p(self._bout), cap,
-                                        _p(self._bcnt)))
-        return [self._bout[i, :min(int(self._bcnt[i]), cap)].copy() for i in range(n)]
+        while True:
+            key = (n, cap)
+            if getattr(self, "_bkey", None) != key:
+                self._bout = np.zeros((n, cap, 4), np.int32)
+                self._bcnt = np.zeros(n, np.int32)
+                self._bkey = key
+            rc = lib().ugd_detect_batch(self._h, ptr, is_device, int(is_bgr), n, w, h, _p(self._bout), cap, _p(self._bcnt))
+            if rc == ERR_TRUNCATED and int(self._bcnt.max()) > cap:      # never cut a list silently: run again with room
+                cap = int(self._bcnt.max())
+                continue
+            self._ck(rc)
+            return [self._bout[i, :int(self._bcnt[i])].copy() for i in range(n)]
+
+    # -- multi-GPU: frames sharded over ranks, lists gathered to the root inside the library ----------
+    def comm_init(self, comm_id: bytes, rank: int, world: int):
+        """ncclCommInitRank on this detector's device; comm_id = comm_unique_id() of the root, handed to every rank."""
+        assert len(comm_id) == 128
+        self._ck(lib().ugd_comm_init(self._h, C.c_char_p(comm_id), rank, world))
+        self.rank, self.world = rank, world
+
+    def comm_info(self):
+        r, w, v = C.c_int(), C.c_int(), C.c_int()
+        self._ck(lib().ugd_comm_info(self._h, C.byref(r), C.byref(w), C.byref(v)))
+        return r.value, w.value, v.value
+
+    def detect_batch_sharded(self, ptr, is_device: bool, is_bgr: bool, n: int, w: int, h: int, slot_frames: int,
+                             root: int = 0, cap: int = 256):
+        """This rank's n frames (host array pointer or device pointer) + the NCCL gather to `root`.
+        Root: list over ranks of lists over that rank's frames of [k,4] arrays; other ranks: their own lists."""
+        if not isinstance(ptr, C.c_void_p):
+            ptr = C.c_void_p(ptr)
+        rank, world, _ = self.comm_info()
+        nslots = world * slot_frames if rank == root else n
+        key = ("s", nslots, cap)
+        if getattr(self, "_skey", None) != key:
+            self._sout = np.zeros((max(nslots, 1), cap, 4), np.int32)
+            self._scnt = np.zeros(max(nslots, 1), np.int32)
+            self._skey = key
+        self._ck(lib().ugd_detect_batch_sharded(self._h, ptr, int(is_device), int(is_bgr), n, w, h, slot_frames, root,
+                                                _p(self._sout), cap, _p(self._scnt)))
+        if rank != root:
+            return [self._sout[i, :int(self._scnt[i])].copy() for i in range(n)]
+        out = []
+        for r in range(world):
+            c = self._scnt[r * slot_frames:(r + 1) * slot_frames]
+            out.append([self._sout[r * slot_frames + i, :int(c[i])].copy() for i in range(slot_frames) if c[i] >= 0])
+        return out
 
     # -- observability ----------------------------------------------------------------------------
     def counters(self) -> dict:

@@ -2,6 +2,7 @@
 // Host orchestration only -- all arithmetic of the path happens in the kernels of k_*.cu.
 #include <algorithm>
 #include <array>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -10,6 +11,9 @@
 #include <mutex>
 #include <string>
 #include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>      // types and prototypes only: libnccl.so.2 is bound at run time (dlopen), never at link time
 
 #include "kernels.cuh"
 
@@ -43,8 +47,17 @@ struct DevAreaPlan {                  // INTER_AREA tables for one (source size 
     void release() { xfirst.release(); yfirst.release(); xtaps.release(); ytaps.release(); }
 };
 
+// The dense-stage nodes live in ONE __constant__ image per device, shared by every detector on that device.  The bank
+// records whose image is resident (cascade uid + dense_stages: detectors of the same cascade share it without a reload)
+// and which detectors have scans in flight against it; a detector with a different image waits (on its own stream, no
+// host block) for those scans before it uploads its own.  The mutex is held from the check through the k_scan launches
+// and the last-use event, so no other detector can swap the image between a bind and the launches that rely on it.
+struct ConstBank {
+    uint64_t uid = 0; int dense = -1;
+    std::vector<ugd_detector*> users;
+};
 std::mutex g_const_mu;
-const void* g_const_owner = nullptr;  // which detector's dense nodes currently sit in __constant__
+ConstBank g_bank[64];
 
 inline size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
 
@@ -52,6 +65,7 @@ inline size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
 
 struct ugd_detector {
     const Cascade* casc = nullptr;
+    uint64_t casc_uid = 0;
     ugd_params prm{};
     int device = 0, max_w = 0, max_h = 0, max_batch = 1;
     int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 32;
@@ -82,9 +96,19 @@ struct ugd_detector {
     ugd_counters ctr{};
     struct { bool active = false; int nframes = 0, cap = 0; DevPlan* plan = nullptr; } pending;   // ugd_submit_batch ... ugd_wait_batch
     bool profiling = false, want_map = false;
+    bool truncated = false;                           // some frame of the current call had more rects than cap
     float ktime[UGD_K_COUNT] = {0}; int64_t klaunch[UGD_K_COUNT] = {0};
     cudaEvent_t ev[UGD_K_COUNT + 1] = {nullptr};
     cudaEvent_t ev_area[2] = {nullptr, nullptr};
+    // multi-GPU gather (ugd_comm_*, ugd_detect_batch_sharded)
+    struct {
+        ncclComm_t comm = nullptr; bool own = false; int rank = 0, world = 1;
+        bool call = false; int slot_frames = 0;       // a sharded call is being enqueued: run_group also files its lists in `send`
+        DevPtr send, recv, packed;
+        int* h_packed = nullptr; size_t h_packed_cap = 0;
+    } shard;
+    ScanConstImage const_img;                         // host image of this detector's __constant__ data
+    cudaEvent_t ev_const_use = nullptr;               // recorded after every k_scan launch of this detector
     std::string err;
     int sm_count = 148;
 };
@@ -121,7 +145,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
-    if (c.has_tilted) CK(init_tilted_attributes(dp->host.max_level_w));
+    if (c.has_tilted) CK(init_tilted_attributes(d->device, dp->host.max_level_w));
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
     *out = dp.get();
     d->plans[key] = std::move(dp);
@@ -197,7 +221,7 @@ int upload_cascade(ugd_detector* d) {
     // warp evaluates together take the same branches (stage sums are order-independent).
     std::vector<int> order(c.nnodes());
     for (int i = 0; i < c.nnodes(); ++i) order[i] = i;
-    if (c.max_tree_nodes == 1)
+    if (c.max_tree_nodes == 1 && c.sum_exact)          // (a cascade whose sums are not exact keeps file order: see DevBufs::seq_sum)
         for (int s = 0; s < c.nstages(); ++s)
             std::stable_sort(order.begin() + c.stage_first_node[s], order.begin() + c.stage_first_node[s + 1],
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
@@ -252,13 +276,20 @@ int upload_cascade(ugd_detector* d) {
     return UGD_OK;
 }
 
-// The dense-stage nodes live in one __constant__ array shared by all detectors of the process.
-int bind_constants(ugd_detector* d) {
+// Makes this detector's image the resident one (see ConstBank), launches the scan and records the last-use event.
+int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
     std::lock_guard<std::mutex> lk(g_const_mu);
-    if (g_const_owner == d) return UGD_OK;
-    const Cascade& c = *d->casc;
-    CK(upload_scan_constants(c, d->dense_stages, d->stream));
-    g_const_owner = d;
+    ConstBank& bk = g_bank[d->device & 63];
+    if (bk.uid != d->casc_uid || bk.dense != d->dense_stages) {
+        for (ugd_detector* u : bk.users)
+            if (u != d) CK(cudaStreamWaitEvent(st, u->ev_const_use, 0));
+        bk.users.clear();
+        CK(upload_scan_constants(d->const_img, st));
+        bk.uid = d->casc_uid; bk.dense = d->dense_stages;
+    }
+    launch_scan(b, wk, nblocks, nblocks_step2, st);
+    CK(cudaEventRecord(d->ev_const_use, st));
+    if (std::find(bk.users.begin(), bk.users.end(), d) == bk.users.end()) bk.users.push_back(d);
     return UGD_OK;
 }
 
@@ -317,6 +348,7 @@ void finish_group(ugd_detector* d, const Plan& p, int f0, int nframes, ugd_rect*
     for (int f = 0; f < nframes; ++f) {
         const int n = d->h_counts[f0 + f];
         counts[f] = n;
+        if (n > cap) d->truncated = true;
         memcpy(out + (size_t)f * cap, d->h_out + (size_t)(f0 + f) * cap, (size_t)std::min(n, cap) * sizeof(ugd_rect));
         const unsigned long long* k = d->h_ctr + (size_t)(f0 + f) * kCtrPerFrame;
         d->ctr.windows_evaluated += (int64_t)k[CTR_EVALUATED];
@@ -345,12 +377,12 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     const Plan& p = dp->host;
     const Cascade& c = *d->casc;
     int rc;
-    if ((rc = bind_constants(d))) return rc;
     DevBufs b{};
     b.w = p.w; b.h = p.h; b.nlevels = (int)p.levels.size(); b.nframes = nframes;
     b.win_w = c.win_w; b.win_h = c.win_h; b.nstages = c.nstages(); b.dense_stages = d->dense_stages;
     b.stumps_only = c.max_tree_nodes == 1;
     b.fast_scan = scan_mode(c); b.word_off = scan_word_offsets(c) ? 1 : 0;
+    b.seq_sum = c.sum_exact ? 0 : 1;
     { static const int kmin = getenv("UGD_SCAN_KMIN") ? atoi(getenv("UGD_SCAN_KMIN")) : 2; b.scan_kmin = std::max(kmin, 1); }   // 2: measured optimum (1: -2 %, 3: -3 %, 4: -8 %)
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeC = d->nodeC.as<uint4>();
@@ -414,7 +446,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
-        launch_scan(b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st);
+        if ((rc = scan_with_constants(d, b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st))) return rc;
     }
     mark(d, 8);
     launch_group(b, st);
@@ -423,6 +455,11 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     CK(cudaMemcpyAsync(d->h_out + (size_t)f0 * cap, b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(d->h_counts + f0, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(d->h_ctr + (size_t)f0 * kCtrPerFrame, b.counters, (size_t)nframes * kCtrPerFrame * 8, cudaMemcpyDeviceToHost, st));
+    if (d->shard.call) {                              // this rank's message for the gather: rect slots, then counts
+        uint8_t* msg = d->shard.send.as<uint8_t>();
+        CK(cudaMemcpyAsync(msg + (size_t)f0 * cap * sizeof(ugd_rect), b.out, (size_t)nframes * cap * sizeof(ugd_rect), cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(msg + (size_t)d->shard.slot_frames * cap * sizeof(ugd_rect) + (size_t)f0 * 4, b.outcount, (size_t)nframes * 4, cudaMemcpyDeviceToDevice, st));
+    }
     d->last = b; d->last_plan = dp; d->last_was_bgr = is_bgr;
     if (ovl) { CK(cudaEventRecord(d->ev_scan_done[set], st)); d->set_used[set] = true; }
     if (defer) return UGD_OK;
@@ -440,6 +477,12 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     d->last = b; d->last_plan = dp; d->last_was_bgr = is_bgr;
     if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     return UGD_OK;
+}
+
+int truncation_status(ugd_detector* d) {
+    if (!d->truncated) return UGD_OK;
+    d->err = "a frame has more rectangles than cap: counts hold the true numbers, call again with a larger cap";
+    return UGD_ERR_TRUNCATED;
 }
 
 int get_area_plan(ugd_detector* d, int sw, int sh, int dw, int dh, DevAreaPlan** out) {
@@ -473,8 +516,27 @@ int wait_pending(ugd_detector* d, ugd_rect* out, int* counts);
 
 // async_submit: enqueue everything (copies, kernels, result copies to pinned memory) and return without waiting;
 // ugd_wait_batch finishes the call.  out/counts are not touched until then.
+int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
+                size_t host_row_stride, ugd_rect* out, int cap, int* counts, bool async_submit);
+
+// A failure in the middle of the group loop leaves enqueued work behind: drain it before the error goes up, so the
+// caller may free or reuse its buffers.
+void drain(ugd_detector* d) {
+    if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
+    if (d->img_stream) cudaStreamSynchronize(d->img_stream);
+    if (d->stream) cudaStreamSynchronize(d->stream);
+    d->pending.active = false;
+}
+
 int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
                   size_t host_row_stride, ugd_rect* out, int cap, int* counts, bool async_submit = false) {
+    const int rc = detect_body(d, frames, is_device, is_bgr, nframes, w, h, host_row_stride, out, cap, counts, async_submit);
+    if (rc != UGD_OK && rc != UGD_ERR_TRUNCATED && rc != UGD_ERR_ARG && d) drain(d);
+    return rc;
+}
+
+int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
+                size_t host_row_stride, ugd_rect* out, int cap, int* counts, bool async_submit) {
     if (!d || !frames || nframes < 0 || cap <= 0 || w <= 0 || h <= 0) return UGD_ERR_ARG;
     if (!async_submit && (!out || !counts)) return UGD_ERR_ARG;
     if (d->pending.active) { d->err = "a submitted batch is still pending: call ugd_wait_batch first"; return UGD_ERR_ARG; }
@@ -484,6 +546,7 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
     int rc;
     if ((rc = get_plan(d, w, h, &dp))) return rc;
     d->ctr = ugd_counters{};
+    d->truncated = false;
     memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
     const size_t ch = is_bgr ? 3 : 1;
     const size_t tight = (size_t)w * h * ch;
@@ -539,8 +602,9 @@ int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_b
     if (defer) {
         d->pending.active = true; d->pending.nframes = nframes; d->pending.cap = cap; d->pending.plan = dp;
         if (!async_submit) return wait_pending(d, out, counts);
+        return UGD_OK;
     }
-    return UGD_OK;
+    return truncation_status(d);
 }
 
 int wait_pending(ugd_detector* d, ugd_rect* out, int* counts) {
@@ -552,7 +616,55 @@ int wait_pending(ugd_detector* d, ugd_rect* out, int* counts) {
     for (int f0 = 0; f0 < nframes; f0 += d->max_batch)
         finish_group(d, d->pending.plan->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
     if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
-    return UGD_OK;
+    return truncation_status(d);
+}
+
+// ---- NCCL, bound at run time --------------------------------------------------------------------
+struct NcclApi {
+    void* h = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclSend) Send = nullptr;
+    decltype(&ncclRecv) Recv = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    decltype(&ncclGetVersion) GetVersion = nullptr;
+    std::string err;
+};
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        // a process that already carries an NCCL (torch's bundled one) gets that same library back by soname
+        const char* names[] = {getenv("UGD_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) {
+            if (!n) continue;
+            api.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (api.h) break;
+        }
+        if (!api.h) { api.err = std::string("cannot load libnccl.so.2: ") + (dlerror() ? dlerror() : "?"); return; }
+#define UGD_SYM(f) api.f = reinterpret_cast<decltype(api.f)>(dlsym(api.h, "nccl" #f)); if (!api.f) { api.err = "libnccl lacks nccl" #f; api.h = nullptr; return; }
+        UGD_SYM(GetUniqueId) UGD_SYM(CommInitRank) UGD_SYM(CommDestroy) UGD_SYM(Send) UGD_SYM(Recv) UGD_SYM(GroupStart)
+        UGD_SYM(GroupEnd) UGD_SYM(GetErrorString) UGD_SYM(GetVersion)
+#undef UGD_SYM
+    });
+    return api.h ? &api : nullptr;
+}
+
+int fail_nccl(ugd_detector* d, ncclResult_t r, const char* what) {
+    NcclApi* n = nccl_api();
+    d->err = std::string(what) + ": " + (n ? n->GetErrorString(r) : "NCCL not loaded");
+    return UGD_ERR_COMM;
+}
+#define NK(call)                                                        \
+    do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) return fail_nccl(d, r_, #call); } while (0)
+
+void comm_release(ugd_detector* d) {
+    if (d->shard.comm && d->shard.own) { NcclApi* n = nccl_api(); if (n) n->CommDestroy(d->shard.comm); }
+    d->shard.comm = nullptr; d->shard.own = false; d->shard.rank = 0; d->shard.world = 1;
 }
 
 }  // namespace
@@ -567,6 +679,8 @@ int ugd_cascade_load_xml(const char* path, ugd_cascade** out) {
     std::string err;
     int rc = load_cascade_xml(path, c->c, err);
     if (rc != UGD_OK) { fprintf(stderr, "ugdet: %s: %s\n", path, err.c_str()); return rc; }
+    static std::atomic<uint64_t> next_uid{1};
+    c->uid = next_uid.fetch_add(1);
     *out = c.release();
     return UGD_OK;
 }
@@ -612,7 +726,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     if (max_w > 4095 + c->c.win_w || max_h > 4095 + c->c.win_h) return UGD_ERR_CAPACITY;   // window ids and tile offsets are sized for frames up to 4K
     std::unique_ptr<ugd_detector> up(new ugd_detector);
     ugd_detector* d = up.get();
-    d->casc = &c->c;
+    d->casc = &c->c; d->casc_uid = c->uid;
     if (p) d->prm = *p; else ugd_params_default(&d->prm);
     if (!(d->prm.scale_factor > 1.0)) return UGD_ERR_ARG;
     d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
@@ -645,8 +759,12 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
     for (auto& ev : d->ev_area) cudaEventCreate(&ev);
-    if ((e = init_kernel_attributes(d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
+    cudaEventCreateWithFlags(&d->ev_const_use, cudaEventDisableTiming);
+    if ((e = init_kernel_attributes(cuda_device, d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
+    }
+    if (build_scan_constants(*d->casc, d->dense_stages, d->const_img) != cudaSuccess) {
+        fprintf(stderr, "ugdet: a dense-stage node has a corner count the scan evaluators do not cover\n"); ugd_destroy(up.release()); return UGD_ERR_UNSUPPORTED;
     }
     int rc = upload_cascade(d);
     if (rc != UGD_OK) { fprintf(stderr, "ugdet: %s\n", d->err.c_str()); ugd_destroy(up.release()); return rc; }
@@ -659,7 +777,15 @@ void ugd_destroy(ugd_detector* d) {
     cudaSetDevice(d->device);
     if (d->stream) cudaStreamSynchronize(d->stream);
     if (d->img_stream) cudaStreamSynchronize(d->img_stream);
-    { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
+    {   // the streams are idle: nothing of this detector reads the constant bank any more
+        std::lock_guard<std::mutex> lk(g_const_mu);
+        auto& us = g_bank[d->device & 63].users;
+        us.erase(std::remove(us.begin(), us.end(), d), us.end());
+    }
+    if (d->ev_const_use) cudaEventDestroy(d->ev_const_use);
+    comm_release(d);
+    d->shard.send.release(); d->shard.recv.release(); d->shard.packed.release();
+    if (d->shard.h_packed) cudaFreeHost(d->shard.h_packed);
     for (auto& kv : d->plans) kv.second->release();
     for (auto& kv : d->area_plans) kv.second->release();
     d->src_full.release(); d->area_dst.release();
@@ -687,7 +813,6 @@ int ugd_set_stream(ugd_detector* d, void* s) {
     if (!d) return UGD_ERR_ARG;
     if (d->stream) cudaStreamSynchronize(d->stream);
     d->stream = s ? static_cast<cudaStream_t>(s) : d->own_stream;
-    { std::lock_guard<std::mutex> lk(g_const_mu); if (g_const_owner == d) g_const_owner = nullptr; }
     return UGD_OK;
 }
 
@@ -743,6 +868,7 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
     if ((rc = get_area_plan(d, src_w, src_h, scan_w, scan_h, &ap))) return rc;
     if ((rc = get_plan(d, scan_w, scan_h, &dp))) return rc;
     d->ctr = ugd_counters{};
+    d->truncated = false;
     memset(d->ktime, 0, sizeof d->ktime); memset(d->klaunch, 0, sizeof d->klaunch);
     const size_t stight = (size_t)src_w * src_h * 3, dstride = round_up((size_t)scan_w * scan_h * 3, 256);
     // host frames in more than one group: the H2D copy of group g+1 overlaps the kernels of group g (two input buffers)
@@ -785,7 +911,7 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
             finish_group(d, dp->host, f0, std::min(d->max_batch, nframes - f0), out + (size_t)f0 * cap, cap, counts + f0, &overflow);
         if (overflow) { d->err = "per-frame candidate list overflowed (raise ugd_params.max_raw_per_frame)"; return UGD_ERR_CAPACITY; }
     }
-    return UGD_OK;
+    return truncation_status(d);
 }
 
 int ugd_submit_batch(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h, int cap) {
@@ -917,6 +1043,135 @@ int ugd_get_level_tilted(ugd_detector* d, int level, int32_t* T) {
     return UGD_OK;
 }
 
+// ---- multi-GPU: frames sharded over ranks, lists gathered to the root over NCCL ------------------------------
+int ugd_comm_unique_id(uint8_t* id) {
+    if (!id) return UGD_ERR_ARG;
+    NcclApi* n = nccl_api();
+    if (!n) return UGD_ERR_COMM;
+    ncclUniqueId u;
+    static_assert(sizeof u == UGD_COMM_ID_BYTES, "ncclUniqueId size");
+    if (n->GetUniqueId(&u) != ncclSuccess) return UGD_ERR_COMM;
+    memcpy(id, &u, sizeof u);
+    return UGD_OK;
+}
+
+int ugd_comm_init(ugd_detector* d, const uint8_t* id, int rank, int world) {
+    if (!d || !id || world < 1 || rank < 0 || rank >= world) return UGD_ERR_ARG;
+    NcclApi* n = nccl_api();
+    if (!n) { d->err = "NCCL is not available: libnccl.so.2 could not be loaded"; return UGD_ERR_COMM; }
+    CK(cudaSetDevice(d->device));
+    comm_release(d);
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof u);
+    NK(n->CommInitRank(&d->shard.comm, world, u, rank));
+    d->shard.own = true; d->shard.rank = rank; d->shard.world = world;
+    return UGD_OK;
+}
+
+int ugd_comm_attach(ugd_detector* d, void* nccl_comm, int rank, int world) {
+    if (!d || world < 1 || rank < 0 || rank >= world || (!nccl_comm && world > 1)) return UGD_ERR_ARG;
+    if (world > 1 && !nccl_api()) { d->err = "NCCL is not available: libnccl.so.2 could not be loaded"; return UGD_ERR_COMM; }
+    comm_release(d);
+    d->shard.comm = static_cast<ncclComm_t>(nccl_comm); d->shard.own = false; d->shard.rank = rank; d->shard.world = world;
+    return UGD_OK;
+}
+
+int ugd_comm_info(const ugd_detector* d, int* rank, int* world, int* nccl_version) {
+    if (!d) return UGD_ERR_ARG;
+    if (rank) *rank = d->shard.rank;
+    if (world) *world = d->shard.world;
+    if (nccl_version) { *nccl_version = 0; if (NcclApi* n = nccl_api()) n->GetVersion(nccl_version); }
+    return UGD_OK;
+}
+
+void ugd_shard_range(int nframes, int rank, int world, int* lo, int* hi) {
+    if (lo) *lo = (int)((int64_t)rank * nframes / world);
+    if (hi) *hi = (int)((int64_t)(rank + 1) * nframes / world);
+}
+
+int ugd_detect_batch_sharded(ugd_detector* d, const void* frames, int is_device, int is_bgr, int nframes, int w, int h,
+                             int slot_frames, int root, ugd_rect* out, int cap, int* counts) {
+    if (!d || !out || !counts || nframes < 0 || slot_frames < nframes || cap <= 0 || slot_frames <= 0) return UGD_ERR_ARG;
+    const int world = d->shard.world, rank = d->shard.rank;
+    if (root < 0 || root >= world) return UGD_ERR_ARG;
+    if (world > 1 && !d->shard.comm) { d->err = "no communicator: call ugd_comm_init or ugd_comm_attach first"; return UGD_ERR_ARG; }
+    if (d->pending.active) { d->err = "a submitted batch is still pending: call ugd_wait_batch first"; return UGD_ERR_ARG; }
+    CK(cudaSetDevice(d->device));
+    NcclApi* nc = world > 1 ? nccl_api() : nullptr;
+    const bool is_root = rank == root;
+    const size_t rect_bytes = (size_t)slot_frames * cap * sizeof(ugd_rect);
+    const size_t msg = rect_bytes + (size_t)slot_frames * 4;                     // one rank's message
+    const size_t nslots = (size_t)world * slot_frames;
+    const size_t hdr = round_up(4 + nslots * 4, 16);                             // packed: total, counts, then the rects
+    ugd_rect* lout = is_root ? out + (size_t)rank * slot_frames * cap : out;     // where this rank's own lists go
+    int* lcounts = is_root ? counts + (size_t)rank * slot_frames : counts;
+    int rc = UGD_OK;
+    if (world > 1) {
+        CK(d->shard.send.reserve(msg + 256));
+        CK(cudaMemsetAsync(d->shard.send.as<uint8_t>() + rect_bytes, 0xff, (size_t)slot_frames * 4, d->stream));   // absent frames: count -1
+        if (is_root) {
+            CK(d->shard.recv.reserve((size_t)world * msg + 256));
+            CK(d->shard.packed.reserve(hdr + nslots * cap * sizeof(ugd_rect) + 256));
+            if (hdr > d->shard.h_packed_cap * 4 || !d->shard.h_packed) {
+                if (d->shard.h_packed) cudaFreeHost(d->shard.h_packed);
+                d->shard.h_packed = nullptr;
+                CK(cudaMallocHost((void**)&d->shard.h_packed, hdr));
+                d->shard.h_packed_cap = hdr / 4;
+            }
+        }
+        d->shard.call = true; d->shard.slot_frames = slot_frames;
+    }
+    // everything of this rank's frames is enqueued (copies, kernels, result copies, the message for the gather) ...
+    if (nframes > 0)
+        rc = detect_body(d, frames, is_device != 0, is_bgr != 0, nframes, w, h, (size_t)w * (is_bgr ? 3 : 1), nullptr, cap, nullptr, true);
+    d->shard.call = false;
+    if (rc != UGD_OK) { drain(d); return rc; }
+    // ... then the exchange step on the same stream: every peer sends its slots to the root, which packs what
+    // arrived into one dense list before it crosses PCIe
+    if (world > 1) {
+        NK(nc->GroupStart());
+        if (is_root) {
+            for (int r = 0; r < world; ++r)
+                if (r != root) NK(nc->Recv(d->shard.recv.as<uint8_t>() + (size_t)r * msg, msg, ncclUint8, r, d->shard.comm, d->stream));
+        } else {
+            NK(nc->Send(d->shard.send.as<uint8_t>(), msg, ncclUint8, root, d->shard.comm, d->stream));
+        }
+        NK(nc->GroupEnd());
+        if (is_root) {
+            launch_pack_lists(d->shard.recv.as<uint8_t>(), msg, world, slot_frames, cap, root, d->shard.packed.as<int>(), hdr, d->stream);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(d->shard.h_packed, d->shard.packed.p, hdr, cudaMemcpyDeviceToHost, d->stream));
+        }
+    }
+    if (nframes > 0) rc = wait_pending(d, lout, lcounts);                        // synchronises the stream
+    else CK(cudaStreamSynchronize(d->stream));
+    if (rc != UGD_OK && rc != UGD_ERR_TRUNCATED) return rc;
+    if (is_root) {
+        for (int f = nframes; f < slot_frames; ++f) lcounts[f] = -1;
+        if (world > 1) {
+            const int total = d->shard.h_packed[0];
+            const int* pc = d->shard.h_packed + 1;
+            std::vector<ugd_rect> rects((size_t)std::max(total, 1));
+            if (total > 0) CK(cudaMemcpy(rects.data(), d->shard.packed.as<uint8_t>() + hdr, (size_t)total * sizeof(ugd_rect), cudaMemcpyDeviceToHost));
+            size_t at = 0;
+            for (int r = 0; r < world; ++r) {
+                if (r == root) continue;
+                for (int f = 0; f < slot_frames; ++f) {
+                    const size_t e = (size_t)r * slot_frames + f;
+                    const int n = pc[e];
+                    counts[e] = n;
+                    const int take = std::max(std::min(n, cap), 0);
+                    if (take) memcpy(out + e * cap, rects.data() + at, (size_t)take * sizeof(ugd_rect));
+                    at += (size_t)take;
+                    if (n > cap) rc = UGD_ERR_TRUNCATED;
+                }
+            }
+            if (rc == UGD_ERR_TRUNCATED) d->err = "a frame has more rectangles than cap: counts hold the true numbers, call again with a larger cap";
+        }
+    }
+    return rc;
+}
+
 const char* ugd_strerror(int code) {
     switch (code) {
         case UGD_OK: return "ok";
@@ -927,6 +1182,8 @@ const char* ugd_strerror(int code) {
         case UGD_ERR_CUDA: return "CUDA error";
         case UGD_ERR_CAPACITY: return "capacity exceeded";
         case UGD_ERR_NOMEM: return "out of memory";
+        case UGD_ERR_TRUNCATED: return "more rectangles than cap (true counts returned)";
+        case UGD_ERR_COMM: return "NCCL error";
         default: return "unknown error";
     }
 }

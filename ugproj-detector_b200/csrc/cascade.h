@@ -49,4 +49,4 @@ int load_cascade_xml(const std::string& path, Cascade& out, std::string& err);
 
 }  // namespace ugd
 
-struct ugd_cascade { ugd::Cascade c; };
+struct ugd_cascade { ugd::Cascade c; uint64_t uid = 0; };   // uid: process-unique, never reused (keys the constant bank)

@@ -28,6 +28,7 @@
 // val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, exact for the shipped cascades
 // (ugd_cascade_info.sum_exact), hence independent of summation order.
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "kernels.cuh"
@@ -135,7 +136,9 @@ static int sort_and_classify(DNode& d) {
     return nc == 6 ? 4 : nc == 8 ? 5 : nc == 9 ? 6 : nc == 12 ? 7 : 8;
 }
 
-cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st) {
+// Host image of everything k_scan reads from __constant__ for one (cascade, dense_stages) pair.  Built once per
+// detector (ugd_create); uploaded whenever the detector takes the device's constant bank over (api.cu: bind_constants).
+cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstImage& img) {
     const int nn = c.stage_first_node[dense_stages];
     if (nn > kMaxDenseNodes || dense_stages > kMaxDenseStages) return cudaErrorInvalidValue;
     ScanGeom g = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
@@ -147,7 +150,8 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
     }
     const int mode = scan_mode(c);
     const bool fast = mode == 1;
-    std::vector<DNode> dn((size_t)std::max(nn, 1));
+    std::vector<DNode>& dn = img.dn;
+    dn.assign((size_t)std::max(nn, 1), DNode{});
     for (int t = 0; t < c.ntrees(); ++t) {
         const int base = c.tree_first_node[t];
         for (int k = 0; k < c.tree_nnodes[t]; ++k) {
@@ -176,8 +180,10 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             } else { d.lval = h.left_val; d.rval = h.right_val; }
         }
     }
-    std::vector<double> base((size_t)std::max(dense_stages, 1), 0.0);
-    std::vector<int> ncf((size_t)std::max(dense_stages, 1) * 9, 0);
+    std::vector<double>& base = img.base;
+    std::vector<int>& ncf = img.ncf;
+    base.assign((size_t)std::max(dense_stages, 1), 0.0);
+    ncf.assign((size_t)std::max(dense_stages, 1) * 9, 0);
     if (mode == 2) {
         for (int s = 0; s < dense_stages; ++s)
             for (int t = c.stage_first_tree[s]; t < c.stage_first_tree[s] + c.stage_ntrees[s]; ++t)
@@ -204,14 +210,21 @@ cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream
             }
             ncf[s * 9 + 8] = n;
         }
+    img.first_node.assign(c.stage_first_node.begin(), c.stage_first_node.begin() + dense_stages + 1);
+    img.thr.assign(c.stage_thr.begin(), c.stage_thr.begin() + dense_stages);
+    img.geom = g;
+    return cudaSuccess;
+}
+
+// Asynchronous on `st`: the image belongs to the detector and outlives the copies.
+cudaError_t upload_scan_constants(const ScanConstImage& img, cudaStream_t st) {
     cudaError_t e;
-    if ((e = cudaMemcpyToSymbolAsync(c_dn, dn.data(), sizeof(DNode) * dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
-    if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, c.stage_first_node.data(), sizeof(int) * (size_t)(dense_stages + 1), 0, cudaMemcpyHostToDevice, st))) return e;
-    if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, c.stage_thr.data(), sizeof(float) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
-    if ((e = cudaMemcpyToSymbolAsync(c_stage_base, base.data(), sizeof(double) * (size_t)dense_stages, 0, cudaMemcpyHostToDevice, st))) return e;
-    if ((e = cudaMemcpyToSymbolAsync(c_stage_nc_first, ncf.data(), sizeof(int) * ncf.size(), 0, cudaMemcpyHostToDevice, st))) return e;
-    if ((e = cudaMemcpyToSymbolAsync(c_geom, &g, sizeof g, 0, cudaMemcpyHostToDevice, st))) return e;
-    return cudaStreamSynchronize(st);      // dn is a local: the copy must finish before it goes away
+    if ((e = cudaMemcpyToSymbolAsync(c_dn, img.dn.data(), sizeof(DNode) * img.dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, img.first_node.data(), sizeof(int) * img.first_node.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, img.thr.data(), sizeof(float) * img.thr.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_base, img.base.data(), sizeof(double) * img.base.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_stage_nc_first, img.ncf.data(), sizeof(int) * img.ncf.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    return cudaMemcpyToSymbolAsync(c_geom, &img.geom, sizeof img.geom, 0, cudaMemcpyHostToDevice, st);
 }
 
 __device__ __forceinline__ int near_thr(double sum, float thr) {
@@ -830,7 +843,7 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                 double sum = 0.0;
                 for (; st < nstages; ++st) {
                     const int nt = b.stage_ntrees[st];
-                    double part = 0.0;
+                    double part = 0.0, seq = 0.0;
                     if (MODE == 1) {
                         const int n0 = b.stage_first_node[st];
                         for (int t = lane; t < nt; t += 32) {
@@ -844,7 +857,8 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                     } else {
                         const int t0 = b.stage_first_tree[st];
                         unsigned visited = 0;
-                        for (int t = lane; t < nt; t += 32) {
+                        // walks tree t for this lane's window; returns the leaf it ends in
+                        auto tree_leaf = [&](int t) {
                             const int base = b.tree_first_node[t0 + t];
                             int at = 0;
                             float leaf;
@@ -859,12 +873,23 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                                 if (!go) break;
                                 at = go;
                             }
-                            part += (double)leaf;
+                            return leaf;
+                        };
+                        if (MODE == 0 && b.seq_sum) {   // (the exact evaluators, MODE 1 and 2, are only chosen for cascades with exact sums)
+                            // the stage sums of this cascade are not exactly representable (ugd_cascade_info.sum_exact == 0):
+                            // add the leaves one by one in file order, exactly as the oracle's loop does
+                            for (int c0 = 0; c0 < nt; c0 += 32) {
+                                const float leaf = c0 + lane < nt ? tree_leaf(c0 + lane) : 0.f;
+                                const int m = min(32, nt - c0);
+                                for (int i = 0; i < m; ++i) seq += (double)__shfl_sync(0xffffffffu, leaf, i);
+                            }
+                        } else {
+                            for (int t = lane; t < nt; t += 32) part += (double)tree_leaf(t);
                         }
                         visited = __reduce_add_sync(0xffffffffu, visited);
                         if (lane == 0) weak += visited;
                     }
-                    sum = warp_sum(part);
+                    sum = (MODE == 0 && b.seq_sum) ? seq : warp_sum(part);
                     const float thr = b.stage_thr[st];
                     if (lane == 0 && near_thr(sum, thr)) atomicAdd(&s_ctr[2], 1u);
                     if (sum < (double)thr) break;
@@ -885,7 +910,9 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     }
 }
 
-static int g_scan_smem = 0;
+// cudaFuncSetAttribute applies per device: the limit already granted is tracked per device and only ever raised.
+static std::mutex g_attr_mu;
+static int g_scan_smem[64] = {0};
 
 // Shared memory of one launch: the tile (x2 planes for tilted cascades), doubled when two buffers still leave
 // room for six blocks per SM next to the static arrays (the asynchronous prefetch of the next tile).
@@ -923,11 +950,13 @@ void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_
     }
 }
 
-cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted) {
+cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_tilted) {
     const ScanGeom g = make_scan_geom(win_w, win_h, has_tilted);
     int dbl;
     const int scan_smem = (int)std::max(scan_smem_bytes(g, 0, has_tilted, &dbl), scan_smem_bytes(g, 1, has_tilted, &dbl));
-    if (scan_smem > g_scan_smem) {
+    std::lock_guard<std::mutex> lk(g_attr_mu);
+    int& granted = g_scan_smem[device & 63];
+    if (scan_smem > granted) {
         const void* variants[9] = {(const void*)k_scan<0, false, 64>, (const void*)k_scan<0, true, 64>, (const void*)k_scan<1, false, 64>,
                                    (const void*)k_scan<1, true, 64>, (const void*)k_scan<2, false, 64>, (const void*)k_scan<2, true, 64>,
                                    (const void*)k_scan<0, false, 128>, (const void*)k_scan<1, false, 128>, (const void*)k_scan<2, false, 128>};
@@ -935,7 +964,7 @@ cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted) {
             cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
             if (e != cudaSuccess) return e;
         }
-        g_scan_smem = scan_smem;
+        granted = scan_smem;
     }
     return cudaSuccess;
 }

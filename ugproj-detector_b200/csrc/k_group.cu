@@ -209,4 +209,59 @@ void launch_group(const DevBufs& b, cudaStream_t st) {
     k_group<<<b.nframes, 256, 0, st>>>(b);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU gather, root side: the peers' fixed slots {rect[cap] per frame, then count per frame}
+// arrive over NVLink in `recv` ([world] messages); this kernel packs them into one dense list so that the
+// root's device-to-host copy moves the rectangles that exist, not world x frames x cap slots.
+//   packed = { int total; int counts[world * slot_frames]; ugd_rect rects[total] }   (rects 16-byte aligned)
+// One block; entries of rank `skip_rank` (the root's own frames: delivered by its local path) count as empty.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_pack_lists(const uint8_t* __restrict__ recv, size_t msg_bytes, int world, int slot_frames, int cap,
+                                                      int skip_rank, int* __restrict__ packed, size_t rect_off_bytes) {
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n = world * slot_frames;
+    ugd_rect* dst = reinterpret_cast<ugd_rect*>(reinterpret_cast<uint8_t*>(packed) + rect_off_bytes);
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int e0 = 0; e0 < n; e0 += 1024) {
+        const int e = e0 + tid;
+        int cnt = -1, take = 0;
+        const ugd_rect* src = nullptr;
+        if (e < n) {
+            const int r = e / slot_frames, f = e - r * slot_frames;
+            const uint8_t* msg = recv + (size_t)r * msg_bytes;
+            cnt = reinterpret_cast<const int*>(msg + (size_t)slot_frames * cap * sizeof(ugd_rect))[f];
+            src = reinterpret_cast<const ugd_rect*>(msg) + (size_t)f * cap;
+            if (r == skip_rank) cnt = -1;
+            take = max(min(cnt, cap), 0);
+            packed[1 + e] = cnt;
+        }
+        int incl = take;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            int v = s_warp[lane], w = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += u; }
+            s_warp[lane] = w - v;                       // exclusive over warps
+        }
+        __syncthreads();
+        const int off = s_base + s_warp[wid] + incl - take;
+        for (int k = 0; k < take; ++k) dst[off + k] = src[k];
+        __syncthreads();
+        if (tid == 1023) s_base = off + take;
+        __syncthreads();
+    }
+    if (tid == 0) packed[0] = s_base;
+}
+
+void launch_pack_lists(const uint8_t* recv, size_t msg_bytes, int world, int slot_frames, int cap, int skip_rank, int* packed,
+                       size_t rect_off_bytes, cudaStream_t st) {
+    k_pack_lists<<<1, 1024, 0, st>>>(recv, msg_bytes, world, slot_frames, cap, skip_rank, packed, rect_off_bytes);
+}
+
 }  // namespace ugd

@@ -2,6 +2,8 @@
 // equalizeHist, pyramid resize, integral / squared-integral images.  All integer, bit-exact with
 // the oracle.  These passes are HBM-bound: every kernel
 // moves 16-byte vectors per thread, consecutive threads touch consecutive addresses.
+#include <mutex>
+
 #include "kernels.cuh"
 
 namespace ugd {
@@ -453,10 +455,16 @@ static size_t tilted_smem(int max_w) { return (size_t)4 * (max_w + 3) * sizeof(u
 
 // Called once per plan (per frame size) on the detector's device: levels wider than ~3000 pixels need more
 // than the default 48 KB of dynamic shared memory.
-cudaError_t init_tilted_attributes(int max_w) {
-    const size_t need = tilted_smem(max_w);
+cudaError_t init_tilted_attributes(int device, int max_w) {
+    static std::mutex mu;
+    static int granted[64] = {0};                       // per device, only ever raised (a smaller plan must not lower it)
+    const int need = (int)tilted_smem(max_w);
     if (need <= 48 * 1024) return cudaSuccess;
-    return cudaFuncSetAttribute(k_tilted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    std::lock_guard<std::mutex> lk(mu);
+    if (need <= granted[device & 63]) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(k_tilted, cudaFuncAttributeMaxDynamicSharedMemorySize, need);
+    if (e == cudaSuccess) granted[device & 63] = need;
+    return e;
 }
 
 void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st) {

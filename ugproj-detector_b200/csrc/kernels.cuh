@@ -59,6 +59,7 @@ struct DevBufs {
     //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
     const uint4* nodeC; const uint32_t* nodeM;
     const uint4* nodeTA[2]; const uint4* nodeTB[2];   // A/B with byte offsets into the scan tile (grid step 1 / 2 layouts)
+    int seq_sum;                                      // stage sums are not exact in fp64: the late stages add their leaves in file order
     int word_off;                                     // the A/B offsets are in 32-bit words (two tiles / large windows: bytes do not fit 16 bits)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
     const int32_t* tree_first_node; const int32_t* stage_first_node;
@@ -94,7 +95,17 @@ int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset
 int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
 bool scan_word_offsets(const Cascade& c);                         // per-lane tables in words instead of bytes
 int scan_mode(const Cascade& c);
-cudaError_t upload_scan_constants(const Cascade& c, int dense_stages, cudaStream_t st);
+// Host image of the __constant__ data of one (cascade, dense_stages) pair; built once per detector.
+struct ScanConstImage {
+    std::vector<DNode> dn;
+    std::vector<int> first_node;                      // [dense_stages + 1]
+    std::vector<float> thr;                           // [dense_stages]
+    std::vector<double> base;                         // [dense_stages]
+    std::vector<int> ncf;                             // [dense_stages][9]
+    ScanGeom geom;
+};
+cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstImage& img);
+cudaError_t upload_scan_constants(const ScanConstImage& img, cudaStream_t st);   // asynchronous: img must outlive the copies
 
 // ---- INTER_AREA decimation to the scan size (k_area.cu) ----
 struct AreaTap { int32_t si; float a; };              // source index, weight
@@ -120,9 +131,11 @@ void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st);
-cudaError_t init_tilted_attributes(int max_w);
+cudaError_t init_tilted_attributes(int device, int max_w);
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
 void launch_group(const DevBufs& b, cudaStream_t st);
-cudaError_t init_kernel_attributes(int win_w, int win_h, bool has_tilted);
+void launch_pack_lists(const uint8_t* recv, size_t msg_bytes, int world, int slot_frames, int cap, int skip_rank, int* packed,
+                       size_t rect_off_bytes, cudaStream_t st);
+cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_tilted);
 
 }  // namespace ugd

@@ -32,6 +32,18 @@ def unpack_slots(slots: np.ndarray):
     return [slots[i, 1:1 + min(int(slots[i, 0, 0]), cap)].copy() for i in range(slots.shape[0])]
 
 
+def init_comm(det, rank: int, world: int):
+    """Gives the detector its own NCCL communicator (ugd_comm_init): rank 0 draws the unique id through the library and
+    torch.distributed -- the harness's plumbing, any backend -- carries the 128 bytes to the other ranks.  The gather
+    itself then runs inside libugdet.so (ugd_detect_batch_sharded), not through torch."""
+    import torch.distributed as dist
+    from . import comm_unique_id
+    box = [comm_unique_id() if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(box, src=0)
+    det.comm_init(box[0], rank, world)
+
+
 def gather_to_rank0(local_slots, world: int, rank: int, max_frames: int):
     """torch.distributed gather of slot tensors to rank 0 (NCCL on GPUs, gloo on CPU).
     local_slots: torch int32 tensor [F_r, cap+1, 4] (F_r may differ by one between ranks; padded to
