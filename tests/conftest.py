@@ -82,33 +82,57 @@ def pass_everything_cascade(out_path, win=(20, 20)):
     return str(out_path)
 
 
-def inexact_cascade(path, out_path, every=4):
-    """A copy of an old-format stump cascade with extra stumps whose leaves are tiny (~1e-9, full 24-bit mantissas)
-    at the head of every stage and after every `every`-th tree: decisions barely move, but the exponent spread of the
-    leaves now exceeds what an fp64 sum holds exactly, so ugd_cascade_info.sum_exact is 0 and the low bits of a stage
-    sum depend on the order of addition -- the engine must add the leaves in file order, like the oracle and cv2."""
-    import re
-    text = open(path).read()
-    k = [0]
+def old_format_xml(f, extra_tree=None):
+    """Writes a FlatCascade (oracle.cascade_xml.load_cascade: either XML format) back out as an old-format
+    (opencv-haar-classifier) file.  extra_tree(stage, k) -> XML of an extra tree to insert before tree k of the stage
+    (k == ntrees: at the end), or None."""
+    import numpy as np
+    out = ['<?xml version="1.0"?>', "<opencv_storage>", '<cascade type_id="opencv-haar-classifier">',
+           f"<size>{f.win_w} {f.win_h}</size>", "<stages>"]
+    for s in range(f.nstages):
+        out.append("<_><!-- stage --><trees>")
+        nt = int(f.stage_ntrees[s])
+        for k, t in enumerate(range(f.stage_first_tree[s], f.stage_first_tree[s] + nt)):
+            if extra_tree and extra_tree(s, k):
+                out.append(extra_tree(s, k))
+            out.append("<_>")
+            for j in range(f.tree_nnodes[t]):
+                n = f.tree_first_node[t] + j
+                out.append("<_><feature><rects>")
+                for r in range(3):
+                    if f.node_weights[n, r] != 0:
+                        x, y, w, h = f.node_rects[n, r]
+                        out.append(f"<_>{x} {y} {w} {h} {float(f.node_weights[n, r])!r}</_>")
+                out.append(f"</rects><tilted>{int(f.node_tilted[n])}</tilted></feature><threshold>{float(f.node_thr[n])!r}</threshold>")
+                out.append(f"<left_node>{f.node_left[n]}</left_node>" if f.node_left[n] else f"<left_val>{float(f.node_left_val[n])!r}</left_val>")
+                out.append(f"<right_node>{f.node_right[n]}</right_node>" if f.node_right[n] else f"<right_val>{float(f.node_right_val[n])!r}</right_val>")
+                out.append("</_>")
+            out.append("</_>")
+        if extra_tree and extra_tree(s, nt):
+            out.append(extra_tree(s, nt))
+        thr = float(np.float32(f.stage_thr[s]))          # already f32(xml) - 1e-5f
+        out.append(f"</trees><stage_threshold>{thr!r}</stage_threshold><parent>{s - 1}</parent><next>-1</next></_>")
+    out += ["</stages>", "</cascade>", "</opencv_storage>"]
+    return "\n".join(out)
 
-    def tiny():
-        k[0] += 1
-        a, b = 1.2345678e-9 * (1.0 + 0.37 * (k[0] % 11)), 2.7182818e-9 * (1.0 + 0.21 * (k[0] % 7))
+
+def inexact_cascade(path, out_path, every=4):
+    """A copy of a stump cascade (either XML format in, old format out) with extra stumps whose leaves are tiny (~1e-9,
+    full 24-bit mantissas) at the head of every stage and after every `every`-th tree: decisions barely move, but the
+    exponent spread of the leaves now exceeds what an fp64 sum holds exactly, so ugd_cascade_info.sum_exact is 0 and
+    the low bits of a stage sum depend on the order of addition -- the engine must add the leaves in file order, like
+    the oracle and cv2."""
+    from oracle.cascade_xml import load_cascade
+    f = load_cascade(path)
+
+    def tiny(s, k):
+        if k % every:
+            return None
+        i = 131 * s + k
+        a, b = 1.2345678e-9 * (1.0 + 0.37 * (i % 11)), 2.7182818e-9 * (1.0 + 0.21 * (i % 7))
         return ("<_><_><feature><rects><_>%d %d 6 4 -1.</_><_>%d %d 3 4 2.</_></rects><tilted>0</tilted></feature>"
                 "<threshold>%.6f</threshold><left_val>%.9e</left_val><right_val>%.9e</right_val></_></_>"
-                % (k[0] % 9, k[0] % 7, k[0] % 9, k[0] % 7, 0.001 * (k[0] % 5 - 2), a, b))
-    out, pos, ntree = [], 0, 0
-    for m in re.finditer(r"<trees>|</_>\s*</_>(?=\s*(?:<!--[^>]*-->\s*)?(?:<_>|</trees>))", text):
-        out.append(text[pos:m.end()])
-        pos = m.end()
-        if m.group(0) == "<trees>":
-            ntree = 0
-            out.append(tiny())
-        else:
-            ntree += 1
-            if ntree % every == 0:
-                out.append(tiny())
-    out.append(text[pos:])
+                % (i % 9, i % 7, i % 9, i % 7, 0.001 * (i % 5 - 2), a, b))
     with open(out_path, "w") as fh:
-        fh.write("".join(out))
+        fh.write(old_format_xml(f, tiny))
     return str(out_path)

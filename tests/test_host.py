@@ -11,7 +11,7 @@ import textwrap
 import numpy as np
 import pytest
 
-from conftest import CASCADES, ROOT, all_cv2_haar_cascades
+from conftest import CASCADES, ROOT, all_cv2_haar_cascades, old_format_xml
 
 FIELDS = ["stage_first_tree", "stage_ntrees", "stage_thr", "tree_first_node", "tree_nnodes", "node_rects",
           "node_weights", "node_thr", "node_left", "node_right", "node_left_val", "node_right_val", "node_tilted"]
@@ -56,32 +56,6 @@ def test_xml_loader_reads_every_cv2_haar_cascade(ug):
     assert ntilted >= 9
 
 
-def _old_format_xml(f):
-    """Writes a FlatCascade back out as an old-format (opencv-haar-classifier) file."""
-    out = ['<?xml version="1.0"?>', "<opencv_storage>", '<cascade type_id="opencv-haar-classifier">',
-           f"<size>{f.win_w} {f.win_h}</size>", "<stages>"]
-    for s in range(f.nstages):
-        out.append("<_><!-- stage --><trees>")
-        for t in range(f.stage_first_tree[s], f.stage_first_tree[s] + f.stage_ntrees[s]):
-            out.append("<_>")
-            for k in range(f.tree_nnodes[t]):
-                n = f.tree_first_node[t] + k
-                out.append("<_><feature><rects>")
-                for r in range(3):
-                    if f.node_weights[n, r] != 0:
-                        x, y, w, h = f.node_rects[n, r]
-                        out.append(f"<_>{x} {y} {w} {h} {float(f.node_weights[n, r])!r}</_>")
-                out.append(f"</rects><tilted>0</tilted></feature><threshold>{float(f.node_thr[n])!r}</threshold>")
-                out.append(f"<left_node>{f.node_left[n]}</left_node>" if f.node_left[n] else f"<left_val>{float(f.node_left_val[n])!r}</left_val>")
-                out.append(f"<right_node>{f.node_right[n]}</right_node>" if f.node_right[n] else f"<right_val>{float(f.node_right_val[n])!r}</right_val>")
-                out.append("</_>")
-            out.append("</_>")
-        thr = float(np.float32(f.stage_thr[s]))          # already f32(xml) - 1e-5f
-        out.append(f"</trees><stage_threshold>{thr!r}</stage_threshold><parent>{s - 1}</parent><next>-1</next></_>")
-    out += ["</stages>", "</cascade>", "</opencv_storage>"]
-    return "\n".join(out)
-
-
 def test_old_format_loader_roundtrip(ug, tmp_path):
     """Old-format reader exercised without the reference tree: new-format cascade -> old-format text ->
     product loader; node data must come back bit for bit (stage thresholds lose 1e-5f once more)."""
@@ -89,7 +63,7 @@ def test_old_format_loader_roundtrip(ug, tmp_path):
     from oracle.cascade_xml import load_cascade
     f = load_cascade(cv2.data.haarcascades + "haarcascade_frontalface_alt2.xml")
     p = tmp_path / "old.xml"
-    p.write_text(_old_format_xml(f))
+    p.write_text(old_format_xml(f))
     c = ug.Cascade(str(p))
     d = c.dump()
     assert c.info.old_format == 1 and c.info.max_tree_nodes == 2

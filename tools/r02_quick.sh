@@ -1,0 +1,15 @@
+#!/bin/bash
+# quick GPU check of a k_scan change: the decision-level parity tests, then the headline bench without the legs
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q -k "decisions or every_cv2 or stage_map or inexact or golden or two_cascades or properties" > gpurun_out/quick_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/quick_pytest.log
+python bench.py --steps 5 --warmup 3 --no-configs > gpurun_out/quick_bench.json 2> gpurun_out/quick_bench.err; echo "bench rc=$?"
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/quick_bench.json'))
+print('value',round(d['value'],1),'e2e',round(d['e2e']['value'],1),'pageable',round(d['e2e_pageable']['value'],1),'parity',d['parity']['mismatches'],'/',d['parity']['frames_checked'])
+print('roofline frac',round(d['roofline']['frac'],4),'peak',round(d['roofline']['peak'],0),'nominal frac',round(d['roofline']['frac_of_nominal'],4))
+print({k:round(v['ms_per_launch'],4) for k,v in d['kernels'].items()})
+PY
+for c in alt2 default alt_tree; do python bench.py --steps 3 --warmup 3 --no-configs --no-cpu-baseline --cascade $c 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print('$c', round(d['value'],1), round(d['kernels']['k_scan']['ms_per_launch'],3))"; done

@@ -82,6 +82,7 @@ struct ugd_detector {
     std::map<std::vector<int>, std::unique_ptr<DevAreaPlan>> area_plans;
     DevPtr src_full, area_dst;                        // full-size input frames / standalone resize output
     // cascade on device
+    DevPtr qbase;
     DevPtr nodeC, nodeM, nodeTA[2], nodeTB[2], st_first_tree, st_ntrees, st_thr, tree_first_node, st_first_node;
     // frame buffers
     DevPtr bgr, gray_raw, gray_eq, mask, hist, pyr, S, SQ, T, carryS, carryQ, raw, rawsum,
@@ -227,6 +228,7 @@ int upload_cascade(ugd_detector* d) {
                              [&](int a, int b) { return c.corners[a].nc < c.corners[b].nc; });
     const ScanGeom geom = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
     const bool words = scan_word_offsets(c);
+    const bool exact_stumps = scan_mode(c) == 1;
     std::vector<uint4> B(c.nnodes()), C(c.nnodes()), TA[2], TB[2];
     for (int si = 0; si < 2; ++si) { TA[si].resize(c.nnodes()); TB[si].resize(c.nnodes()); }
     std::vector<uint32_t> M(c.nnodes());
@@ -257,6 +259,11 @@ int upload_cascade(ugd_detector* d) {
         }
         uint32_t thr, lv, rv;
         memcpy(&thr, &h.thr, 4); memcpy(&lv, &h.left_val, 4); memcpy(&rv, &h.right_val, 4);
+        if (exact_stumps) {                           // the group evaluator adds (left - right) where a node goes left: see add_if_lt
+            const double d128 = ((double)h.left_val - (double)h.right_val) * 128.0;
+            uint64_t u; memcpy(&u, &d128, 8);
+            lv = (uint32_t)u; rv = (uint32_t)(u >> 32);
+        }
         C[i] = make_uint4(cf[8] | cf[9] << 8 | cf[10] << 16 | cf[11] << 24, thr, lv, rv);
         M[i] = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16;
     }
@@ -272,6 +279,9 @@ int upload_cascade(ugd_detector* d) {
     if ((rc = upload(d, d->st_thr, c.stage_thr))) return rc;
     if ((rc = upload(d, d->tree_first_node, c.tree_first_node))) return rc;
     if ((rc = upload(d, d->st_first_node, c.stage_first_node))) return rc;
+    std::vector<double> qbase;
+    stage_right_sums(c, qbase);
+    if ((rc = upload(d, d->qbase, qbase))) return rc;
     CK(cudaStreamSynchronize(d->stream));
     return UGD_OK;
 }
@@ -383,6 +393,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.stumps_only = c.max_tree_nodes == 1;
     b.fast_scan = scan_mode(c); b.word_off = scan_word_offsets(c) ? 1 : 0;
     b.seq_sum = c.sum_exact ? 0 : 1;
+    b.qbase = d->qbase.as<double>();
     { static const int kmin = getenv("UGD_SCAN_KMIN") ? atoi(getenv("UGD_SCAN_KMIN")) : 2; b.scan_kmin = std::max(kmin, 1); }   // 2: measured optimum (1: -2 %, 3: -3 %, 4: -8 %)
     b.levels = dp->levels.as<LevelInfo>(); b.xtab = dp->xtab.as<uint32_t>(); b.ytab = dp->ytab.as<uint32_t>();
     b.nodeC = d->nodeC.as<uint4>();
@@ -732,7 +743,7 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     d->device = cuda_device; d->max_w = max_w; d->max_h = max_h; d->max_batch = max_batch;
     d->rawcap = d->prm.max_raw_per_frame > 0 ? (int)round_up((size_t)d->prm.max_raw_per_frame, 4) : 8192;
     // in-tile stages: default 8 (measured optimum for frontalface_alt at 720p), bounded by the __constant__ node budget
-    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 8;
+    int D = d->prm.dense_stages > 0 ? d->prm.dense_stages : 9;     // r02: 9 measured best on alt / alt_tree, equal to 8..10 on alt2 / default
     if (const char* e = getenv("UGD_TILE_MIN")) d->tile_min = atoi(e);
     D = std::min(D, std::min(d->casc->nstages(), kMaxDenseStages));
     while (D > 1 && d->casc->stage_first_node[D] > kMaxDenseNodes) --D;
@@ -789,7 +800,7 @@ void ugd_destroy(ugd_detector* d) {
     for (auto& kv : d->plans) kv.second->release();
     for (auto& kv : d->area_plans) kv.second->release();
     d->src_full.release(); d->area_dst.release();
-    DevPtr* all[] = {&d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+    DevPtr* all[] = {&d->qbase, &d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ, &d->T,
                      &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in, &d->S2, &d->SQ2, &d->T2, &d->mask2};

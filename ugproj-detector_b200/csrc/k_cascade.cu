@@ -28,18 +28,25 @@
 // val = f32(float(r) * vnf); stage sums are fp64 sums of fp32 leaves, exact for the shipped cascades
 // (ugd_cascade_info.sum_exact), hence independent of summation order.
 #include <algorithm>
+#include <cmath>
+#include <cstring>
 #include <mutex>
 #include <vector>
 
 #include "kernels.cuh"
 
+#ifndef UGD_DADD_PRED
+#define UGD_DADD_PRED 0                   // 1: conditional stage-sum add written as a predicated DADD -- ptxas turns it into DADD + 2 FSEL (4 instructions); 0: FSET.BF mask + DFMA (3)
+#endif
+
 namespace ugd {
 
-__constant__ DNode c_dn[kMaxDenseNodes];
+__constant__ DNodeL c_dn[2][kMaxDenseNodes];                  // in-tile nodes, one table per tile layout (grid step 1 / 2)
+__constant__ int4 c_coef[kMaxDenseNodes];                     // their coefficients as 12 int8 (only nodes outside the four patterns read them)
 __constant__ int c_stage_first_node[kMaxDenseStages + 1];   // first in-tile node of stage s (s <= dense_stages)
 __constant__ float c_stage_thr[kMaxDenseStages];
 __constant__ double c_stage_base[kMaxDenseStages];
-__constant__ int c_stage_nc_first[kMaxDenseStages][9];      // exact stump evaluator: first node of each evaluator class (4 patterns, then 6 / 8 / 9 / 12 corners), end
+__constant__ int4 c_stage_nc_first[kMaxDenseStages][3];      // exact stump evaluator: first node of each evaluator class (4 patterns, then 6 / 8 / 9 / 12 corners), end
 __constant__ ScanGeom c_geom;
 
 // Tile pitches are chosen so that the bank shift between consecutive window rows, (step * pitch) mod 32,
@@ -150,8 +157,7 @@ cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstIm
     }
     const int mode = scan_mode(c);
     const bool fast = mode == 1;
-    std::vector<DNode>& dn = img.dn;
-    dn.assign((size_t)std::max(nn, 1), DNode{});
+    std::vector<DNode> dn((size_t)std::max(nn, 1), DNode{});
     for (int t = 0; t < c.ntrees(); ++t) {
         const int base = c.tree_first_node[t];
         for (int k = 0; k < c.tree_nnodes[t]; ++k) {
@@ -168,7 +174,7 @@ cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstIm
             d.meta = (uint32_t)cn.nc | (uint32_t)h.left << 8 | (uint32_t)h.right << 16 |
                      (k == c.tree_nnodes[t] - 1 ? 1u << 24 : 0u);
             d.thr = h.thr;
-            if (mode == 1) d.delta = ((double)h.left_val - (double)h.right_val) * 128.0;   // see add_if_lt
+            if (mode == 1) d.delta = ((double)h.left_val - (double)h.right_val) * (UGD_DADD_PRED ? 1.0 : 128.0);   // see add_if_lt
             else if (mode == 2) {
                 // tree value = cr + [root takes its leaf](root leaf - cr) + [root takes the child and child goes left](cl - cr)
                 const HostNode& kid = c.nodes[base + 1];
@@ -183,7 +189,7 @@ cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstIm
     std::vector<double>& base = img.base;
     std::vector<int>& ncf = img.ncf;
     base.assign((size_t)std::max(dense_stages, 1), 0.0);
-    ncf.assign((size_t)std::max(dense_stages, 1) * 9, 0);
+    ncf.assign((size_t)std::max(dense_stages, 1) * 12, 0);
     if (mode == 2) {
         for (int s = 0; s < dense_stages; ++s)
             for (int t = c.stage_first_tree[s]; t < c.stage_first_tree[s] + c.stage_ntrees[s]; ++t)
@@ -205,21 +211,45 @@ cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstIm
             std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<int, DNode>& x, const std::pair<int, DNode>& y) { return x.first < y.first; });
             int n = a;
             for (int k = 0; k < 8; ++k) {
-                ncf[s * 9 + k] = n;
+                ncf[s * 12 + k] = n;
                 while (n < z && keyed[n - a].first == k) { dn[n] = keyed[n - a].second; ++n; }
             }
-            ncf[s * 9 + 8] = n;
+            ncf[s * 12 + 8] = n;
         }
+    // device form: one 64-byte node per tile layout (offsets, then {thr, meta, delta} as one 16-byte word) + int8 coefficients
+    for (int si = 0; si < 2; ++si) {
+        img.dn[si].assign(dn.size(), DNodeL{});
+        for (size_t n = 0; n < dn.size(); ++n) {
+            DNodeL& o = img.dn[si][n];
+            memcpy(o.off, dn[n].off[si], sizeof o.off);
+            o.thr = dn[n].thr; o.meta = dn[n].meta; o.delta = dn[n].delta;
+        }
+    }
+    img.coef.assign(dn.size(), make_int4(0, 0, 0, 0));
+    for (size_t n = 0; n < dn.size(); ++n) {
+        int8_t c8[16] = {0};
+        for (int j = 0; j < 12; ++j) c8[j] = (int8_t)dn[n].coef[j];
+        memcpy(&img.coef[n], c8, 16);
+    }
     img.first_node.assign(c.stage_first_node.begin(), c.stage_first_node.begin() + dense_stages + 1);
     img.thr.assign(c.stage_thr.begin(), c.stage_thr.begin() + dense_stages);
     img.geom = g;
     return cudaSuccess;
 }
 
+// Sum of the right leaves of every stage: the exact stump evaluators add (left - right) where a node goes left.
+void stage_right_sums(const Cascade& c, std::vector<double>& qbase) {
+    qbase.assign((size_t)c.nstages(), 0.0);
+    for (int st = 0; st < c.nstages(); ++st)
+        for (int n = c.stage_first_node[st]; n < c.stage_first_node[st + 1]; ++n) qbase[st] += (double)c.nodes[n].right_val;
+}
+
 // Asynchronous on `st`: the image belongs to the detector and outlives the copies.
 cudaError_t upload_scan_constants(const ScanConstImage& img, cudaStream_t st) {
     cudaError_t e;
-    if ((e = cudaMemcpyToSymbolAsync(c_dn, img.dn.data(), sizeof(DNode) * img.dn.size(), 0, cudaMemcpyHostToDevice, st))) return e;
+    for (int si = 0; si < 2; ++si)
+        if ((e = cudaMemcpyToSymbolAsync(c_dn, img.dn[si].data(), sizeof(DNodeL) * img.dn[si].size(), sizeof(DNodeL) * kMaxDenseNodes * (size_t)si, cudaMemcpyHostToDevice, st))) return e;
+    if ((e = cudaMemcpyToSymbolAsync(c_coef, img.coef.data(), sizeof(int4) * img.coef.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_first_node, img.first_node.data(), sizeof(int) * img.first_node.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_thr, img.thr.data(), sizeof(float) * img.thr.size(), 0, cudaMemcpyHostToDevice, st))) return e;
     if ((e = cudaMemcpyToSymbolAsync(c_stage_base, img.base.data(), sizeof(double) * img.base.size(), 0, cudaMemcpyHostToDevice, st))) return e;
@@ -227,43 +257,46 @@ cudaError_t upload_scan_constants(const ScanConstImage& img, cudaStream_t st) {
     return cudaMemcpyToSymbolAsync(c_geom, &img.geom, sizeof img.geom, 0, cudaMemcpyHostToDevice, st);
 }
 
-__device__ __forceinline__ int near_thr(double sum, float thr) {
-    return fabs(sum - (double)thr) <= 1e-5 * fabs((double)thr);
+__device__ __forceinline__ int near_thr(double sum, double thr, double eps) { return fabs(sum - thr) <= eps; }
+
+// ---- in-tile evaluators --------------------------------------------------------------------------------------------
+// `t` points at a window's origin inside the shared tile; node data is warp-uniform and comes from the constant bank
+// through the uniform datapath (LDCU.128: four offsets, or {thr, meta, delta}, per instruction); the node pointer is
+// walked, never recomputed.  K windows per lane share every node fetch.
+__device__ __forceinline__ int tile_at(const char* t, int off) { return *reinterpret_cast<const int*>(t + off); }
+__device__ __forceinline__ int coef_of(const int4& c, int j) {
+    const int w = j < 4 ? c.x : j < 8 ? c.y : c.z;
+    return (int)(int8_t)(w >> (8 * (j & 3)));
 }
 
-// One in-tile stage for one window.  `t` points at the window's origin inside the shared tile; the
-// loop and every node field are warp-uniform, so node data is broadcast from the constant bank.
-#define TILE_AT(cf, of) ((cf) * *reinterpret_cast<const int*>(t + (of)))
-// feature response r of one node: two independent IMAD chains, extra corners behind uniform branches
-__device__ __forceinline__ int node_resp(const DNode& d, int si, const char* __restrict__ t) {
-    const int4* o4 = reinterpret_cast<const int4*>(d.off[si]);
-    const int4* c4 = reinterpret_cast<const int4*>(d.coef);
-    const int4 o0 = o4[0], k0 = c4[0], o1 = o4[1], k1 = c4[1];
-    int a = TILE_AT(k0.x, o0.x) + TILE_AT(k0.y, o0.y) + TILE_AT(k0.z, o0.z);
-    int c = TILE_AT(k0.w, o0.w) + TILE_AT(k1.x, o1.x) + TILE_AT(k1.y, o1.y);
+// feature response of one node (any corner count) for one window, coefficients from the table
+__device__ __forceinline__ int node_resp(const DNodeL& d, const int4 cf, const char* __restrict__ t) {
+    const int4* o4 = reinterpret_cast<const int4*>(d.off);
+    const int4 o0 = o4[0], o1 = o4[1];
+    int a = coef_of(cf, 0) * tile_at(t, o0.x) + coef_of(cf, 1) * tile_at(t, o0.y) + coef_of(cf, 2) * tile_at(t, o0.z);
+    int c = coef_of(cf, 3) * tile_at(t, o0.w) + coef_of(cf, 4) * tile_at(t, o1.x) + coef_of(cf, 5) * tile_at(t, o1.y);
     const int nc = d.meta & 255u;
     if (nc > 6) {
-        a += TILE_AT(k1.z, o1.z); c += TILE_AT(k1.w, o1.w);
+        a += coef_of(cf, 6) * tile_at(t, o1.z); c += coef_of(cf, 7) * tile_at(t, o1.w);
         if (nc > 8) {
-            const int4 o2 = o4[2], k2 = c4[2];
-            a += TILE_AT(k2.x, o2.x);
-            if (nc > 9) { c += TILE_AT(k2.y, o2.y); a += TILE_AT(k2.z, o2.z); c += TILE_AT(k2.w, o2.w); }
+            const int4 o2 = o4[2];
+            a += coef_of(cf, 8) * tile_at(t, o2.x);
+            if (nc > 9) { c += coef_of(cf, 9) * tile_at(t, o2.y); a += coef_of(cf, 10) * tile_at(t, o2.z); c += coef_of(cf, 11) * tile_at(t, o2.w); }
         }
     }
     return a + c;
 }
-#undef TILE_AT
 
 // Generic evaluator (any tree shape, plain fp64 sum of leaves in file order), one window per lane.
-__device__ __forceinline__ double tile_stage_generic(int s, int si, const char* __restrict__ t, float vnf) {
+__device__ __forceinline__ double tile_stage_generic(int s, const DNodeL* __restrict__ dn, const char* __restrict__ t, float vnf) {
     const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
     double sum = 0.0;
     float leaf = 0.f;
     int at = 0, k = 0;
     for (int n = n0; n < n1; ++n) {
-        const DNode& d = c_dn[n];
+        const DNodeL& d = dn[n];
         const uint32_t meta = d.meta;
-        const bool lt = __fmul_rn(__int2float_rn(node_resp(d, si, t)), vnf) < d.thr;
+        const bool lt = __fmul_rn(__int2float_rn(node_resp(d, c_coef[n], t)), vnf) < d.thr;
         if (at == k) {
             const int go = lt ? ((meta >> 8) & 255u) : ((meta >> 16) & 255u);
             leaf = lt ? d.lval : d.rval;
@@ -274,42 +307,56 @@ __device__ __forceinline__ double tile_stage_generic(int s, int si, const char* 
     return sum;
 }
 
-// Exact stump evaluator for K windows per lane (the same node is applied to the K windows, so its
-// constant-bank fetches are paid once per K feature evaluations).  Nodes of a stage are sorted by corner
-// count at upload time (sums are exact, hence order-independent), so NC is a compile-time constant.
-// sum += delta where val < thr, in two instructions: FSET.BF writes 1.0f / 0.0f, and those bits read as the HIGH word
-// of a double (low word 0) are 2^-7 / 0.0, so one DFMA with delta * 128 (stored that way at upload, exact) adds
-// delta or nothing -- rounded once, exactly like the DADD it replaces (the compiler's own choice for the
-// conditional add is DADD + two FSEL behind an FSETP).
+// sum += delta where val < thr, in two instructions: FSETP + a predicated DADD (rounded once, like the reference's
+// `sum += leaf`; the compiler's own choice for the conditional add is DADD + two FSEL behind the FSETP).  delta128 is the
+// leaf difference times 128 (kept that way for the mask form below, exact): UGD_DADD_PRED selects the predicated form,
+// which needs no zeroed low word for the mask.
 __device__ __forceinline__ void add_if_lt(double& sum, float val, float thr, double delta128) {
+#if UGD_DADD_PRED
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.rn.f64 %0, %0, %3;\n\t}" : "+d"(sum) : "f"(val), "f"(thr), "d"(delta128));
+#else
+    // FSET.BF writes 1.0f / 0.0f; those bits read as the HIGH word of a double (low word 0) are 2^-7 / 0.0, so one DFMA
+    // with delta * 128 adds delta or nothing
     asm("{\n\t.reg .f32 m;\n\t.reg .b32 z;\n\t.reg .f64 md;\n\tset.lt.f32.f32 m, %1, %2;\n\tmov.b32 z, 0;\n\t"
         "mov.b64 md, {z, m};\n\tfma.rn.f64 %0, md, %3, %0;\n\t}" : "+d"(sum) : "f"(val), "f"(thr), "d"(delta128));
+#endif
+}
+// sum += m * delta128 with m = 2^-7 or 0 given as the high word of a double
+__device__ __forceinline__ void add_masked(double& sum, unsigned m_hi, double delta128) {
+    asm("{\n\t.reg .b32 z;\n\t.reg .f64 md;\n\tmov.b32 z, 0;\n\tmov.b64 md, {z, %1};\n\tfma.rn.f64 %0, md, %2, %0;\n\t}" : "+d"(sum) : "r"(m_hi), "d"(delta128));
 }
 
-template <int NC, int K>
-__device__ __forceinline__ void stage_nodes(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-#pragma unroll 1
-    for (int n = n0; n < n1; ++n) {
-        const DNode& d = c_dn[n];
-        // 16-byte fetches (LDCU.128): four offsets / four coefficients / {thr, meta, delta} per instruction
-        const int4* o4 = reinterpret_cast<const int4*>(d.off[si]);
-        const int4* c4 = reinterpret_cast<const int4*>(d.coef);
-        int o[12], cf[12];
+// the NC tile offsets of a node, fetched 16 / 8 / 4 bytes at a time
+template <int NC>
+__device__ __forceinline__ void load_offsets(const DNodeL* d, int (&o)[12]) {
+    const int4* o4 = reinterpret_cast<const int4*>(d->off);
 #pragma unroll
-        for (int q = 0; q < (NC + 3) / 4; ++q) {
-            const int4 ov = o4[q], cv = c4[q];
-            o[4 * q] = ov.x; o[4 * q + 1] = ov.y; o[4 * q + 2] = ov.z; o[4 * q + 3] = ov.w;
-            cf[4 * q] = cv.x; cf[4 * q + 1] = cv.y; cf[4 * q + 2] = cv.z; cf[4 * q + 3] = cv.w;
-        }
+    for (int q = 0; q < NC / 4; ++q) { const int4 v = o4[q]; o[4 * q] = v.x; o[4 * q + 1] = v.y; o[4 * q + 2] = v.z; o[4 * q + 3] = v.w; }
+    if (NC % 4 >= 2) { const int2 v = *reinterpret_cast<const int2*>(d->off + (NC / 4) * 4); o[(NC / 4) * 4] = v.x; o[(NC / 4) * 4 + 1] = v.y; }
+    if (NC % 2) o[NC - 1] = d->off[NC - 1];
+}
+
+// Exact stump evaluator, nodes [d, e) of one coefficient pattern (PAT >= 0: compile-time coefficients, +-1 terms fold
+// into three-input adds) or of one corner count with coefficients from the table (PAT < 0).
+template <int PAT, int NC, int K>
+__device__ __forceinline__ void stage_run(const DNodeL* __restrict__ d, const DNodeL* __restrict__ e, const int4* __restrict__ cfp,
+                                          const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+#pragma unroll 1
+    for (; d != e; ++d) {
+        int o[12];
+        load_offsets<NC>(d, o);
+        int4 cf = make_int4(0, 0, 0, 0);
+        if (PAT < 0) { cf = *cfp; ++cfp; }
         int acc[K];
 #pragma unroll
         for (int k = 0; k < K; ++k) acc[k] = 0;
 #pragma unroll
-        for (int j = 0; j < NC; ++j) {                  // corner by corner: offset and coefficient fetched once for the K windows
+        for (int j = 0; j < NC; ++j) {                  // corner by corner: the offset is fetched once for the K windows
+            const int cj = PAT >= 0 ? pat_coef(PAT < 0 ? 0 : PAT, j) : coef_of(cf, j);
 #pragma unroll
-            for (int k = 0; k < K; ++k) acc[k] += cf[j] * *reinterpret_cast<const int*>(t[k] + o[j]);
+            for (int k = 0; k < K; ++k) acc[k] += cj * tile_at(t[k], o[j]);
         }
-        const int4 tail = *reinterpret_cast<const int4*>(&d.thr);
+        const int4 tail = *reinterpret_cast<const int4*>(&d->thr);          // {thr, meta, delta}: one 16-byte fetch
         const float thr = __int_as_float(tail.x);
         const double delta = __hiloint2double(tail.w, tail.z);
 #pragma unroll
@@ -317,54 +364,31 @@ __device__ __forceinline__ void stage_nodes(int n0, int n1, int si, const char* 
     }
 }
 
-// The same for nodes whose coefficient vector is pattern PAT: coefficients are compile-time constants.
-template <int PAT, int K>
-__device__ __forceinline__ void stage_nodes_pat(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-    constexpr int NC = pat_nc(PAT);
-#pragma unroll 1
-    for (int n = n0; n < n1; ++n) {
-        const DNode& d = c_dn[n];
-        const int32_t* o = d.off[si];
-        int acc[K];
-#pragma unroll
-        for (int k = 0; k < K; ++k) acc[k] = 0;
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-            const int oj = o[j];
-#pragma unroll
-            for (int k = 0; k < K; ++k) acc[k] += pat_coef(PAT, j) * *reinterpret_cast<const int*>(t[k] + oj);
-        }
-        const float thr = d.thr;
-        const double delta = d.delta;
-#pragma unroll
-        for (int k = 0; k < K; ++k) add_if_lt(sum[k], __fmul_rn(__int2float_rn(acc[k]), vnf[k]), thr, delta);
-    }
-}
-
 template <int K>
-__device__ __forceinline__ void tile_stage_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-    const int* f = c_stage_nc_first[s];
+__device__ __forceinline__ void tile_stage_k(int s, const DNodeL* __restrict__ dn, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    const int4 fa = c_stage_nc_first[s][0], fb = c_stage_nc_first[s][1];
+    const int f8 = c_stage_nc_first[s][2].x;
 #pragma unroll
     for (int k = 0; k < K; ++k) sum[k] = k == 0 ? c_stage_base[s] : sum[0];
-    stage_nodes_pat<0, K>(f[0], f[1], si, t, vnf, sum);
-    stage_nodes_pat<1, K>(f[1], f[2], si, t, vnf, sum);
-    if (kPatterns > 2) {
-        stage_nodes_pat<2, K>(f[2], f[3], si, t, vnf, sum);
-        stage_nodes_pat<3, K>(f[3], f[4], si, t, vnf, sum);
+    stage_run<0, 6, K>(dn + fa.x, dn + fa.y, nullptr, t, vnf, sum);
+    stage_run<1, 8, K>(dn + fa.y, dn + fa.z, nullptr, t, vnf, sum);
+    if (fa.z != fb.x) {                                 // centre-surround patterns: rare
+        stage_run<2, 9, K>(dn + fa.z, dn + fa.w, nullptr, t, vnf, sum);
+        stage_run<3, 9, K>(dn + fa.w, dn + fb.x, nullptr, t, vnf, sum);
     }
-    if (f[4] != f[8]) {                                 // nodes outside the four patterns: coefficients from the table
-        stage_nodes<6, K>(f[4], f[5], si, t, vnf, sum);
-        stage_nodes<8, K>(f[5], f[6], si, t, vnf, sum);
-        stage_nodes<9, K>(f[6], f[7], si, t, vnf, sum);
-        stage_nodes<12, K>(f[7], f[8], si, t, vnf, sum);
+    if (fb.x != f8) {                                   // nodes outside the four patterns: coefficients from the table
+        stage_run<-1, 6, K>(dn + fb.x, dn + fb.y, c_coef + fb.x, t, vnf, sum);
+        stage_run<-1, 8, K>(dn + fb.y, dn + fb.z, c_coef + fb.y, t, vnf, sum);
+        stage_run<-1, 9, K>(dn + fb.z, dn + fb.w, c_coef + fb.z, t, vnf, sum);
+        stage_run<-1, 12, K>(dn + fb.w, dn + f8, c_coef + fb.w, t, vnf, sum);
     }
 }
 
 // Exact evaluator for two-node trees (scan_mode 2), K windows per lane.  Corner counts differ from node to
 // node, so the extra corners sit behind warp-uniform branches (paid once per K windows).
 template <int K>
-__device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* const (&t)[K], int (&acc)[K]) {
-    const int32_t* o = d.off[si];
+__device__ __forceinline__ void node_resp_k(const DNodeL& d, const int4 cf, const char* const (&t)[K], int (&acc)[K]) {
+    const int32_t* o = d.off;
     const int nc = d.meta & 255u;
     const unsigned pat = (d.meta >> 26) & 3u;
 #pragma unroll
@@ -372,15 +396,15 @@ __device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* 
 #define PCORNER(P, j)                                                                               \
     {                                                                                               \
         const int oj = o[j];                                                                        \
-        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += pat_coef(P, j) * *reinterpret_cast<const int*>(t[k] + oj); \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += pat_coef(P, j) * tile_at(t[k], oj); \
     }
     if (pat == 1) { PCORNER(0, 0) PCORNER(0, 1) PCORNER(0, 2) PCORNER(0, 3) PCORNER(0, 4) PCORNER(0, 5) return; }
     if (pat == 2) { PCORNER(1, 0) PCORNER(1, 1) PCORNER(1, 2) PCORNER(1, 3) PCORNER(1, 4) PCORNER(1, 5) PCORNER(1, 6) PCORNER(1, 7) return; }
 #undef PCORNER
 #define CORNER(j)                                                                                   \
     {                                                                                               \
-        const int oj = o[j], cj = d.coef[j];                                                        \
-        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += cj * *reinterpret_cast<const int*>(t[k] + oj); \
+        const int oj = o[j], cj = coef_of(cf, j);                                                   \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) acc[k] += cj * tile_at(t[k], oj);             \
     }
     CORNER(0) CORNER(1) CORNER(2) CORNER(3) CORNER(4) CORNER(5)
     if (nc > 6) {
@@ -393,25 +417,23 @@ __device__ __forceinline__ void node_resp_k(const DNode& d, int si, const char* 
 #undef CORNER
 }
 
-// sum += m * delta128 with m = 2^-7 or 0 given as the high word of a double (see add_if_lt)
-__device__ __forceinline__ void add_masked(double& sum, unsigned m_hi, double delta128) {
-    asm("{\n\t.reg .b32 z;\n\t.reg .f64 md;\n\tmov.b32 z, 0;\n\tmov.b64 md, {z, %1};\n\tfma.rn.f64 %0, md, %2, %0;\n\t}" : "+d"(sum) : "r"(m_hi), "d"(delta128));
-}
-
 // (Pattern classes were tried here too -- pairs ordered by (root, child) pattern, nine loops: alt2 13.7 ms against 11.7
 // for this single loop; its stages hold 3 to 34 trees, too few per class to pay for nine loop set-ups.)
 template <int K>
-__device__ __forceinline__ void tree_pairs(int n0, int n1, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+__device__ __forceinline__ void tile_trees_k(int s, const DNodeL* __restrict__ dn, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) sum[k] = c_stage_base[s];
+    const int n0 = c_stage_first_node[s], n1 = c_stage_first_node[s + 1];
+    const int4* cf = c_coef + n0;
 #pragma unroll 1
-    for (int n = n0; n < n1; n += 2) {
-        const DNode& root = c_dn[n];
-        const DNode& kid = c_dn[n + 1];
+    for (const DNodeL* root = dn + n0; root != dn + n1; root += 2, cf += 2) {
+        const DNodeL& kid = root[1];
         int ar[K], ak[K];
-        node_resp_k<K>(root, si, t, ar);
-        node_resp_k<K>(kid, si, t, ak);
-        const unsigned flip = (root.meta >> 25) & 1u ? 0x3f800000u : 0u;     // the root's leaf is on its right: taken when NOT lt
-        const float thr_r = root.thr, thr_k = kid.thr;
-        const double d_r = root.delta, d_k = kid.delta;
+        node_resp_k<K>(*root, cf[0], t, ar);
+        node_resp_k<K>(kid, cf[1], t, ak);
+        const unsigned flip = (root->meta >> 25) & 1u ? 0x3f800000u : 0u;     // the root's leaf is on its right: taken when NOT lt
+        const float thr_r = root->thr, thr_k = kid.thr;
+        const double d_r = root->delta, d_k = kid.delta;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             // 1.0f / 0.0f masks (FSET.BF): the tree adds the root's leaf difference when the root takes its leaf,
@@ -425,17 +447,10 @@ __device__ __forceinline__ void tree_pairs(int n0, int n1, int si, const char* c
     }
 }
 
-template <int K>
-__device__ __forceinline__ void tile_trees_k(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-#pragma unroll
-    for (int k = 0; k < K; ++k) sum[k] = c_stage_base[s];
-    tree_pairs<K>(c_stage_first_node[s], c_stage_first_node[s + 1], si, t, vnf, sum);
-}
-
 template <int MODE, int K>
-__device__ __forceinline__ void stage_eval(int s, int si, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
-    if (MODE == 1) tile_stage_k<K>(s, si, t, vnf, sum);
-    else tile_trees_k<K>(s, si, t, vnf, sum);
+__device__ __forceinline__ void stage_eval(int s, const DNodeL* __restrict__ dn, const char* const (&t)[K], const float (&vnf)[K], double (&sum)[K]) {
+    if (MODE == 1) tile_stage_k<K>(s, dn, t, vnf, sum);
+    else tile_trees_k<K>(s, dn, t, vnf, sum);
 }
 
 __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scale, int rw, int rh, int x, int y, double sum) {
@@ -492,6 +507,30 @@ __device__ __forceinline__ int lane_resp(const DevBufs& b, const uint4* __restri
     return a + c;
 }
 
+// the same from node words already in registers (the group evaluator fetches a node once for several windows)
+template <bool WORDS>
+__device__ __forceinline__ int lane_resp_abc(const uint4& A, const uint4& B, uint32_t c8, uint32_t pb2, uint32_t nc) {
+    const uint32_t o01 = A.x + pb2, o23 = A.y + pb2, o45 = A.z + pb2;
+    int a = sx8(B.z, 0) * lds32(lo16<WORDS>(o01)) + sx8(B.z, 1) * lds32(hi16<WORDS>(o01)) + sx8(B.z, 2) * lds32(lo16<WORDS>(o23));
+    int c = sx8(B.z, 3) * lds32(hi16<WORDS>(o23)) + sx8(B.w, 0) * lds32(lo16<WORDS>(o45)) + sx8(B.w, 1) * lds32(hi16<WORDS>(o45));
+    if (nc > 6) {
+        const uint32_t o67 = A.w + pb2;
+        a += sx8(B.w, 2) * lds32(lo16<WORDS>(o67));
+        c += sx8(B.w, 3) * lds32(hi16<WORDS>(o67));
+        if (nc > 8) {
+            const uint32_t o89 = B.x + pb2;
+            a += sx8(c8, 0) * lds32(lo16<WORDS>(o89));
+            if (nc > 9) {
+                const uint32_t oab = B.y + pb2;
+                c += sx8(c8, 1) * lds32(hi16<WORDS>(o89));
+                a += sx8(c8, 2) * lds32(lo16<WORDS>(oab));
+                c += sx8(c8, 3) * lds32(hi16<WORDS>(oab));
+            }
+        }
+    }
+    return a + c;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
@@ -521,14 +560,15 @@ __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict_
 // Windows per lane that share a node fetch in the exact evaluators, and resident blocks per SM the register
 // budget is cut for.  Measured on B200 (alt, 720p, ms per 64 frames): K=4 / 4 blocks (64 regs) 10.7, K=4 / 5 blocks 11.2,
 // K=3 / 5 blocks 11.8, K=2 / 5 blocks 10.2, K=2 / 6 blocks (40 regs) 9.9, K=2 / 8 blocks (32 regs, spills) 10.8,
-// K=1 / 6 blocks 11.3: two windows per fetch already buy most of the amortisation (24.5 vs 22 instructions per
-// window and node), and the 12 extra warps per SM fill the issue slots the stage barriers leave empty.
+// K=1 / 6 blocks 11.3: two windows per fetch already buy most of the amortisation, and the 12 extra warps per SM
+// fill the issue slots the stage barriers leave empty.
 // Warps per block (NW): 16 warps on the same 16 x 128 tile (three blocks per SM, same 48 resident warps) measured 9.5 %
 // slower than 8 (9.78 vs 8.93 ms): half as many rounds per warp leaves fewer window pairs, and twice as many warps
 // wait at every end-of-stage barrier.
-#ifndef UGD_SCAN_KMAX
-#define UGD_SCAN_KMAX 2
+#ifndef UGD_QUEUE_GROUP
+#define UGD_QUEUE_GROUP 1
 #endif
+constexpr int kQueueGroup = UGD_QUEUE_GROUP;           // windows per warp that share a node fetch in the late-stage queue (exact stump cascades)
 #ifndef UGD_SCAN_MINBLOCKS
 #define UGD_SCAN_MINBLOCKS 6
 #endif
@@ -564,7 +604,7 @@ struct Live {
 
 template <int MODE, bool WORDS, int C, int NW = kScanWarps>
 __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarps / NW : 1536 / (NW * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
-    constexpr int R = kTileRows, KMAX = UGD_SCAN_KMAX;
+    constexpr int R = kTileRows;
     constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
     static_assert((C == 64 || C == 128) && R == 16 && R % NW == 0, "32 or 64 windows per bank class");
     extern __shared__ int s_tiles[];
@@ -583,6 +623,7 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     const int rect_w = Lg.rect_w, rect_h = Lg.rect_h;
     const uint32_t pos_off = Lg.pos_off;
     const int si = step - 1;
+    const DNodeL* __restrict__ dn = c_dn[si];
     const int TP = c_geom.TP[si], TCH = c_geom.TCH[si], TC = c_geom.TC[si], TR = c_geom.TR[si], SH = c_geom.SH[si];
     const int r0 = it.first;
     const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
@@ -593,9 +634,13 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
     if (tid < 5) s_ctr[tid] = 0;
     unsigned run_par = 0;                              // per owned row: parity of the stage-0 failure run ending just before the next segment
-    unsigned weak = 0;                                 // lane 0 of each warp tallies weak classifiers
+    // per-lane tallies, reduced once at the end of the block: evaluated | low variance << 16,  near a threshold | passed the
+    // variance test << 16 (a lane sees at most a few hundred windows of a block: 16 bits each are plenty)
+    unsigned cA = 0, cB = 0;
+    unsigned weak = 0;                                 // lane 0 of each warp: weak classifiers of stages >= 1
     const int nw0 = c_stage_first_node[1] - c_stage_first_node[0];
     const float thr0 = c_stage_thr[0];
+    const double thr0d = (double)thr0, eps0 = 1e-5 * fabs((double)thr0);
 
     // The tile buffer is double (dbl = 1) when shared memory allows: the next tile's patch is then copied
     // asynchronously while this tile is being evaluated, and its latency disappears behind the stages.
@@ -621,27 +666,33 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
             stage_tile<NW>(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
             if (Tp) stage_tile<NW>(nxt + TR * TP, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
         }
-        // ---- 2. variance normalisation + stage 0 + x-skip, row segment by row segment ----
+        // ---- 2. variance normalisation + stage 0 + x-skip: a warp owns R / NW rows of the tile and walks each in
+        //         segments of 32 windows; everything that depends on the row only is warp-uniform ----
 #pragma unroll 1
-        for (int seg = 0; seg < (R / NW) * SEG; ++seg) {
-            const int k = seg >> LSEG, h = seg & (SEG - 1);
+        for (int k = 0; k < R / NW; ++k) {
             const int rl = w + k * NW, row = r0 + rl;
             const bool row_valid = row < nyg;
-            {
+            const int y = row_valid ? row * step : 0;
+            // the four corners of the squared-integral sum over the window's inner (ow-2) x (oh-2) box, as four row pointers
+            const int32_t* qa = Q + ((y + 1) * P + 1);
+            const int32_t* qb = qa + (ow - 2);
+            const int32_t* qc = Q + ((y + oh - 1) * P + 1);
+            const int32_t* qd = qc + (ow - 2);
+            const char* trow = reinterpret_cast<const char*>(s_tile + (rl * step) * TP);
+            int run_in = (run_par >> k) & 1;           // only the parity of the run length matters
+#pragma unroll 1
+            for (int h = 0; h < SEG; ++h) {
+                if (xi0 + 32 * h >= nxg) break;        // warp-uniform: segment past the end of the row
                 const int c = 32 * h + lane, xi = xi0 + c;
-                if (xi0 + 32 * h >= nxg) continue;     // warp-uniform: segment past the end of the row
-                const int run_in = (run_par >> k) & 1;  // only the parity of the run length matters
                 const bool valid = row_valid && xi < nxg;
-                const int x = valid ? xi * step : 0, y = valid ? row * step : 0;
-                const char* t = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
+                const int x = valid ? xi * step : 0;
+                const char* t = trow + 4 * c;
                 float vnf = 1.f;
                 bool ok = false;
                 {
                     const int32_t* no = c_geom.norm_off[si];
-                    const int vs = *reinterpret_cast<const int*>(t + no[0]) - *reinterpret_cast<const int*>(t + no[1]) -
-                                   *reinterpret_cast<const int*>(t + no[2]) + *reinterpret_cast<const int*>(t + no[3]);
-                    const int32_t* q = Q + (size_t)y * P + x;
-                    const uint32_t vq = (uint32_t)q[P + 1] - (uint32_t)q[P + ow - 1] - (uint32_t)q[(oh - 1) * P + 1] + (uint32_t)q[(oh - 1) * P + ow - 1];
+                    const int vs = tile_at(t, no[0]) - tile_at(t, no[1]) - tile_at(t, no[2]) + tile_at(t, no[3]);
+                    const uint32_t vq = (uint32_t)qa[x] - (uint32_t)qb[x] - (uint32_t)qc[x] + (uint32_t)qd[x];
                     double nf = area * (double)vq - (double)vs * (double)vs;
                     if (nf > 0.0) {
                         nf = sqrt(nf);
@@ -653,36 +704,24 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                 double sum;
                 if (MODE) {
                     const char* t1[1] = {t}; const float v1[1] = {vnf}; double s1[1];
-                    stage_eval<MODE, 1>(0, si, t1, v1, s1);
+                    stage_eval<MODE, 1>(0, dn, t1, v1, s1);
                     sum = s1[0];
-                } else sum = tile_stage_generic(0, si, t, vnf);
-                const bool pass0 = !(sum < (double)thr0);
+                } else sum = tile_stage_generic(0, dn, t, vnf);
+                const bool pass0 = !(sum < thr0d);
                 // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
                 // ending at i-1 has even length (a failure is only seen at evaluated positions)
                 const bool f0 = valid && ok && !pass0;
                 const unsigned F = __ballot_sync(0xffffffffu, f0);
                 const unsigned inv = ~F & below;
                 const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
-                const int run_out = (F == 0xffffffffu) ? run_in + 32 : __clz((int)~F);
-                run_par = (run_par & ~(1u << k)) | ((unsigned)(run_out & 1) << k);
+                run_in = ((F == 0xffffffffu) ? run_in + 32 : __clz((int)~F)) & 1;
                 const bool evaluated = valid && !(run & 1);
-                const bool alive = evaluated && ok && pass0;
-                {
-                    const unsigned em = __ballot_sync(0xffffffffu, evaluated);
-                    const unsigned lm = __ballot_sync(0xffffffffu, evaluated && !ok);
-                    const unsigned s0 = __ballot_sync(0xffffffffu, evaluated && ok);
-                    const unsigned nm = __ballot_sync(0xffffffffu, evaluated && ok && near_thr(sum, thr0));
-                    if (lane == 0) {
-                        atomicAdd(&s_ctr[0], __popc(em));
-                        if (lm) atomicAdd(&s_ctr[1], __popc(lm));
-                        if (nm) atomicAdd(&s_ctr[2], __popc(nm));
-                        weak += __popc(s0) * (unsigned)nw0;
-                    }
-                }
-                if (map && valid) {
-                    if (!evaluated) map[row * nxg_pad + xi] = kMapSkip;
-                    else if (!ok) map[row * nxg_pad + xi] = kMapLowVar;
-                    else if (!pass0) map[row * nxg_pad + xi] = 0;
+                const bool varok = evaluated && ok;
+                const bool alive = varok && pass0;
+                cA += (evaluated ? 1u : 0u) + ((evaluated && !ok) ? 0x10000u : 0u);
+                cB += ((varok && near_thr(sum, thr0d, eps0)) ? 1u : 0u) + (varok ? 0x10000u : 0u);
+                if (map) {
+                    if (valid && !alive) map[row * nxg_pad + xi] = !evaluated ? kMapSkip : !ok ? kMapLowVar : (int16_t)0;
                 }
                 s_vnf[rl * C + c] = vnf;
                 if (alive) {
@@ -694,6 +733,7 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                     }
                 }
             }
+            run_par = (run_par & ~(1u << k)) | ((unsigned)run_in << k);
         }
         __syncthreads();
         // ---- 3. stage by stage on the per-class survivor masks ----
@@ -710,104 +750,66 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
             if (w == 0)                                 // masks of the stage before: nobody reads them any more
 #pragma unroll
                 for (int i = 0; i < NMW; ++i) s_alive[nxt2][i][lane] = 0;
-            const int nws = c_stage_first_node[s + 1] - c_stage_first_node[s];
             const float thr = c_stage_thr[s];
-            if (MODE) {
-                // exact evaluators: the rounds are dealt to the warps in runs of `per` (at least scan_kmin, so that
-                // late stages with fewer rounds than warps still pair windows up), KMAX consecutive rounds at
-                // once: the windows a lane holds share every node fetch
-                Live<NMW> mm = m;
-                const int per = max((rounds + NW - 1) / NW, b.scan_kmin);
-                const int g_beg = min(w * per, rounds), g_end = min(g_beg + per, rounds);
-                mm.skip(g_beg);
-                for (int g = g_beg; g < g_end; g += KMAX) {
-                    const int K = min(KMAX, g_end - g);
-                    int bit[4]; bool act[4]; const char* tw[4]; float vn[4]; double sum[4];
+            const double thrd = (double)thr, eps = 1e-5 * fabs((double)thr);
+            const bool last = s + 1 == nstages;         // block-uniform: the stage that accepts
+            if (tid == 0) weak += (unsigned)total * (unsigned)(c_stage_first_node[s + 1] - c_stage_first_node[s]);   // every live window runs the whole stage
+            // the rounds are dealt to the warps in runs of `per` (at least scan_kmin, so that late stages with fewer
+            // rounds than warps still pair windows up); a warp takes two consecutive rounds at once: the two windows
+            // a lane holds share every node fetch
+            Live<NMW> mm = m;
+            const int per = max((rounds + NW - 1) / NW, b.scan_kmin);
+            const int g_beg = min(w * per, rounds), g_end = min(g_beg + per, rounds);
+            mm.skip(g_beg);
+            for (int g = g_beg; g < g_end; g += MODE ? 2 : 1) {
+                const bool two = MODE != 0 && g + 1 < g_end;                   // warp-uniform
+                int bit0, bit1 = 0;
+                const bool act0 = mm.pop(bit0);
+                bool act1 = false;
+                if (two) act1 = mm.pop(bit1);
+                const int rl0 = bit0 >> LSEG, c0 = ((lane - SH * rl0) & 31) + ((bit0 & (SEG - 1)) << 5);
+                const int rl1 = bit1 >> LSEG, c1 = ((lane - SH * rl1) & 31) + ((bit1 & (SEG - 1)) << 5);
+                const char* tw0 = reinterpret_cast<const char*>(s_tile + (rl0 * step) * TP + c0);
+                const char* tw1 = reinterpret_cast<const char*>(s_tile + (rl1 * step) * TP + c1);
+                double sum0, sum1 = 0.0;
+                if (MODE == 0) {
+                    sum0 = tile_stage_generic(s, dn, tw0, s_vnf[rl0 * C + c0]);
+                } else if (two) {
+                    const char* t2[2] = {tw0, tw1}; const float v2[2] = {s_vnf[rl0 * C + c0], s_vnf[rl1 * C + c1]}; double s2[2];
+                    stage_eval<MODE ? MODE : 1, 2>(s, dn, t2, v2, s2);
+                    sum0 = s2[0]; sum1 = s2[1];
+                } else {
+                    const char* t1[1] = {tw0}; const float v1[1] = {s_vnf[rl0 * C + c0]}; double s1[1];
+                    stage_eval<MODE ? MODE : 1, 1>(s, dn, t1, v1, s1);
+                    sum0 = s1[0];
+                }
+                const bool pass0 = act0 && !(sum0 < thrd), pass1 = act1 && !(sum1 < thrd);
+                cB += ((act0 && near_thr(sum0, thrd, eps)) ? 1u : 0u) + ((act1 && near_thr(sum1, thrd, eps)) ? 1u : 0u);
+                if (map) {
+                    if (act0 && !pass0) map[(r0 + rl0) * nxg_pad + xi0 + c0] = (int16_t)s;
+                    if (act1 && !pass1) map[(r0 + rl1) * nxg_pad + xi0 + c1] = (int16_t)s;
+                }
+                if (last) {                             // accepted: nothing left to do for these windows
+                    if (pass0) { emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c0) * step, (r0 + rl0) * step, sum0); if (map) map[(r0 + rl0) * nxg_pad + xi0 + c0] = (int16_t)nstages; }
+                    if (pass1) { emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c1) * step, (r0 + rl1) * step, sum1); if (map) map[(r0 + rl1) * nxg_pad + xi0 + c1] = (int16_t)nstages; }
+                } else {
+                    unsigned pb[NMW];
 #pragma unroll
-                    for (int k = 0; k < KMAX; ++k) {
-                        act[k] = mm.pop(bit[k]);
-                        const int rl = bit[k] >> LSEG, c = ((lane - SH * rl) & 31) + ((bit[k] & (SEG - 1)) << 5);
-                        tw[k] = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
-                        vn[k] = s_vnf[rl * C + c];
-                    }
-                    if (K == 1 || KMAX == 1) {
-                        const char* t1[1] = {tw[0]}; float v1[1] = {vn[0]}; double s1[1];
-                        stage_eval<MODE, 1>(s, si, t1, v1, s1);
-                        sum[0] = s1[0];
-                    } else if (K == 2 || KMAX == 2) {
-                        const char* t2[2] = {tw[0], tw[1]}; float v2[2] = {vn[0], vn[1]}; double s2[2];
-                        stage_eval<MODE, 2>(s, si, t2, v2, s2);
-                        sum[0] = s2[0]; sum[1] = s2[1];
-                    } else if (K == 3 || KMAX == 3) {
-                        const char* t3[3] = {tw[0], tw[1], tw[2]}; float v3[3] = {vn[0], vn[1], vn[2]}; double s3[3];
-                        stage_eval<MODE, 3>(s, si, t3, v3, s3);
-                        sum[0] = s3[0]; sum[1] = s3[1]; sum[2] = s3[2];
-                    } else {
-                        stage_eval<MODE, 4>(s, si, tw, vn, sum);
-                    }
-                    unsigned passbits[NMW];
-#pragma unroll
-                    for (int i = 0; i < NMW; ++i) passbits[i] = 0;
-#pragma unroll
-                    for (int k = 0; k < KMAX; ++k) {
-                        if (k < K) {                    // warp-uniform
-                            bool pass = act[k] && !(sum[k] < (double)thr);
-                            const unsigned am = __ballot_sync(0xffffffffu, act[k]);
-                            const unsigned nm = __ballot_sync(0xffffffffu, act[k] && near_thr(sum[k], thr));
-                            if (lane == 0) {
-                                weak += (unsigned)__popc(am) * (unsigned)nws;
-                                if (nm) atomicAdd(&s_ctr[2], __popc(nm));
-                            }
-                            const int rl = bit[k] >> LSEG, c = ((lane - SH * rl) & 31) + ((bit[k] & (SEG - 1)) << 5);
-                            const int mpos = (r0 + rl) * nxg_pad + xi0 + c;
-                            if (act[k] && !pass && map) map[mpos] = (int16_t)s;
-                            if (pass && s + 1 == nstages) {
-                                emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum[k]);
-                                if (map) map[mpos] = (int16_t)nstages;
-                                pass = false;           // accepted: nothing left to do for it
-                            }
-                            if (pass) {
-                                if (NMW == 1 || bit[k] < 32) passbits[0] |= 1u << bit[k];
-                                else passbits[NMW - 1] |= 1u << (bit[k] - 32);
-                            }
-                        }
-                    }
+                    for (int i = 0; i < NMW; ++i) pb[i] = 0;
+                    if (pass0) pb[NMW == 1 ? 0 : bit0 >> 5] |= 1u << (bit0 & 31);
+                    if (pass1) pb[NMW == 1 ? 0 : bit1 >> 5] |= 1u << (bit1 & 31);
 #pragma unroll
                     for (int i = 0; i < NMW; ++i)
-                        if (passbits[i]) atomicOr(&s_alive[nxt][i][lane], passbits[i]);
+                        if (pb[i]) atomicOr(&s_alive[nxt][i][lane], pb[i]);
                 }
-            } else {
-            Live<NMW> mm = m;
-            mm.skip(w);                                 // this warp takes rounds w, w+8, ...
-            for (int j = w; j < rounds; j += NW) {
-                int bit;
-                const bool act = mm.pop(bit);
-                const int rl = bit >> LSEG, c = ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
-                const char* tw = reinterpret_cast<const char*>(s_tile + (rl * step) * TP + c);
-                const double sum = tile_stage_generic(s, si, tw, s_vnf[rl * C + c]);
-                bool pass = act && !(sum < (double)thr);
-                const unsigned am = __ballot_sync(0xffffffffu, act);
-                const unsigned nm = __ballot_sync(0xffffffffu, act && near_thr(sum, thr));
-                if (lane == 0) {
-                    weak += (unsigned)__popc(am) * (unsigned)nws;
-                    if (nm) atomicAdd(&s_ctr[2], __popc(nm));
-                }
-                const int mpos = (r0 + rl) * nxg_pad + xi0 + c;
-                if (act && !pass && map) map[mpos] = (int16_t)s;
-                if (pass && s + 1 == nstages) {
-                    emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum);
-                    if (map) map[mpos] = (int16_t)nstages;
-                    pass = false;                       // accepted: nothing left to do for it
-                }
-                if (pass) atomicOr(&s_alive[nxt][bit >> 5][lane], 1u << (bit & 31));
-                mm.skip(NW - 1);
-            }
             }
             __syncthreads();
             cur = nxt; ++s;
         }
-        // ---- 4. the few survivors of the in-tile stages: block-local work queue, one window per warp at a
-        //         time, the 32 lanes evaluate 32 weak classifiers of a stage against the tile in shared memory ----
+        // ---- 4. the few survivors of the in-tile stages: block-local work queue.  The 32 lanes of a warp evaluate 32 weak
+        //         classifiers of a stage against the tile in shared memory (node data from global memory through L1).
+        //         Exact stump cascades: a warp takes kQueueGroup windows at a time and applies every node it fetches to all
+        //         of them, so the node fetch (four loads, the coefficient unpacking) is paid once per group ----
         if (total > 0 && s < nstages) {
             if (w == 0) {
                 const int cnt = m.count();
@@ -829,6 +831,65 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
             __syncthreads();
             const uint4* __restrict__ nA = b.nodeTA[si];
             const uint4* __restrict__ nB = b.nodeTB[si];
+            if (MODE == 1) {
+                constexpr int KQ = kQueueGroup;
+                for (;;) {
+                    int i0 = 0;
+                    if (lane == 0) i0 = atomicAdd(&s_pop, KQ);
+                    i0 = __shfl_sync(0xffffffffu, i0, 0);
+                    if (i0 >= total) break;
+                    uint32_t pb2[KQ];
+                    float vn[KQ];
+                    int wid[KQ];
+                    unsigned alive = 0;                 // bit k: window k of the group is still in the cascade (warp-uniform)
+#pragma unroll
+                    for (int k = 0; k < KQ; ++k) {
+                        wid[k] = s_list[min(i0 + k, total - 1)];
+                        vn[k] = s_vnf[wid[k]];
+                        const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + ((wid[k] / C) * step) * TP + (wid[k] & (C - 1)));
+                        const uint32_t pw = WORDS ? pbase >> 2 : pbase;
+                        pb2[k] = pw | pw << 16;
+                        if (i0 + k < total) alive |= 1u << k;
+                    }
+                    for (int st = s; st < nstages && alive; ++st) {
+                        const int n0 = b.stage_first_node[st], nt = b.stage_ntrees[st];
+                        double part[KQ];
+#pragma unroll
+                        for (int k = 0; k < KQ; ++k) part[k] = 0.0;
+                        for (int t = lane; t < nt; t += 32) {
+                            const int n = n0 + t;
+                            const uint4 A = __ldg(nA + n), B = __ldg(nB + n), Cq = __ldg(b.nodeC + n);
+                            const uint32_t nc = __ldg(b.nodeM + n) & 255u;
+                            const float nthr = __uint_as_float(Cq.y);
+                            const double delta = __hiloint2double((int)Cq.w, (int)Cq.z);      // (left - right) * 128, see add_if_lt
+#pragma unroll
+                            for (int k = 0; k < KQ; ++k) {
+                                if (!(alive >> k & 1)) continue;                                // warp-uniform
+                                const int r = lane_resp_abc<WORDS>(A, B, Cq.x, pb2[k], nc);
+                                add_if_lt(part[k], __fmul_rn(__int2float_rn(r), vn[k]), nthr, delta);
+                            }
+                        }
+                        const float thr = b.stage_thr[st];
+                        const double thrd = (double)thr, eps = 1e-5 * fabs((double)thr), base = b.qbase[st];
+                        if (lane == 0) weak += (unsigned)nt * (unsigned)__popc(alive);
+#pragma unroll
+                        for (int k = 0; k < KQ; ++k) {
+                            if (!(alive >> k & 1)) continue;
+                            const double sum = warp_sum(part[k]) + base;
+                            if (lane == 0 && near_thr(sum, thrd, eps)) ++cB;
+                            const bool rejected = sum < thrd;
+                            if (rejected || st + 1 == nstages) {
+                                alive &= ~(1u << k);
+                                if (lane == 0) {
+                                    const int rl = wid[k] / C, c = wid[k] & (C - 1);
+                                    if (!rejected) emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c) * step, (r0 + rl) * step, sum);
+                                    if (map) map[(r0 + rl) * nxg_pad + xi0 + c] = (int16_t)(rejected ? st : nstages);
+                                }
+                            }
+                        }
+                    }
+                }
+            } else {
             for (;;) {
                 int i = 0;
                 if (lane == 0) i = atomicAdd(&s_pop, 1);
@@ -844,54 +905,42 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                 for (; st < nstages; ++st) {
                     const int nt = b.stage_ntrees[st];
                     double part = 0.0, seq = 0.0;
-                    if (MODE == 1) {
-                        const int n0 = b.stage_first_node[st];
-                        for (int t = lane; t < nt; t += 32) {
-                            const int n = n0 + t;
+                    const int t0 = b.stage_first_tree[st];
+                    unsigned visited = 0;
+                    // walks tree t for this lane's window; returns the leaf it ends in
+                    auto tree_leaf = [&](int t) {
+                        const int base = b.tree_first_node[t0 + t];
+                        int at = 0;
+                        float leaf;
+                        for (;;) {
+                            const uint32_t M = __ldg(b.nodeM + base + at);
                             uint4 Cq;
-                            const int r = lane_resp<WORDS>(b, nA, nB, n, pb2, __ldg(b.nodeM + n) & 255u, Cq);
+                            const int r = lane_resp<WORDS>(b, nA, nB, base + at, pb2, M & 255u, Cq);
+                            ++visited;
                             const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
-                            part += (double)__uint_as_float(lt ? Cq.z : Cq.w);
+                            leaf = __uint_as_float(lt ? Cq.z : Cq.w);
+                            const int go = lt ? ((M >> 8) & 255u) : ((M >> 16) & 255u);
+                            if (!go) break;
+                            at = go;
                         }
-                        if (lane == 0) weak += (unsigned)nt;
+                        return leaf;
+                    };
+                    if (MODE == 0 && b.seq_sum) {       // (the exact evaluators, MODE 1 and 2, are only chosen for cascades with exact sums)
+                        // the stage sums of this cascade are not exactly representable (ugd_cascade_info.sum_exact == 0):
+                        // add the leaves one by one in file order, exactly as the oracle's loop does
+                        for (int k0 = 0; k0 < nt; k0 += 32) {
+                            const float leaf = k0 + lane < nt ? tree_leaf(k0 + lane) : 0.f;
+                            const int mcnt = min(32, nt - k0);
+                            for (int i2 = 0; i2 < mcnt; ++i2) seq += (double)__shfl_sync(0xffffffffu, leaf, i2);
+                        }
                     } else {
-                        const int t0 = b.stage_first_tree[st];
-                        unsigned visited = 0;
-                        // walks tree t for this lane's window; returns the leaf it ends in
-                        auto tree_leaf = [&](int t) {
-                            const int base = b.tree_first_node[t0 + t];
-                            int at = 0;
-                            float leaf;
-                            for (;;) {
-                                const uint32_t M = __ldg(b.nodeM + base + at);
-                                uint4 Cq;
-                                const int r = lane_resp<WORDS>(b, nA, nB, base + at, pb2, M & 255u, Cq);
-                                ++visited;
-                                const bool lt = __fmul_rn(__int2float_rn(r), vnf) < __uint_as_float(Cq.y);
-                                leaf = __uint_as_float(lt ? Cq.z : Cq.w);
-                                const int go = lt ? ((M >> 8) & 255u) : ((M >> 16) & 255u);
-                                if (!go) break;
-                                at = go;
-                            }
-                            return leaf;
-                        };
-                        if (MODE == 0 && b.seq_sum) {   // (the exact evaluators, MODE 1 and 2, are only chosen for cascades with exact sums)
-                            // the stage sums of this cascade are not exactly representable (ugd_cascade_info.sum_exact == 0):
-                            // add the leaves one by one in file order, exactly as the oracle's loop does
-                            for (int c0 = 0; c0 < nt; c0 += 32) {
-                                const float leaf = c0 + lane < nt ? tree_leaf(c0 + lane) : 0.f;
-                                const int m = min(32, nt - c0);
-                                for (int i = 0; i < m; ++i) seq += (double)__shfl_sync(0xffffffffu, leaf, i);
-                            }
-                        } else {
-                            for (int t = lane; t < nt; t += 32) part += (double)tree_leaf(t);
-                        }
-                        visited = __reduce_add_sync(0xffffffffu, visited);
-                        if (lane == 0) weak += visited;
+                        for (int t = lane; t < nt; t += 32) part += (double)tree_leaf(t);
                     }
+                    visited = __reduce_add_sync(0xffffffffu, visited);
+                    if (lane == 0) weak += visited;
                     sum = (MODE == 0 && b.seq_sum) ? seq : warp_sum(part);
                     const float thr = b.stage_thr[st];
-                    if (lane == 0 && near_thr(sum, thr)) atomicAdd(&s_ctr[2], 1u);
+                    if (lane == 0 && near_thr(sum, (double)thr, 1e-5 * fabs((double)thr))) ++cB;
                     if (sum < (double)thr) break;
                 }
                 if (lane == 0) {
@@ -899,10 +948,22 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                     if (map) map[(r0 + rl) * nxg_pad + xi0 + c] = (int16_t)st;
                 }
             }
+            }
         }
         if (dbl) s_tile = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
     }
-    if (lane == 0 && weak) atomicAdd(&s_ctr[3], weak);
+    // ---- per-lane tallies -> block counters -> per-frame counters ----
+    {
+        const unsigned ev = __reduce_add_sync(0xffffffffu, cA & 0xffffu), lv = __reduce_add_sync(0xffffffffu, cA >> 16);
+        const unsigned nr = __reduce_add_sync(0xffffffffu, cB & 0xffffu), vk = __reduce_add_sync(0xffffffffu, cB >> 16);
+        if (lane == 0) {
+            if (ev) atomicAdd(&s_ctr[0], ev);
+            if (lv) atomicAdd(&s_ctr[1], lv);
+            if (nr) atomicAdd(&s_ctr[2], nr);
+            weak += vk * (unsigned)nw0;                // stage 0: every window that passed the variance test
+            if (weak) atomicAdd(&s_ctr[3], weak);
+        }
+    }
     __syncthreads();
     if (tid < 5 && s_ctr[tid]) {
         constexpr unsigned slots = CTR_EVALUATED | CTR_LOWVAR << 4 | CTR_NEAR << 8 | CTR_WEAK << 12 | CTR_QUEUED << 16;   // s_ctr[i] -> counter

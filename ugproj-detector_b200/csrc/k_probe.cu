@@ -14,24 +14,28 @@ __global__ void __launch_bounds__(kProbeThreads) k_lds_probe(int iters, unsigned
     __shared__ unsigned tile[4096];                          // 16 KB
     for (int i = threadIdx.x; i < 4096; i += kProbeThreads) tile[i] = i * 2654435761u;
     __syncthreads();
-    // lane l of every warp reads bank l: word index = lane + 32 * row, rows walk the tile
-    unsigned base = (unsigned)__cvta_generic_to_shared(tile) + 4u * (threadIdx.x & 31);
-    unsigned row = threadIdx.x >> 5;
-    unsigned acc[kProbeUnroll];
+    // lane l of every warp reads bank l (word index = lane + 32 * row); the 16 loads of an iteration use immediate
+    // offsets from one base register, and one LOP3 folds two of them, so the loop issues ~1.6 instructions per LDS:
+    // the shared-memory pipe, not the issue slots, is what it measures
+    const unsigned base = (unsigned)__cvta_generic_to_shared(tile) + 4u * (threadIdx.x & 31) + 128u * (threadIdx.x >> 5);
+    unsigned acc[kProbeUnroll / 2];
 #pragma unroll
-    for (int u = 0; u < kProbeUnroll; ++u) acc[u] = 0;
-    for (int it = 0; it < iters; ++it) {
-#pragma unroll
-        for (int u = 0; u < kProbeUnroll; ++u) {
-            unsigned v;
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + 128u * ((row + u) & 127u)));
-            acc[u] ^= v;
-        }
-        row += kProbeUnroll;
+    for (int u = 0; u < kProbeUnroll / 2; ++u) acc[u] = 0;
+#define UGD_LDS2(u)                                                                                        \
+    {                                                                                                      \
+        unsigned v0, v1;                                                                                   \
+        asm volatile("ld.volatile.shared.b32 %0, [%1+" #u "*2048];" : "=r"(v0) : "r"(base) : "memory");                       \
+        asm volatile("ld.volatile.shared.b32 %0, [%1+" #u "*2048+1024];" : "=r"(v1) : "r"(base) : "memory");                  \
+        acc[u] ^= v0 ^ v1;                                                                                 \
     }
+#pragma unroll 1
+    for (int it = 0; it < iters; ++it) {
+        UGD_LDS2(0) UGD_LDS2(1) UGD_LDS2(2) UGD_LDS2(3) UGD_LDS2(4) UGD_LDS2(5) UGD_LDS2(6) UGD_LDS2(7)
+    }
+#undef UGD_LDS2
     unsigned x = 0;
 #pragma unroll
-    for (int u = 0; u < kProbeUnroll; ++u) x ^= acc[u];
+    for (int u = 0; u < kProbeUnroll / 2; ++u) x ^= acc[u];
     if (x == 0x12345u) sink[0] = x;                          // keeps the loads alive without a store per thread
 }
 

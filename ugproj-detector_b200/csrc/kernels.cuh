@@ -12,7 +12,7 @@
 
 namespace ugd {
 
-constexpr int kMaxDenseNodes = 380;       // nodes of the in-tile stages, held in __constant__ (160 B each)
+constexpr int kMaxDenseNodes = 380;       // nodes of the in-tile stages, held in __constant__ (2 x 64 B + 16 B each)
 constexpr int kMaxDenseStages = 48;
 
 // In-tile node: merged corner list.  BYTE offsets into the shared-memory tile are precomputed for the
@@ -29,7 +29,20 @@ struct alignas(16) DNode {
         double delta;                     // exact evaluators: leaf difference (stumps: times 128, see add_if_lt)
     };
 };
-static_assert(sizeof(DNode) == 160, "DNode layout");
+static_assert(sizeof(DNode) == 160, "DNode layout");          // host-side working form (both layouts, int32 coefficients)
+
+// Device form of an in-tile node for ONE tile layout: 64 bytes, every group fetched with one LDCU.128 through the
+// uniform datapath -- offsets 0-3 / 4-7 / 8-11, then {thr, meta, delta} together.
+struct alignas(16) DNodeL {
+    int32_t off[12];                      // tile BYTE offsets of the merged corners (sorted by coefficient for pattern nodes)
+    float   thr;
+    uint32_t meta;                        // nc | lnode << 8 | rnode << 16 | last << 24 | flags (see build_scan_constants)
+    union {
+        struct { float lval, rval; };     // generic evaluator: the two leaves
+        double delta;                     // exact evaluators: leaf difference times 128 (see add_if_lt)
+    };
+};
+static_assert(sizeof(DNodeL) == 64, "DNodeL layout");
 
 constexpr int kTileRows = 16;             // scan tile: kTileRows x kTileCols windows = 32 per bank class
 constexpr int kTileCols = 64;             // (grid-step-1 levels: 128 columns, 64 per class, when shared memory allows)
@@ -56,9 +69,11 @@ struct DevBufs {
     const uint32_t* xtab; const uint32_t* ytab;
     // cascade (per-lane evaluator of the late stages, SoA in global memory; the dense stages live in __constant__)
     // node n: A = 8 x u16 byte offsets from the window origin (corners 0-7); B = {off8|off9<<16, off10|off11<<16, coef0-3, coef4-7};
-    //              C = {coef8-11, thr, left leaf, right leaf}; M = nc | lnode<<8 | rnode<<16
+    //              C = {coef8-11, thr, left leaf, right leaf} -- exact stump cascades (fast_scan == 1): {coef8-11, thr, (left - right) * 128 as a double};
+    //              M = nc | lnode<<8 | rnode<<16
     const uint4* nodeC; const uint32_t* nodeM;
     const uint4* nodeTA[2]; const uint4* nodeTB[2];   // A/B with byte offsets into the scan tile (grid step 1 / 2 layouts)
+    const double* qbase;                              // exact stump cascades: per stage, the sum of the right leaves (nodeC then holds thr and (left - right) * 128)
     int seq_sum;                                      // stage sums are not exact in fp64: the late stages add their leaves in file order
     int word_off;                                     // the A/B offsets are in 32-bit words (two tiles / large windows: bytes do not fit 16 bits)
     const int32_t* stage_first_tree; const int32_t* stage_ntrees; const float* stage_thr;
@@ -97,13 +112,15 @@ bool scan_word_offsets(const Cascade& c);                         // per-lane ta
 int scan_mode(const Cascade& c);
 // Host image of the __constant__ data of one (cascade, dense_stages) pair; built once per detector.
 struct ScanConstImage {
-    std::vector<DNode> dn;
+    std::vector<DNodeL> dn[2];                        // per tile layout
+    std::vector<int4> coef;                           // 12 int8 coefficients per node
     std::vector<int> first_node;                      // [dense_stages + 1]
     std::vector<float> thr;                           // [dense_stages]
     std::vector<double> base;                         // [dense_stages]
-    std::vector<int> ncf;                             // [dense_stages][9]
+    std::vector<int> ncf;                             // [dense_stages][12] (9 used)
     ScanGeom geom;
 };
+void stage_right_sums(const Cascade& c, std::vector<double>& qbase);   // per stage: sum of the right leaves
 cudaError_t build_scan_constants(const Cascade& c, int dense_stages, ScanConstImage& img);
 cudaError_t upload_scan_constants(const ScanConstImage& img, cudaStream_t st);   // asynchronous: img must outlive the copies
 
