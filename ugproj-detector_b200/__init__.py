@@ -50,6 +50,38 @@ class Counters(C.Structure):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
+class RectLists:
+    """The per-frame rect lists of one batch call, kept as the two arrays the C ABI filled -- rects [frames, cap, 4] and
+    counts [frames] -- so that a call over hundreds of frames creates no per-frame Python objects until somebody looks.
+    Behaves like a list of [n_i, 4] int32 arrays (len, indexing, iteration)."""
+    __slots__ = ("rects", "counts", "start", "n")
+
+    def __init__(self, rects, counts, start=0, n=None):
+        self.rects, self.counts, self.start = rects, counts, start
+        self.n = len(counts) - start if n is None else n
+
+    def __len__(self):
+        return self.n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(self.n))]
+        if i < 0:
+            i += self.n
+        if not 0 <= i < self.n:
+            raise IndexError(i)
+        return self.rects[self.start + i, :min(int(self.counts[self.start + i]), self.rects.shape[1])]
+
+    def __iter__(self):
+        return (self[i] for i in range(self.n))
+
+    def __add__(self, other):
+        return list(self) + list(other)
+
+    def total(self):
+        return int(self.counts[self.start:self.start + self.n].sum())
+
+
 class UgdError(RuntimeError):
     def __init__(self, code, detail=""):
         self.code = code
@@ -249,7 +281,7 @@ class Detector:
         cnt = np.zeros(n, np.int32)
         self._ck(lib().ugd_wait_batch(self._h, _p(out), _p(cnt)))
         self._pending = None
-        return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(n)]
+        return RectLists(out, cnt)
 
     def detect_batch_scaled(self, frames: np.ndarray, scan_size, cap: int = 256):
         """frames: [N,H,W,3] full-size BGR host array; scan_size = (w, h) as cfg scan.frame_size.  INTER_AREA
@@ -262,11 +294,11 @@ class Detector:
     def detect_batch_scaled_ptr(self, ptr, is_device: bool, n: int, w: int, h: int, scan_size, cap: int = 256):
         if not isinstance(ptr, C.c_void_p):
             ptr = C.c_void_p(ptr)
-        out = np.zeros((n, cap, 4), np.int32)
+        out = np.empty((n, cap, 4), np.int32)
         cnt = np.zeros(n, np.int32)
         self._ck(lib().ugd_detect_batch_scaled(self._h, ptr, int(is_device), n, w, h, int(scan_size[0]), int(scan_size[1]),
                                                _p(out), cap, _p(cnt)))
-        return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(n)]
+        return RectLists(out, cnt)
 
     def resize_area(self, img: np.ndarray, dw: int, dh: int) -> np.ndarray:
         """cv2.resize(img, (dw, dh), interpolation=INTER_AREA) on the device (decimation only)."""
@@ -282,24 +314,21 @@ class Detector:
 
     def _batch(self, ptr, is_device, is_bgr, n, w, h, cap):
         while True:
-            key = (n, cap)
-            if getattr(self, "_bkey", None) != key:
-                self._bout = np.zeros((n, cap, 4), np.int32)
-                self._bcnt = np.zeros(n, np.int32)
-                self._bkey = key
-            rc = lib().ugd_detect_batch(self._h, ptr, is_device, int(is_bgr), n, w, h, _p(self._bout), cap, _p(self._bcnt))
-            if rc == ERR_TRUNCATED and int(self._bcnt.max()) > cap:      # never cut a list silently: run again with room
-                cap = int(self._bcnt.max())
+            out = np.empty((max(n, 1), cap, 4), np.int32)            # fresh arrays: the result owns them, nothing is copied
+            cnt = np.zeros(max(n, 1), np.int32)
+            rc = lib().ugd_detect_batch(self._h, ptr, is_device, int(is_bgr), n, w, h, _p(out), cap, _p(cnt))
+            if rc == ERR_TRUNCATED and int(cnt.max()) > cap:         # never cut a list silently: run again with room
+                cap = int(cnt.max())
                 continue
             self._ck(rc)
-            return [self._bout[i, :int(self._bcnt[i])].copy() for i in range(n)]
+            return RectLists(out, cnt, 0, n)
 
     # -- multi-GPU: frames sharded over ranks, lists gathered to the root inside the library ----------
     def comm_init(self, comm_id: bytes, rank: int, world: int):
         """ncclCommInitRank on this detector's device; comm_id = comm_unique_id() of the root, handed to every rank."""
         assert len(comm_id) == 128
         self._ck(lib().ugd_comm_init(self._h, C.c_char_p(comm_id), rank, world))
-        self.rank, self.world = rank, world
+        self.rank, self.world = rank, world           # cached: detect_batch_sharded is on the timed path
 
     def comm_info(self):
         r, w, v = C.c_int(), C.c_int(), C.c_int()
@@ -312,22 +341,16 @@ class Detector:
         Root: list over ranks of lists over that rank's frames of [k,4] arrays; other ranks: their own lists."""
         if not isinstance(ptr, C.c_void_p):
             ptr = C.c_void_p(ptr)
-        rank, world, _ = self.comm_info()
+        rank, world = getattr(self, "rank", 0), getattr(self, "world", 1)
         nslots = world * slot_frames if rank == root else n
-        key = ("s", nslots, cap)
-        if getattr(self, "_skey", None) != key:
-            self._sout = np.zeros((max(nslots, 1), cap, 4), np.int32)
-            self._scnt = np.zeros(max(nslots, 1), np.int32)
-            self._skey = key
+        out = np.empty((max(nslots, 1), cap, 4), np.int32)           # fresh arrays: the result owns them, nothing is copied
+        cnt = np.zeros(max(nslots, 1), np.int32)
         self._ck(lib().ugd_detect_batch_sharded(self._h, ptr, int(is_device), int(is_bgr), n, w, h, slot_frames, root,
-                                                _p(self._sout), cap, _p(self._scnt)))
+                                                _p(out), cap, _p(cnt)))
         if rank != root:
-            return [self._sout[i, :int(self._scnt[i])].copy() for i in range(n)]
-        out = []
-        for r in range(world):
-            c = self._scnt[r * slot_frames:(r + 1) * slot_frames]
-            out.append([self._sout[r * slot_frames + i, :int(c[i])].copy() for i in range(slot_frames) if c[i] >= 0])
-        return out
+            return RectLists(out, cnt, 0, n)
+        # a rank's frames fill its slots from the front; the slots it did not use carry -1
+        return [RectLists(out, cnt, r * slot_frames, int((cnt[r * slot_frames:(r + 1) * slot_frames] >= 0).sum())) for r in range(world)]
 
     # -- observability ----------------------------------------------------------------------------
     def counters(self) -> dict:

@@ -36,8 +36,8 @@ struct DevPtr {                       // grow-only device allocation
 
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
-    DevPtr levels, xtab, ytab, wk_resize, wk_colsum, wk_carry, wk_bands, wk_scan;
-    void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release(); wk_colsum.release();
+    DevPtr levels, xtab, ytab, wk_resize, wk_carry, wk_bands, wk_scan;
+    void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release();
                      wk_carry.release(); wk_bands.release(); wk_scan.release(); }
 };
 
@@ -142,7 +142,6 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->xtab, dp->host.xtab))) return rc;
     if ((rc = upload(d, dp->ytab, dp->host.ytab))) return rc;
     if ((rc = upload(d, dp->wk_resize, dp->host.wk_resize))) return rc;
-    if ((rc = upload(d, dp->wk_colsum, dp->host.wk_colsum))) return rc;
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
@@ -437,9 +436,8 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 1);
     if (is_bgr) launch_equalize(b, si);
     mark(d, 2);
-    launch_resize(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), si);
+    launch_resize_colsum(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), si);    // pyramid + strip column sums in one kernel
     mark(d, 3);
-    launch_colsum(b, dp->wk_colsum.as<WorkItem>(), (int)p.wk_colsum.size(), si);
     mark(d, 4);
     launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), si);
     mark(d, 5);
@@ -478,7 +476,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     bool overflow = false;
     finish_group(d, p, f0, nframes, out, cap, counts, &overflow);
     if (d->profiling) {
-        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 1, 1, 1, b.T ? 1 : 0, 1, 1, 0};   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
+        const int launches[UGD_K_COUNT] = {is_bgr ? 1 : 0, is_bgr ? 1 : 0, 1, 0, 1, 1, b.T ? 1 : 0, 1, 1, 0};   // (k_colsum is part of k_resize since r02)   // k_scan: its two launches (grid step 2 / step 1 levels) are timed as one
         for (int k = 0; k < UGD_K_AREA; ++k) {
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev[k], d->ev[k + 1]);
@@ -1123,11 +1121,12 @@ int ugd_detect_batch_sharded(ugd_detector* d, const void* frames, int is_device,
         if (is_root) {
             CK(d->shard.recv.reserve((size_t)world * msg + 256));
             CK(d->shard.packed.reserve(hdr + nslots * cap * sizeof(ugd_rect) + 256));
-            if (hdr > d->shard.h_packed_cap * 4 || !d->shard.h_packed) {
+            const size_t need = hdr + nslots * cap * sizeof(ugd_rect);           // pinned: header, then every rect that can arrive
+            if (need > d->shard.h_packed_cap || !d->shard.h_packed) {
                 if (d->shard.h_packed) cudaFreeHost(d->shard.h_packed);
                 d->shard.h_packed = nullptr;
-                CK(cudaMallocHost((void**)&d->shard.h_packed, hdr));
-                d->shard.h_packed_cap = hdr / 4;
+                CK(cudaMallocHost((void**)&d->shard.h_packed, need));
+                d->shard.h_packed_cap = need;
             }
         }
         d->shard.call = true; d->shard.slot_frames = slot_frames;
@@ -1162,8 +1161,11 @@ int ugd_detect_batch_sharded(ugd_detector* d, const void* frames, int is_device,
         if (world > 1) {
             const int total = d->shard.h_packed[0];
             const int* pc = d->shard.h_packed + 1;
-            std::vector<ugd_rect> rects((size_t)std::max(total, 1));
-            if (total > 0) CK(cudaMemcpy(rects.data(), d->shard.packed.as<uint8_t>() + hdr, (size_t)total * sizeof(ugd_rect), cudaMemcpyDeviceToHost));
+            ugd_rect* rects = reinterpret_cast<ugd_rect*>(reinterpret_cast<uint8_t*>(d->shard.h_packed) + hdr);
+            if (total > 0) {                                                     // the rects that exist, not world x frames x cap slots
+                CK(cudaMemcpyAsync(rects, d->shard.packed.as<uint8_t>() + hdr, (size_t)total * sizeof(ugd_rect), cudaMemcpyDeviceToHost, d->stream));
+                CK(cudaStreamSynchronize(d->stream));
+            }
             size_t at = 0;
             for (int r = 0; r < world; ++r) {
                 if (r == root) continue;
@@ -1172,7 +1174,7 @@ int ugd_detect_batch_sharded(ugd_detector* d, const void* frames, int is_device,
                     const int n = pc[e];
                     counts[e] = n;
                     const int take = std::max(std::min(n, cap), 0);
-                    if (take) memcpy(out + e * cap, rects.data() + at, (size_t)take * sizeof(ugd_rect));
+                    if (take) memcpy(out + e * cap, rects + at, (size_t)take * sizeof(ugd_rect));
                     at += (size_t)take;
                     if (n > cap) rc = UGD_ERR_TRUNCATED;
                 }

@@ -142,75 +142,77 @@ void launch_equalize(const DevBufs& b, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3  pyramid resize, every level of every frame in one launch (a7; INTER_LINEAR_EXACT, A.2).
-// One thread = 4 consecutive output pixels; coefficient tables come from the plan.
+// K3  pyramid resize (a7; INTER_LINEAR_EXACT, A.2) fused with the first phase of the integral (a8): per-strip column
+// sums.  One thread owns FOUR output columns of one level and walks the 32 rows of a strip: the x side of the
+// bilinear blend (source column, 8.8 coefficients, source pointer) is set up once and reused for every row, the pixels
+// of a row leave as one 32-bit store (a warp writes 128 consecutive bytes), and the running column sums of pixel and
+// pixel^2 are written once per strip -- the pyramid is never re-read for them.  ~19 instructions per output pixel
+// (the separate kernels took 56 + 4); all levels of all frames in one launch.
+// The tables never point at the last source column / row: there (i0 = n-2, c1 = 256) stands for (n-1, 0), so the
+// "+1" neighbour is always inside the frame and needs no clamp.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_resize(DevBufs b, const WorkItem* __restrict__ wk) {
+constexpr int kResizeThreads = 64;     // x 4 columns = 256 columns per block
+
+__global__ void __launch_bounds__(kResizeThreads) k_resize_colsum(DevBufs b, const WorkItem* __restrict__ wk) {
     const WorkItem it = wk[blockIdx.x];
     const LevelInfo& L = b.levels[it.level];
+    const int strip = it.first & 0xffff, chunk = it.first >> 16;
     const int quads = L.img_pitch >> 2;
-    const int q = it.first + threadIdx.x;
-    if (q >= quads * L.sh) return;
-    const int y = q / quads, qx = q - y * quads;
+    const int qx = chunk * kResizeThreads + threadIdx.x;
+    if (qx >= quads) return;
     const int frame = blockIdx.y;
-    const uint8_t* src = b.src_gray + (size_t)frame * b.src_stride;
-    const uint32_t ye = __ldg(b.ytab + L.ytab_off + y);
-    const int y0 = ye & 0xffff, cy1 = ye >> 16, cy0 = 256 - cy1;
-    const int y1 = min(y0 + 1, b.h - 1);
-    const uint8_t* r0 = src + (size_t)y0 * b.src_pitch;
-    const uint8_t* r1 = src + (size_t)y1 * b.src_pitch;
+    const int sw = L.sw, pitch = L.img_pitch, spitch = b.src_pitch;
     const uint4 xe4 = __ldg(reinterpret_cast<const uint4*>(b.xtab + L.xtab_off) + qx);
     const uint32_t xe[4] = {xe4.x, xe4.y, xe4.z, xe4.w};
-    uint32_t outv = 0;
+    const uint8_t* src = b.src_gray + (size_t)frame * b.src_stride;
+    const uint8_t* col[4];
+    int cx1[4];
+    bool live[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        int x = qx * 4 + k;
-        if (x < L.sw) {
-            int x0 = xe[k] & 0xffff, cx1 = xe[k] >> 16, cx0 = 256 - cx1;
-            int x1 = min(x0 + 1, b.w - 1);
-            int t0 = (int)__ldg(r0 + x0) * cx0 + (int)__ldg(r0 + x1) * cx1;
-            int t1 = (int)__ldg(r1 + x0) * cx0 + (int)__ldg(r1 + x1) * cx1;
-            uint32_t v = (uint32_t)(t0 * cy0 + t1 * cy1 + 32768) >> 16;
-            outv |= v << (8 * k);
-        }
+        col[k] = src + (xe[k] & 0xffffu);
+        cx1[k] = (int)(xe[k] >> 16);
+        live[k] = qx * 4 + k < sw;                          // columns of the row padding stay 0
     }
-    uint8_t* dst = b.pyr + (size_t)frame * b.pyr_stride + L.img_off;
-    *reinterpret_cast<uint32_t*>(dst + (size_t)y * L.img_pitch + qx * 4) = outv;
-}
-
-void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
-    if (nblocks) k_resize<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
-}
-
-// ------------------------------------------------------------------------------------------------
-// K4  integral images S and SQ (a8).  Two small passes give every 32-row strip its starting column sums:
-//   colsum : per 32-row strip, column sums of pixel and pixel^2            (1 B/px read)
-//   carry  : exclusive scan of those sums down the strips (tiny)
-// and k_integral_bands (below) then writes both planes in one sweep, each output element once.
-// Arithmetic is uint32 modular, which reproduces cv2's wrapping int32 SQ plane bit for bit.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_colsum(DevBufs b, const WorkItem* __restrict__ wk) {
-    const WorkItem it = wk[blockIdx.x];
-    const LevelInfo& L = b.levels[it.level];
-    const int quads = L.img_pitch >> 2;
-    const int i = it.first + threadIdx.x;
-    if (i >= quads * L.nstrips) return;
-    const int strip = i / quads, qx = i - strip * quads;
-    const int frame = blockIdx.y;
-    const uint8_t* img = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + qx * 4;
+    const uint32_t* ytab = b.ytab + L.ytab_off;
     const int v0 = strip * kStripRows, v1 = min(v0 + kStripRows, L.sh);
+    uint8_t* dst = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + (size_t)v0 * pitch + qx * 4;
     uint32_t s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
-#pragma unroll 8
-    for (int v = v0; v < v1; ++v) {
-        uint32_t p = *reinterpret_cast<const uint32_t*>(img + (size_t)v * L.img_pitch);
+#pragma unroll 2
+    for (int v = v0; v < v1; ++v, dst += pitch) {
+        const uint32_t ye = __ldg(ytab + v);
+        const int cy1 = (int)(ye >> 16), cy0 = 256 - cy1;
+        const size_t roff = (size_t)(ye & 0xffffu) * spitch;
+        uint32_t outv = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { uint32_t c = (p >> (8 * k)) & 255u; s[k] += c; q[k] += c * c; }
+        for (int k = 0; k < 4; ++k) {
+            const uint8_t* r0 = col[k] + roff;
+            const uint8_t* r1 = r0 + spitch;
+            const int cx0 = 256 - cx1[k];
+            const int t0 = (int)__ldg(r0) * cx0 + (int)__ldg(r0 + 1) * cx1[k];
+            const int t1 = (int)__ldg(r1) * cx0 + (int)__ldg(r1 + 1) * cx1[k];
+            const uint32_t pv = live[k] ? (uint32_t)(t0 * cy0 + t1 * cy1 + 32768) >> 16 : 0u;
+            outv |= pv << (8 * k);
+            s[k] += pv; q[k] += pv * pv;
+        }
+        *reinterpret_cast<uint32_t*>(dst) = outv;
     }
-    size_t o = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * L.img_pitch + qx * 4;
+    const size_t o = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * pitch + qx * 4;
     *reinterpret_cast<uint4*>(b.carryS + o) = make_uint4(s[0], s[1], s[2], s[3]);
     *reinterpret_cast<uint4*>(b.carryQ + o) = make_uint4(q[0], q[1], q[2], q[3]);
 }
 
+void launch_resize_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
+    if (nblocks) k_resize_colsum<<<dim3(nblocks, b.nframes), kResizeThreads, 0, st>>>(b, wk);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4  integral images S and SQ (a8).  The strip column sums come from k_resize_colsum; a small pass turns them into the
+// starting column sums of every 32-row strip:
+//   carry  : exclusive scan of the strip sums down the strips (tiny)
+// and k_integral_bands (below) then writes both planes in one sweep, each output element once.
+// Arithmetic is uint32 modular, which reproduces cv2's wrapping int32 SQ plane bit for bit.
+// ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_carry(DevBufs b, const WorkItem* __restrict__ wk) {
     const WorkItem it = wk[blockIdx.x];
     const LevelInfo& L = b.levels[it.level];
@@ -476,9 +478,6 @@ void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cu
     if (nblocks) k_integral_bands<<<dim3(b.nframes, nblocks), 32, 0, st>>>(b, wk);
 }
 
-void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
-    if (nblocks) k_colsum<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
-}
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
     if (nblocks) k_carry<<<dim3(nblocks, b.nframes), 256, 0, st>>>(b, wk);
 }

@@ -143,8 +143,7 @@ void launch_area(const AreaArgs& a, int channels, int nframes, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
 void launch_equalize(const DevBufs& b, cudaStream_t st);
-void launch_resize(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
-void launch_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
+void launch_resize_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);   // pyramid + per-strip column sums
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st);

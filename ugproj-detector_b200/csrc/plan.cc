@@ -22,7 +22,9 @@ void axis_table(int n, int m, uint32_t* tab) {
         double a = fx - (double)i;
         uint32_t i0, c1;
         if (i < 0) { i0 = 0; c1 = 0; }
-        else if (i >= n - 1) { i0 = (uint32_t)(n - 1); c1 = 0; }
+        else if (i >= n - 1) {                        // last sample alone: written as (n-2, 256) so that i0 + 1 stays inside (k_resize_colsum)
+            if (n >= 2) { i0 = (uint32_t)(n - 2); c1 = 256; } else { i0 = 0; c1 = 0; }
+        }
         else { i0 = (uint32_t)i; c1 = (uint32_t)rint_d(a * 256.0); }
         tab[d] = i0 | c1 << 16;
     }
@@ -98,8 +100,8 @@ void build_plan(int w, int h, int win_w, int win_h, double scale_factor, int min
         yt += round_up((uint32_t)L.sh, 4);
         // work tables
         int quads = L.img_pitch / 4;
-        add_work(p.wk_resize, level, (int64_t)quads * L.sh, 256);
-        add_work(p.wk_colsum, level, (int64_t)quads * L.nstrips, 256);
+        for (int strip = 0; strip < L.nstrips; ++strip)                                // one block per (strip of 32 rows, 256 columns); an empty last strip writes zero sums
+            for (int ch = 0; ch * 64 < quads; ++ch) p.wk_resize.push_back({level, strip | ch << 16});
         add_work(p.wk_carry, level, quads, 256);
         for (int seg = 0; seg * kIntSegRows < L.sh; ++seg)                         // one warp per (segment of 64 rows, band of 512 integral columns)
             for (int bnd = 0; bnd * kIntBand < L.sw + 1; ++bnd) p.wk_bands.push_back({level, bnd | seg << 8});

@@ -41,7 +41,7 @@ struct Plan {
     int w = 0, h = 0;
     std::vector<LevelInfo> levels;
     std::vector<uint32_t> xtab, ytab;           // entry = i0 | c1 << 16  (c1 in 0..256)
-    std::vector<WorkItem> wk_resize, wk_colsum, wk_carry, wk_bands, wk_scan;
+    std::vector<WorkItem> wk_resize, wk_carry, wk_bands, wk_scan;   // wk_resize: (strip | column chunk << 16) of k_resize_colsum
     // per-frame sizes
     int max_level_w = 0;                  // widest pyramid level (sizes the tilted-integral kernel's shared memory)
     size_t pyr_bytes = 0, int_ints = 0, pos_entries = 0, carry_ints = 0, map_entries = 0;
