@@ -60,6 +60,13 @@ typedef struct {
                                  Does not change results.                                            */
     int32_t max_raw_per_frame;/* capacity of the per-frame candidate list fed to groupRectangles;
                                  0 = engine default (8192)                                           */
+    int32_t legacy_24;        /* 1 = OpenCV-2.4 compatibility mode: the evaluator of the
+                                 library generation the reference was written against -- cvResize's 11-bit
+                                 INTER_LINEAR, double squared integral, float weights scaled by 1/area,
+                                 stage bias 1e-4, ystep = factor > 2 ? 1 : 2 without x-skip, no final clip,
+                                 and the cascade file's STAGE TREE (<parent>/<next>) walked as a tree
+                                 (haarcascade_frontalface_alt_tree.xml).  Slower path, same C ABI.
+                                 Parity unpinned: no OpenCV 2.4 exists to check it against.           */
 } ugd_params;
 
 typedef struct ugd_cascade  ugd_cascade;

@@ -41,6 +41,11 @@ class FlatCascade:
     node_right_val: np.ndarray     # float32 [nnodes]
     node_tilted: np.ndarray = None  # int32 [nnodes]  1: the node's rects are 45-degree tilted (read the tilted integral)
     tilted: bool = False
+    # the stage tree of the old format (<parent>/<next>, -1 = none; a linear chain elsewhere) and the stage thresholds as
+    # written in the file -- only the OpenCV-2.4 legacy restatement (oracle/haar_legacy.c) reads them
+    stage_thr_raw: np.ndarray = None   # float32 [nstages]  f32(xml)
+    stage_parent: np.ndarray = None    # int32 [nstages]
+    stage_next: np.ndarray = None      # int32 [nstages]
 
     @property
     def nstages(self):
@@ -59,7 +64,7 @@ def _f32(txt: str) -> np.float32:
     return np.float32(float(txt))
 
 
-def _finish(win, stages, trees, nodes, tilted):
+def _finish(win, stages, trees, nodes, tilted, tree_info=None):
     n = len(nodes)
     rects = np.zeros((n, 3, 4), np.int32)
     weights = np.zeros((n, 3), np.float32)
@@ -86,7 +91,10 @@ def _finish(win, stages, trees, nodes, tilted):
         tree_nnodes=np.array([t[1] for t in trees], np.int32),
         node_rects=rects, node_weights=weights, node_thr=thr,
         node_left=left, node_right=right, node_left_val=lval, node_right_val=rval,
-        node_tilted=tl, tilted=bool(tl.any()))
+        node_tilted=tl, tilted=bool(tl.any()),
+        stage_thr_raw=np.array([s[3] for s in stages], np.float32),
+        stage_parent=np.array([s[4] for s in stages], np.int32),
+        stage_next=np.array([s[5] for s in stages], np.int32))
 
 
 def _parse_rect(txt):
@@ -120,8 +128,11 @@ def _load_old(root_el):
                     d["right"] = int(nd.find("right_node").text)
                 nodes.append(d)
             trees.append((first_node, len(tnodes)))
-        thr = np.float32(_f32(st.find("stage_threshold").text) - THRESHOLD_EPS)
-        stages.append((first_tree, len(trees) - first_tree, thr))
+        raw = _f32(st.find("stage_threshold").text)
+        thr = np.float32(raw - THRESHOLD_EPS)
+        par = int(st.find("parent").text) if st.find("parent") is not None else len(stages) - 1
+        nxt = int(st.find("next").text) if st.find("next") is not None else -1
+        stages.append((first_tree, len(trees) - first_tree, thr, raw, par, nxt))
     return _finish(win, stages, trees, nodes, tilted)
 
 
@@ -151,8 +162,9 @@ def _load_new(root_el):
                      "rval": leaves[-r] if r <= 0 else np.float32(0)}
                 nodes.append(d)
             trees.append((first_node, nn))
-        thr = np.float32(_f32(st.find("stageThreshold").text) - THRESHOLD_EPS)
-        stages.append((first_tree, len(trees) - first_tree, thr))
+        raw = _f32(st.find("stageThreshold").text)
+        thr = np.float32(raw - THRESHOLD_EPS)
+        stages.append((first_tree, len(trees) - first_tree, thr, raw, len(stages) - 1, -1))      # the new format has no stage tree
     return _finish(win, stages, trees, nodes, tilted)
 
 

@@ -41,8 +41,8 @@ class Counters(C.Structure):
 def build(force: bool = False) -> str:
     """Compile ``libhaar_oracle.so`` with gcc (recipe: oracle/Makefile)."""
     so = os.path.join(_HERE, "libhaar_oracle.so")
-    src = os.path.join(_HERE, "haar_oracle.c")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("haar_oracle.c", "haar_legacy.c", "haar_oracle.h")]
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "CC=gcc"])
     return so
 

@@ -136,3 +136,19 @@ def inexact_cascade(path, out_path, every=4):
     with open(out_path, "w") as fh:
         fh.write(old_format_xml(f, tiny))
     return str(out_path)
+
+
+def stage_tree_cascade(out_path, win=(20, 20)):
+    """An old-format cascade whose stages form a TREE (like haarcascade_frontalface_alt_tree.xml:1303-1304): stage 0 is the
+    root and passes every window; stage 1 (parent 0, next 2) rejects every window; stage 2 (parent 0) passes every
+    window.  Walked as a tree (OpenCV 2.4) every window is accepted through the `next` branch; evaluated in file order
+    (OpenCV 4.x) every window dies at stage 1."""
+    def stage(thr, parent, nxt):
+        return ("<_><trees><_><_><feature><rects><_>1 1 4 4 -1.</_><_>2 2 2 2 2.</_></rects><tilted>0</tilted></feature>"
+                "<threshold>0.1</threshold><left_val>1.</left_val><right_val>1.</right_val></_></_></trees>"
+                f"<stage_threshold>{thr}</stage_threshold><parent>{parent}</parent><next>{nxt}</next></_>")
+    with open(out_path, "w") as fh:
+        fh.write('<?xml version="1.0"?>\n<opencv_storage><c type_id="opencv-haar-classifier">'
+                 f"<size>{win[0]} {win[1]}</size><stages>" + stage(0.5, -1, -1) + stage(5.0, 0, 2) + stage(0.5, 0, -1) +
+                 "</stages></c></opencv_storage>")
+    return str(out_path)

@@ -190,3 +190,54 @@ def test_inexact_stage_sums_match_cv2_bitwise(orc, cv2ref, synth, tmp_path):
     r, _, wt = cc.detectMultiScale3(g, scaleFactor=1.1, minNeighbors=0, minSize=(30, 30), outputRejectLevels=True)
     assert len(raw) == len(r) > 0
     assert sorted(sums.tolist()) == sorted(np.asarray(wt).reshape(-1).tolist())
+
+
+# ---- the OpenCV-2.4 legacy restatement (oracle/haar_legacy.c).  Its evaluator is UNPINNED (no OpenCV 2.4
+# exists here); the pieces cv2 4.13 still computes the same way are pinned below. ----
+
+def test_legacy_resize_and_integrals_match_cv2(synth):
+    """cvResize's 11-bit INTER_LINEAR survives unchanged as cv2.INTER_LINEAR for 8-bit images, and the int32 / double
+    integral pair is cv2.integral2(CV_32S, CV_64F): both legacy building blocks are bit-equal to cv2 4.13."""
+    import cv2
+    from oracle import legacy
+    g = synth.gray_frame(640, 360, 6, 0)
+    for dw, dh in ((582, 327), (291, 164), (100, 57), (397, 224), (640, 360), (33, 19)):
+        assert np.array_equal(legacy.resize_linear(g, dw, dh), cv2.resize(g, (dw, dh), interpolation=cv2.INTER_LINEAR)), (dw, dh)
+    small = legacy.resize_linear(g, 291, 164)
+    S, SQ = legacy.integral(small)
+    s2, q2 = cv2.integral2(small, sdepth=cv2.CV_32S, sqdepth=cv2.CV_64F)
+    assert np.array_equal(S, s2) and np.array_equal(SQ, q2)
+    bgr = synth.bgr_frame(320, 180, 2, 1)
+    y = cv2.cvtColor(bgr, cv2.COLOR_BGR2YCrCb)[:, :, 0]                   # the 14-bit coefficients are what 4.x keeps for Y
+    assert np.array_equal(legacy.bgr2gray(bgr), y)
+
+
+def test_legacy_stage_tree_is_walked_as_a_tree(orc, cv2ref, synth, tmp_path):
+    """The <parent>/<next> tree: on a crafted three-stage tree every window is accepted through the `next` branch, while
+    the 4.x evaluation in file order rejects everything; on the real alt_tree file the two branches after stage 4 are
+    both walked (a window failing in the first moves on to the second)."""
+    from conftest import stage_tree_cascade
+    from oracle import legacy
+    p = stage_tree_cascade(tmp_path / "tree.xml")
+    oc = orc.OracleCascade.load(p)
+    assert oc.flat.stage_parent.tolist() == [-1, 0, 0] and oc.flat.stage_next.tolist() == [-1, 2, -1]
+    g = synth.gray_frame(160, 120, 1, 0)
+    raw, ctr, smap = legacy.detect_raw(oc, g, want_map=True)
+    assert len(raw) == ctr["grid_windows"] > 0 and (smap == 3).all()       # every window accepted (through stage 2)
+    raw4, _, ctr4 = orc.detect_raw(oc, g)
+    assert len(raw4) == 0                                                   # file order: stage 1 kills everything
+    ot = orc.OracleCascade.load(cv2ref.cascade_path("alt_tree"))
+    if ot.flat.stage_next.max() >= 0:                                       # the old-format file (the new format has no tree)
+        g2 = synth.gray_frame(640, 360, 6, 0)
+        _, _, m2 = legacy.detect_raw(ot, g2, want_map=True)
+        last = set(np.unique(m2).tolist())
+        # a window that fails in branch A (5, 7, 9, ... 39) moves on to branch B (6, 8, ... 46): no window can END in A
+        assert not (last & set(range(5, 40, 2))) and (last & {6, 8, 10, 12})
+        assert ot.flat.nstages in last                                      # and some are accepted
+
+
+def test_legacy_scale_list(orc):
+    from oracle import legacy
+    f = legacy.scale_list(1280, 720, 20, 20)
+    assert len(f) > 25 and f[0] >= 1.5 and np.allclose(f[1:] / f[:-1], 1.1)
+    assert int(np.rint(20 * f[0])) >= 30 > int(np.rint(20 * f[0] / 1.1))

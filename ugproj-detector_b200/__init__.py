@@ -33,7 +33,7 @@ class Params(C.Structure):
     _fields_ = [("scale_factor", C.c_double), ("min_neighbors", C.c_int32), ("min_w", C.c_int32),
                 ("min_h", C.c_int32), ("max_w", C.c_int32), ("max_h", C.c_int32),
                 ("skin_lower", C.c_uint8 * 3), ("skin_upper", C.c_uint8 * 3), ("_pad", C.c_uint8 * 2),
-                ("dense_stages", C.c_int32), ("max_raw_per_frame", C.c_int32)]
+                ("dense_stages", C.c_int32), ("max_raw_per_frame", C.c_int32), ("legacy_24", C.c_int32)]
 
 
 class CascadeInfo(C.Structure):

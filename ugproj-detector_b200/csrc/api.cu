@@ -108,6 +108,14 @@ struct ugd_detector {
         DevPtr send, recv, packed;
         int* h_packed = nullptr; size_t h_packed_cap = 0;
     } shard;
+    // OpenCV-2.4 compatibility mode (ugd_params.legacy_24): its own plans, cascade tables and planes
+    struct LegacyDev {
+        LegacyPlan host;
+        DevPtr levels, tab, c0;
+    };
+    std::map<std::pair<int, int>, std::unique_ptr<LegacyDev>> lg_plans;
+    DevPtr lg_nodes, lg_thr24, lg_parent, lg_next, lg_child, lg_img, lg_S, lg_SQ;
+    const LegacyDev* last_lg = nullptr;
     ScanConstImage const_img;                         // host image of this detector's __constant__ data
     cudaEvent_t ev_const_use = nullptr;               // recorded after every k_scan launch of this detector
     std::string err;
@@ -353,7 +361,14 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
 void mark(ugd_detector* d, int k) { if (d->profiling) cudaEventRecord(d->ev[k], d->stream); }
 
 // Host side of a finished group: results and counters from the pinned staging area (frames f0 .. f0+n of the call).
-void finish_group(ugd_detector* d, const Plan& p, int f0, int nframes, ugd_rect* out, int cap, int* counts, bool* overflow) {
+struct PlanTotals { int64_t levels, level_pixels, grid_windows; };
+PlanTotals plan_totals(const ugd_detector* d, const Plan& p) {
+    if (d->prm.legacy_24 && d->last_lg) return {(int64_t)d->last_lg->host.levels.size(), d->last_lg->host.level_pixels, d->last_lg->host.grid_windows};
+    return {(int64_t)p.levels.size(), p.level_pixels, p.grid_windows};
+}
+
+void finish_group(ugd_detector* d, const Plan& p0, int f0, int nframes, ugd_rect* out, int cap, int* counts, bool* overflow) {
+    const PlanTotals p = plan_totals(d, p0);
     for (int f = 0; f < nframes; ++f) {
         const int n = d->h_counts[f0 + f];
         counts[f] = n;
@@ -371,8 +386,62 @@ void finish_group(ugd_detector* d, const Plan& p, int f0, int nframes, ugd_rect*
     }
     d->ctr.frames += nframes;
     d->ctr.grid_windows += p.grid_windows * nframes;
-    d->ctr.levels = (int64_t)p.levels.size();
+    d->ctr.levels = p.levels;
     d->ctr.level_pixels = p.level_pixels;
+}
+
+int get_legacy_plan(ugd_detector* d, int w, int h, const ugd_detector::LegacyDev** out) {
+    auto key = std::make_pair(w, h);
+    auto it = d->lg_plans.find(key);
+    if (it != d->lg_plans.end()) { *out = it->second.get(); return UGD_OK; }
+    std::unique_ptr<ugd_detector::LegacyDev> lp(new ugd_detector::LegacyDev);
+    const Cascade& c = *d->casc;
+    build_legacy_plan(w, h, c.win_w, c.win_h, d->prm.scale_factor, d->prm.min_w, d->prm.min_h, d->prm.max_w, d->prm.max_h, lp->host);
+    int rc;
+    if ((rc = upload(d, lp->levels, lp->host.levels))) return rc;
+    if ((rc = upload(d, lp->tab, lp->host.tab))) return rc;
+    if ((rc = upload(d, lp->c0, lp->host.c0))) return rc;
+    if (!d->lg_nodes.p) {                              // the hidden cascade of 2.4, once per detector
+        LegacyCascadeHost lc;
+        build_legacy_cascade(c, lc);
+        if ((rc = upload(d, d->lg_nodes, lc.nodes))) return rc;
+        if ((rc = upload(d, d->lg_thr24, lc.thr24))) return rc;
+        if ((rc = upload(d, d->lg_child, lc.child))) return rc;
+        if ((rc = upload(d, d->lg_parent, c.stage_parent))) return rc;
+        if ((rc = upload(d, d->lg_next, c.stage_next))) return rc;
+    }
+    CK(cudaStreamSynchronize(d->stream));
+    *out = lp.get();
+    d->lg_plans[key] = std::move(lp);
+    return UGD_OK;
+}
+
+// The scan of the OpenCV-2.4 compatibility mode in place of resize .. k_scan (everything on `st`).
+int run_legacy_scan(ugd_detector* d, const DevBufs& b, int nframes, cudaStream_t st) {
+    const ugd_detector::LegacyDev* lp = nullptr;
+    int rc;
+    if ((rc = get_legacy_plan(d, b.w, b.h, &lp))) return rc;
+    const LegacyPlan& p = lp->host;
+    const size_t F = (size_t)nframes;
+    CK(d->lg_img.reserve(F * p.img_bytes + 256));
+    CK(d->lg_S.reserve(F * p.int_entries * 4 + 256));
+    CK(d->lg_SQ.reserve(F * p.int_entries * 8 + 256));
+    if (d->want_map) CK(d->stage_map.reserve(std::max<size_t>(p.map_entries, 1) * 2 + 256));
+    LegacyArgs a{};
+    a.levels = lp->levels.as<LegacyLevel>(); a.tab = lp->tab.as<uint32_t>(); a.c0 = lp->c0.as<int16_t>();
+    a.src = b.src_gray; a.src_stride = b.src_stride; a.src_pitch = b.src_pitch; a.w = b.w; a.h = b.h;
+    a.img = d->lg_img.as<uint8_t>(); a.img_stride = p.img_bytes;
+    a.S = d->lg_S.as<int32_t>(); a.SQ = d->lg_SQ.as<double>(); a.int_stride = p.int_entries;
+    a.win_w = b.win_w; a.win_h = b.win_h; a.nstages = b.nstages;
+    a.nodes = d->lg_nodes.as<LegacyNode>(); a.stage_first_tree = b.stage_first_tree; a.stage_ntrees = b.stage_ntrees;
+    a.tree_first_node = b.tree_first_node;
+    a.thr24 = d->lg_thr24.as<float>(); a.parent = d->lg_parent.as<int32_t>(); a.next = d->lg_next.as<int32_t>(); a.child = d->lg_child.as<int32_t>();
+    a.raw = b.raw; a.rawsum = b.rawsum; a.rawcap = b.rawcap; a.rawcount = b.rawcount;
+    a.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr; a.counters = b.counters;
+    if (a.stage_map) CK(cudaMemsetAsync(a.stage_map, 0x80, std::max<size_t>(p.map_entries, 1) * 2, st));
+    launch_legacy(a, p, nframes, st);
+    d->last_lg = lp;
+    return UGD_OK;
 }
 
 // One group of <= max_batch frames already resident on the device (frames f0.. of the call).  With `defer` the
@@ -422,7 +491,9 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
     b.grp_scratch = d->grp.as<int>(); b.grp_stride = 11 * (size_t)d->rawcap;
     b.out = d->out.as<ugd_rect>(); b.outcap = cap; b.outcount = d->outcount.as<int>();
-    b.min_neighbors = d->prm.min_neighbors;
+    const bool legacy = d->prm.legacy_24 != 0;
+    b.min_neighbors = legacy && d->prm.min_neighbors != 0 ? std::max(d->prm.min_neighbors, 1) : d->prm.min_neighbors;
+    b.no_clip = legacy ? 1 : 0; b.gray14 = legacy ? 1 : 0;
     b.counters = d->counters.as<unsigned long long>();
     cudaStream_t st = d->stream;                      // scan stage (and everything, without the group pipeline)
     cudaStream_t si = ovl ? d->img_stream : st;       // image stage
@@ -436,14 +507,14 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     mark(d, 1);
     if (is_bgr) launch_equalize(b, si);
     mark(d, 2);
-    launch_resize_colsum(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), si);    // pyramid + strip column sums in one kernel
+    if (!legacy) launch_resize_colsum(b, dp->wk_resize.as<WorkItem>(), (int)p.wk_resize.size(), si);    // pyramid + strip column sums in one kernel
     mark(d, 3);
     mark(d, 4);
-    launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), si);
+    if (!legacy) launch_carry(b, dp->wk_carry.as<WorkItem>(), (int)p.wk_carry.size(), si);
     mark(d, 5);
-    launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), si);
+    if (!legacy) launch_integral_bands(b, dp->wk_bands.as<WorkItem>(), (int)p.wk_bands.size(), si);
     mark(d, 6);
-    if (b.T) launch_tilted(b, p.max_level_w, si);
+    if (b.T && !legacy) launch_tilted(b, p.max_level_w, si);
     mark(d, 7);
     if (ovl) {
         CK(cudaEventRecord(d->ev_img_done[set], si));
@@ -451,8 +522,10 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     }
     CK(cudaMemsetAsync(b.rawcount, 0, (size_t)nframes * 4, st));
     CK(cudaMemsetAsync(b.counters, 0, (size_t)nframes * kCtrPerFrame * 8, st));
-    if (b.stage_map) CK(cudaMemsetAsync(b.stage_map, 0x80, p.pos_entries * 2, st));
-    {
+    if (b.stage_map && !legacy) CK(cudaMemsetAsync(b.stage_map, 0x80, p.pos_entries * 2, st));
+    if (legacy) {
+        if ((rc = run_legacy_scan(d, b, nframes, st))) return rc;
+    } else {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
         if ((rc = scan_with_constants(d, b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st))) return rc;
@@ -565,7 +638,7 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
     const bool pipelined = tight_host && !d->profiling && nframes > d->max_batch;
     // More than one group: the image stage of group g+1 overlaps the scan stage of group g (two buffer sets, two streams).
     static const bool no_overlap = getenv("UGD_NO_OVERLAP") != nullptr;
-    const bool overlap = !no_overlap && !d->profiling && !d->want_map && nframes > d->max_batch;
+    const bool overlap = !no_overlap && !d->profiling && !d->want_map && !d->prm.legacy_24 && nframes > d->max_batch;
     const bool defer = pipelined || async_submit || overlap;
     if (pipelined) CK(d->stage2.reserve((size_t)d->max_batch * st_stride + 256));
     cudaStream_t in_stream = overlap ? d->img_stream : d->stream;      // the stream that consumes the input frames
@@ -798,7 +871,8 @@ void ugd_destroy(ugd_detector* d) {
     for (auto& kv : d->plans) kv.second->release();
     for (auto& kv : d->area_plans) kv.second->release();
     d->src_full.release(); d->area_dst.release();
-    DevPtr* all[] = {&d->qbase, &d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
+    for (auto& kv : d->lg_plans) { kv.second->levels.release(); kv.second->tab.release(); kv.second->c0.release(); }
+    DevPtr* all[] = {&d->lg_nodes, &d->lg_thr24, &d->lg_parent, &d->lg_next, &d->lg_child, &d->lg_img, &d->lg_S, &d->lg_SQ, &d->qbase, &d->nodeC, &d->nodeM, &d->nodeTA[0], &d->nodeTA[1], &d->nodeTB[0], &d->nodeTB[1], &d->st_first_tree, &d->st_ntrees, &d->st_thr, &d->tree_first_node,
                      &d->st_first_node, &d->bgr, &d->gray_raw, &d->gray_eq, &d->mask, &d->hist, &d->pyr, &d->S, &d->SQ, &d->T,
                      &d->carryS, &d->carryQ, &d->raw, &d->rawsum, &d->rawcount, &d->grp,
                      &d->out, &d->outcount, &d->counters, &d->stage_map, &d->gray_in, &d->S2, &d->SQ2, &d->T2, &d->mask2};
@@ -1005,6 +1079,11 @@ int ugd_get_stage_map(ugd_detector* d, int16_t* map, size_t cap, size_t* n) {
     if (!d || !n || !d->last_plan || !d->last.stage_map) return UGD_ERR_ARG;
     CK(cudaSetDevice(d->device));
     const Plan& p = d->last_plan->host;
+    if (d->prm.legacy_24 && d->last_lg) {              // the legacy scan writes the map in scan order already
+        *n = d->last_lg->host.map_entries;
+        if (map) CK(cudaMemcpy(map, d->stage_map.p, std::min(cap, *n) * 2, cudaMemcpyDeviceToHost));
+        return UGD_OK;
+    }
     *n = p.map_entries;
     if (!map) return UGD_OK;
     std::vector<int16_t> padded(p.pos_entries);

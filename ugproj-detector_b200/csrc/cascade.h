@@ -34,6 +34,8 @@ struct Cascade {
     int max_tree_nodes = 0;
     std::vector<int32_t> stage_first_tree, stage_ntrees;
     std::vector<float>   stage_thr;              // f32(xml) - 1e-5f
+    std::vector<float>   stage_thr_raw;          // f32(xml): the OpenCV-2.4 legacy mode applies its own bias (1e-4)
+    std::vector<int32_t> stage_parent, stage_next;   // the stage tree of the old format (-1 = none); a linear chain otherwise
     std::vector<int32_t> tree_first_node, tree_nnodes;
     std::vector<HostNode> nodes;
     // derived

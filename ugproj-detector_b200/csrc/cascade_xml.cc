@@ -168,7 +168,17 @@ int load_old(const Elem& root, Cascade& c, std::string& err) {
         }
         c.stage_ntrees.push_back(c.ntrees() - c.stage_first_tree.back());
         c.stage_thr.push_back((float)thr - 1e-5f);
+        // the stage tree (only the OpenCV-2.4 legacy mode walks it; 4.x evaluates the stages in file order)
+        double par = (double)c.nstages() - 2.0, nxt = -1.0;
+        one_number(st->child("parent"), par);
+        one_number(st->child("next"), nxt);
+        c.stage_thr_raw.push_back((float)thr);
+        c.stage_parent.push_back((int32_t)par);
+        c.stage_next.push_back((int32_t)nxt);
     }
+    for (int s = 0; s < c.nstages(); ++s)
+        if (c.stage_parent[s] >= s || c.stage_parent[s] < -1 || c.stage_next[s] >= c.nstages() || c.stage_next[s] < -1 ||
+            (c.stage_next[s] >= 0 && c.stage_next[s] <= s)) { err = "malformed stage tree (<parent>/<next>)"; return UGD_ERR_PARSE; }
     c.old_format = true;
     return UGD_OK;
 }
@@ -220,6 +230,9 @@ int load_new(const Elem& root, Cascade& c, std::string& err) {
         }
         c.stage_ntrees.push_back(c.ntrees() - c.stage_first_tree.back());
         c.stage_thr.push_back((float)thr - 1e-5f);
+        c.stage_thr_raw.push_back((float)thr);
+        c.stage_parent.push_back(c.nstages() - 2);        // the new format has no stage tree: a linear chain
+        c.stage_next.push_back(-1);
     }
     c.old_format = false;
     return UGD_OK;

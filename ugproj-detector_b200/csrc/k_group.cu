@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
     const uint8_t* mask = b.mask + (size_t)frame * b.px_stride;
     for (int k = 0; k < nk; ++k) {
         ugd_rect r = kept[k];
+        const ugd_rect unclipped = r;
         const int x0 = max(r.x, 0), y0 = max(r.y, 0), x1 = min(r.x + r.width, b.w), y1 = min(r.y + r.height, b.h);
         bool ok = x1 > x0 && y1 > y0;
         r.x = x0; r.y = y0; r.width = x1 - x0; r.height = y1 - y0;
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
         }
         __syncthreads();
         if (tid == 0) {
-            if (ok) { kept[s_nfinal] = r; ++s_nfinal; }
+            if (ok) { kept[s_nfinal] = b.no_clip ? unclipped : r; ++s_nfinal; }       // (2.4 legacy mode does not clip; the mask mean is over the part inside)
         }
         __syncthreads();
     }

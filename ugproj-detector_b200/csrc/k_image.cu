@@ -45,8 +45,8 @@ __global__ void __launch_bounds__(256) k_preprocess(DevBufs b) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             int B = px[3 * k], G = px[3 * k + 1], R = px[3 * k + 2];
-            int g = (3735 * B + 19235 * G + 9798 * R + 16384) >> 15;
             int Y = (1868 * B + 9617 * G + 4899 * R + 8192) >> 14;
+            int g = b.gray14 ? Y : (3735 * B + 19235 * G + 9798 * R + 16384) >> 15;      // (OpenCV 2.4 used the 14-bit coefficients for BGR2GRAY too)
             int Cr = (int)sat8(((R - Y) * 11682 + 128 * 16384 + 8192) >> 14);
             int Cb = (int)sat8(((B - Y) * 9241 + 128 * 16384 + 8192) >> 14);
             Y = (int)sat8(Y);

@@ -100,6 +100,8 @@ struct DevBufs {
     int* grp_scratch; size_t grp_stride;              // per frame: 11*rawcap ints (labels, class sums, counts, kept rects, class list)
     ugd_rect* out; int outcap; int* outcount;
     int min_neighbors;
+    int no_clip;                                      // OpenCV-2.4 legacy mode: grouped rects are returned as they are
+    int gray14;                                       // OpenCV-2.4 legacy mode: BGR -> gray with the 14-bit coefficients
     unsigned long long* counters;                     // [nframes][kCtrPerFrame]
 };
 
@@ -140,6 +142,37 @@ struct AreaArgs {
 };
 bool build_area_plan(int sw, int sh, int dw, int dh, AreaPlanHost& p);
 void launch_area(const AreaArgs& a, int channels, int nframes, cudaStream_t st);
+
+// ---- OpenCV-2.4 compatibility mode (k_legacy.cu) ----
+struct LegacyLevel {
+    double factor;                                    // the scale as the double running product (rect coordinates use it)
+    int32_t sw, sh, ww, wh, ystep, gx, gy;            // level size, window size in the frame, grid step, grid positions
+    uint32_t img_off, int_off, xtab_off, ytab_off, map_off, pad_;
+};
+struct LegacyPlan {
+    int w = 0, h = 0;
+    std::vector<LegacyLevel> levels;
+    std::vector<uint32_t> tab;                        // per level: sw x entries then sh y entries: (index + 1) | coefficient 1 << 16
+    std::vector<int16_t> c0;                          // coefficient 0 (11 bits)
+    size_t img_bytes = 0, int_entries = 0, map_entries = 0;
+    int64_t grid_windows = 0, level_pixels = 0;
+};
+struct LegacyNode { int32_t rect[3][4]; float w[3]; float thr; int32_t left, right; float lval, rval; int32_t has3; };
+struct LegacyCascadeHost { std::vector<LegacyNode> nodes; std::vector<float> thr24; std::vector<int32_t> child; };
+struct LegacyArgs {
+    const LegacyLevel* levels; const uint32_t* tab; const int16_t* c0;
+    const uint8_t* src; size_t src_stride; int src_pitch, w, h;
+    uint8_t* img; size_t img_stride;
+    int32_t* S; double* SQ; size_t int_stride;
+    int win_w, win_h, nstages;
+    const LegacyNode* nodes; const int32_t* stage_first_tree; const int32_t* stage_ntrees; const int32_t* tree_first_node;
+    const float* thr24; const int32_t* parent; const int32_t* next; const int32_t* child;
+    ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
+    int16_t* stage_map; unsigned long long* counters;
+};
+void build_legacy_plan(int w, int h, int win_w, int win_h, double scale_factor, int min_w, int min_h, int max_w, int max_h, LegacyPlan& p);
+void build_legacy_cascade(const Cascade& c, LegacyCascadeHost& out);
+void launch_legacy(const LegacyArgs& a, const LegacyPlan& p, int nframes, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
 void launch_equalize(const DevBufs& b, cudaStream_t st);
