@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>       // CUtensorMap and its enums only: cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint, libcuda is not linked
 #include <dlfcn.h>
 #include <nccl.h>      // types and prototypes only: libnccl.so.2 is bound at run time (dlopen), never at link time
 
@@ -37,8 +38,13 @@ struct DevPtr {                       // grow-only device allocation
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
     DevPtr levels, xtab, ytab, wk_resize, wk_carry, wk_bands, wk_scan;
+    // TMA tensor maps of the integral planes, one table per buffer set; rebuilt when the planes move or grow
+    DevPtr tmaps[2];
+    const void* tm_S[2] = {nullptr, nullptr}; const void* tm_T[2] = {nullptr, nullptr};
+    int tm_frames[2] = {0, 0};
+    bool tm_ok[2] = {false, false};
     void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release();
-                     wk_carry.release(); wk_bands.release(); wk_scan.release(); }
+                     wk_carry.release(); wk_bands.release(); wk_scan.release(); tmaps[0].release(); tmaps[1].release(); }
 };
 
 struct DevAreaPlan {                  // INTER_AREA tables for one (source size -> scan size) pair
@@ -97,6 +103,8 @@ struct ugd_detector {
     ugd_counters ctr{};
     struct { bool active = false; int nframes = 0, cap = 0; DevPlan* plan = nullptr; } pending;   // ugd_submit_batch ... ugd_wait_batch
     bool profiling = false, want_map = false;
+    bool tma = false;                                 // k_scan stages its grid-step-1 tiles with TMA (the encoder exists and the box fits)
+    bool deint2 = false;                              // S / SQ rows of the grid-step-2 levels are stored de-interleaved (TMA staging of both tile layouts)
     bool truncated = false;                           // some frame of the current call had more rects than cap
     float ktime[UGD_K_COUNT] = {0}; int64_t klaunch[UGD_K_COUNT] = {0};
     cudaEvent_t ev[UGD_K_COUNT + 1] = {nullptr};
@@ -390,6 +398,61 @@ void finish_group(ugd_detector* d, const Plan& p0, int f0, int nframes, ugd_rect
     d->ctr.level_pixels = p.level_pixels;
 }
 
+// ---- TMA tensor maps for k_scan's tile staging ---------------------------------------------------------------------
+// Per level and integral plane (S, and T for tilted cascades): a 3-D int32 tensor (row of P ints, sh + 1 rows, frame) over
+// this buffer set; the box is the scan tile (scan_tma_box).  Grid-step-2 levels get the same map twice -- the kernel asks
+// for the even and the odd columns with two boxes of element stride 2.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+int ensure_tmaps(ugd_detector* d, DevPlan* dp, int set, const int32_t* S, const int32_t* T, int frames_cap) {
+    if (dp->tm_S[set] == S && dp->tm_T[set] == T && dp->tm_frames[set] == frames_cap) return UGD_OK;
+    dp->tm_S[set] = S; dp->tm_T[set] = T; dp->tm_frames[set] = frames_cap; dp->tm_ok[set] = false;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return UGD_OK;                           // no driver entry point: the kernels stage with LDGSTS
+    const Plan& p = dp->host;
+    const Cascade& c = *d->casc;
+    const ScanGeom g = make_scan_geom(c.win_w, c.win_h, c.has_tilted);
+    std::vector<CUtensorMap> maps(p.levels.size() * 4);
+    memset(maps.data(), 0, maps.size() * sizeof(CUtensorMap));
+    for (size_t l = 0; l < p.levels.size(); ++l) {
+        const LevelInfo& L = p.levels[l];
+        const int si = L.step - 1;
+        uint32_t box[3], es[3];
+        if (si && !d->deint2) continue;                // natural rows on a grid-step-2 level: no box (plain staging)
+        if (!scan_tma_box(g, si, box, es)) return UGD_OK;
+        for (int pl = 0; pl < (T ? 2 : 1); ++pl) {
+            // grid step 2: rows are stored [even columns][odd columns] (deint2): one map per half-row
+            for (int hf = 0; hf < (si ? 2 : 1); ++hf) {
+                const int32_t* base = (pl ? T : S) + L.int_off + (si ? hf * (L.P / 2) : 0);
+                const cuuint64_t dims[3] = {(cuuint64_t)(si ? L.P / 2 : L.P), (cuuint64_t)(L.sh + 1), (cuuint64_t)frames_cap};
+                const cuuint64_t strides[2] = {(cuuint64_t)L.P * 4, (cuuint64_t)p.int_ints * 4};
+                CUtensorMap m;
+                if (enc(&m, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, const_cast<int32_t*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+                    return UGD_OK;                     // a shape the encoder refuses: plain staging
+                maps[(l * 2 + pl) * 2 + hf] = m;
+            }
+        }
+    }
+    static_assert(sizeof(CUtensorMap) == 128, "tensor map size");
+    CK(dp->tmaps[set].reserve(std::max<size_t>(maps.size() * sizeof(CUtensorMap), 128)));
+    CK(cudaMemcpyAsync(dp->tmaps[set].p, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice, d->stream));
+    CK(cudaStreamSynchronize(d->stream));
+    dp->tm_ok[set] = true;
+    return UGD_OK;
+}
+
 int get_legacy_plan(ugd_detector* d, int w, int h, const ugd_detector::LegacyDev** out) {
     auto key = std::make_pair(w, h);
     auto it = d->lg_plans.find(key);
@@ -484,6 +547,12 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.pyr = d->pyr.as<uint8_t>(); b.pyr_stride = p.pyr_bytes;
     b.S = (second ? d->S2 : d->S).as<int32_t>(); b.SQ = (second ? d->SQ2 : d->SQ).as<int32_t>(); b.int_stride = p.int_ints;
     b.T = d->casc->has_tilted ? (second ? d->T2 : d->T).as<int32_t>() : nullptr;
+    b.deint2 = d->deint2 ? 1 : 0;
+    if (d->tma) {
+        if ((rc = ensure_tmaps(d, dp, second ? 1 : 0, b.S, b.T, d->max_batch))) return rc;
+        if (!dp->tm_ok[second ? 1 : 0]) { d->err = "tensor maps could not be encoded"; return UGD_ERR_CUDA; }
+        b.tmaps = dp->tmaps[second ? 1 : 0].p;
+    }
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
     b.pos_stride = p.pos_entries;
     b.tile_min = d->tile_min;
@@ -845,6 +914,12 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     if ((e = init_kernel_attributes(cuda_device, d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
     }
+    {   // both tile layouts through TMA <=> the encoder exists, both boxes fit, one plane per tile (the tilted plane keeps the natural layout)
+        const ScanGeom g = make_scan_geom(d->casc->win_w, d->casc->win_h, d->casc->has_tilted);
+        uint32_t box[3], es[3];
+        d->tma = !d->prm.legacy_24 && encode_tiled_fn() && scan_tma_box(g, 0, box, es);
+        d->deint2 = d->tma && !d->casc->has_tilted && scan_tma_box(g, 1, box, es);
+    }
     if (build_scan_constants(*d->casc, d->dense_stages, d->const_img) != cudaSuccess) {
         fprintf(stderr, "ugdet: a dense-stage node has a corner count the scan evaluators do not cover\n"); ugd_destroy(up.release()); return UGD_ERR_UNSUPPORTED;
     }
@@ -1114,6 +1189,17 @@ int ugd_get_level(ugd_detector* d, int level, uint8_t* img, int32_t* S, int32_t*
     const LevelInfo& L = p.levels[level];
     if (img) CK(cudaMemcpy2D(img, L.sw, d->last.pyr + L.img_off, L.img_pitch, L.sw, L.sh, cudaMemcpyDeviceToHost));
     size_t wbytes = (size_t)(L.sw + 1) * 4;
+    if (d->last.deint2 && L.step == 2) {               // rows stored [even columns][odd columns]: put them back in order
+        std::vector<int32_t> row((size_t)L.P * (L.sh + 1));
+        for (int pl = 0; pl < 2; ++pl) {
+            int32_t* dst = pl ? SQ : S;
+            if (!dst) continue;
+            CK(cudaMemcpy(row.data(), (pl ? d->last.SQ : d->last.S) + L.int_off, row.size() * 4, cudaMemcpyDeviceToHost));
+            for (int y = 0; y <= L.sh; ++y)
+                for (int x = 0; x <= L.sw; ++x) dst[(size_t)y * (L.sw + 1) + x] = row[(size_t)y * L.P + (x & 1) * (L.P / 2) + (x >> 1)];
+        }
+        return UGD_OK;
+    }
     if (S) CK(cudaMemcpy2D(S, wbytes, d->last.S + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
     if (SQ) CK(cudaMemcpy2D(SQ, wbytes, d->last.SQ + L.int_off, (size_t)L.P * 4, wbytes, L.sh + 1, cudaMemcpyDeviceToHost));
     return UGD_OK;

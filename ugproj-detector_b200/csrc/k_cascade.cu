@@ -74,22 +74,34 @@ ScanGeom make_scan_geom(int win_w, int win_h, bool tilted) {
             int tp = g.TC[0];
             while (!good_shift(tp & 31)) ++tp;
             g.TP[0] = tp; g.TCH[0] = 0; g.SH[0] = tp & 31;
+            g.OD[0] = 0; g.plane_ints[0] = (g.TR[0] * tp + 31) / 32 * 32;
         } else {
-            int tch = (g.TC[1] + 1) / 2;
-            while (!good_shift((4 * tch) & 31)) ++tch;
-            g.TCH[1] = tch; g.TP[1] = 2 * tch; g.SH[1] = (4 * tch) & 31;
+            // grid step 2: even and odd columns live in two sub-planes ([TR][TCH] each, the odd one OD ints behind the even
+            // one), so that x-adjacent windows (x = 0, 2, 4, ...) sit in consecutive banks -- and so that each sub-plane is
+            // exactly what one TMA box with element stride 2 delivers
+            int tch = ((g.TC[1] + 1) / 2 + 3) & ~3;              // a multiple of 4: every sub-plane row is a whole number of 16-byte units
+            while (!good_shift((2 * tch) & 31)) tch += 4;
+            g.TCH[1] = tch; g.TP[1] = tch; g.SH[1] = (2 * tch) & 31;
+            g.OD[1] = (g.TR[1] * tch + 31) / 32 * 32; g.plane_ints[1] = 2 * g.OD[1];
         }
     }
-    g.tile_ints = std::max(g.TR[0] * g.TP[0], g.TR[1] * g.TP[1]);
+    g.tile_ints = std::max(g.plane_ints[0], g.plane_ints[1]);
     return g;
 }
 
 static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     // byte offset
-    return 4 * (si ? y * g.TP[1] + (x & 1) * g.TCH[1] + (x >> 1) : y * g.TP[0] + x);
+    return 4 * (si ? y * g.TCH[1] + (x & 1) * g.OD[1] + (x >> 1) : y * g.TP[0] + x);
 }
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y) { return tile_off(g, si, x, y); }
+// TMA box of a tile: step 1 = (pitch, rows, 1); step 2 = (sub-plane columns, rows, 1), fetched once per sub-plane.
+// cuTensorMapEncodeTiled takes at most 256 elements per box dimension.
+bool scan_tma_box(const ScanGeom& g, int si, uint32_t (&box)[3], uint32_t (&estride)[3]) {
+    box[0] = (uint32_t)(si ? g.TCH[1] : g.TP[0]); box[1] = (uint32_t)g.TR[si]; box[2] = 1;
+    estride[0] = 1; estride[1] = 1; estride[2] = 1;
+    return box[0] <= 256 && box[1] <= 256 && !getenv("UGD_NO_TMA");
+}
 // The tilted-integral tile (cascades with tilted features only) sits right behind the S tile, same geometry.
-int32_t scan_plane_bytes(const ScanGeom& g, int si) { return 4 * g.TR[si] * g.TP[si]; }
+int32_t scan_plane_bytes(const ScanGeom& g, int si) { return 4 * g.plane_ints[si]; }
 
 // 16-bit byte addresses cover the static shared arrays plus one tile of a small window; anything larger
 // (two tiles for tilted cascades, wide windows) switches the per-lane tables to word offsets.
@@ -537,23 +549,57 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// ---- tile staging: asynchronous global -> shared copies (LDGSTS), 4 bytes per element because the source
-// index is clamped per element and the grid-step-2 layout de-interleaves even / odd columns ----
-__device__ __forceinline__ void cp_async4(int* dst, const int32_t* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+// ---- tile staging ------------------------------------------------------------------------------------------------
+// TMA (cp.async.bulk.tensor): one elected thread asks for the whole patch of an integral plane -- a 3-D box (columns,
+// rows, frame) of a per-level tensor map built on the host -- and every thread waits on an mbarrier for the bytes.
+// Out-of-range rows / columns arrive as zeros (only windows outside the grid ever read them).  On the grid-step-2 levels
+// the integral pass already stores every row as [even columns][odd columns] (TMA cannot stride its innermost dimension),
+// so the patch is two plain boxes, one per sub-plane of the tile.  No per-element address arithmetic, no LDGSTS: SASS
+// shows UTMALDG.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-__device__ __forceinline__ void cp_async_commit_wait() {
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+__device__ __forceinline__ void mbar_expect(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spin = 0; !done; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1 << 24)) __trap();                // a copy that never lands must not hang the device
+    }
+}
+__device__ __forceinline__ void tma_box3(int* dst, const void* tmap, int x, int y, int z, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar)) : "memory");
+}
+// one thread: asks for every plane of the tile whose first window is at level pixel (X0, Y0)
+__device__ __forceinline__ void tma_stage(int* tile, const char* maps, int level, int planes, int plane_ints, int si, int OD, uint32_t bytes,
+                                          int X0, int Y0, int frame, unsigned long long* bar) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the tile's earlier readers (generic proxy) come first
+    mbar_expect(bar, bytes);
+    for (int pl = 0; pl < planes; ++pl) {
+        const char* m = maps + (size_t)((level * 2 + pl) * 2) * 128;
+        int* dst = tile + pl * plane_ints;
+        // grid step 2: the planes are stored de-interleaved (DevBufs::deint2), map 0 = even columns, map 1 = odd columns
+        tma_box3(dst, m, si ? X0 >> 1 : X0, Y0, frame, bar);
+        if (si) tma_box3(dst + OD, m + 128, X0 >> 1, Y0, frame, bar);
+    }
 }
 
+// Fallback (tiles a TMA box cannot describe -- more than 256 columns or rows, i.e. windows wider than 128 pixels -- or a
+// driver without cuTensorMapEncodeTiled): plain loads and shared stores with the source index clamped per element.
 // Copies the patch of one integral plane under the tile whose first window is (xi0, r0) (grid units).
 template <int NW>
 __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict__ plane, int P, int sw, int sh, int X0, int Y0,
-                                           int TR, int TC, int TP, int TCH, int si, int w, int lane) {
+                                           int TR, int TC, int TP, int OD, int si, int w, int lane) {
     for (int r = w; r < TR; r += NW) {
         const int32_t* src = plane + (size_t)min(Y0 + r, sh) * P;
         int* dst = tile + r * TP;
-        for (int c = lane; c < TC; c += 32) cp_async4(dst + (si ? (c & 1) * TCH + (c >> 1) : c), src + min(X0 + c, sw));
+        for (int c = lane; c < TC; c += 32) dst[si ? (c & 1) * OD + (c >> 1) : c] = __ldg(src + min(X0 + c, sw));
     }
 }
 
@@ -607,7 +653,10 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     constexpr int R = kTileRows;
     constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
     static_assert((C == 64 || C == 128) && R == 16 && R % NW == 0, "32 or 64 windows per bank class");
-    extern __shared__ int s_tiles[];
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    // TMA wants its shared destination on 128 bytes: the launch asks for 128 bytes more and the tile buffer starts at the next boundary
+    int* const s_tiles = reinterpret_cast<int*>(s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u));
+    __shared__ __align__(8) unsigned long long s_mbar;
     __shared__ float s_vnf[R * C];
     __shared__ unsigned s_alive[3][NMW][32];           // rotating survivor masks, NMW words per bank class
     __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
@@ -624,7 +673,8 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     const uint32_t pos_off = Lg.pos_off;
     const int si = step - 1;
     const DNodeL* __restrict__ dn = c_dn[si];
-    const int TP = c_geom.TP[si], TCH = c_geom.TCH[si], TC = c_geom.TC[si], TR = c_geom.TR[si], SH = c_geom.SH[si];
+    const int TP = c_geom.TP[si], OD = c_geom.OD[si], TC = c_geom.TC[si], TR = c_geom.TR[si], SH = c_geom.SH[si];
+    const int plane_ints = c_geom.plane_ints[si];
     const int r0 = it.first;
     const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
     const int32_t* Q = b.SQ + (size_t)frame * b.int_stride + Lg.int_off;
@@ -644,27 +694,43 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
 
     // The tile buffer is double (dbl = 1) when shared memory allows: the next tile's patch is then copied
     // asynchronously while this tile is being evaluated, and its latency disappears behind the stages.
-    const int planes = b.T ? 2 : 1, buf_ints = planes * TR * TP;
+    const int planes = b.T ? 2 : 1, buf_ints = planes * plane_ints;
     const int32_t* Tp = b.T ? b.T + (size_t)frame * b.int_stride + Lg.int_off : nullptr;
+    const char* tmaps = reinterpret_cast<const char*>(b.tmaps);     // null: this tile shape has no TMA box (LDGSTS fallback)
+    const uint32_t tma_bytes = (uint32_t)(planes * TR * (si ? 2 * TP : TP) * 4);
+    uint32_t mphase = 0;
+    if (tmaps && tid == 0) mbar_init(&s_mbar, 1);
     int* s_tile = s_tiles;
+    __syncthreads();
     if (dbl) {
-        stage_tile<NW>(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
-        if (Tp) stage_tile<NW>(s_tile + TR * TP, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        if (tmaps) { if (tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, 0, r0 * step, frame, &s_mbar); }
+        else {
+            stage_tile<NW>(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, OD, si, w, lane);
+            if (Tp) stage_tile<NW>(s_tile + plane_ints, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, OD, si, w, lane);
+        }
     }
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96 * NMW; i += NW * 32) (&s_alive[0][0][0])[i] = 0;
         // ---- 1. the S tile (and, for cascades with tilted features, the T tile behind it) ----
-        if (!dbl) {
-            stage_tile<NW>(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
-            if (Tp) stage_tile<NW>(s_tile + TR * TP, Tp, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+        if (tmaps) {
+            if (!dbl && tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, xi0 * step, r0 * step, frame, &s_mbar);
+            mbar_wait(&s_mbar, mphase);
+            mphase ^= 1u;
+        } else {
+            if (!dbl) {
+                stage_tile<NW>(s_tile, S, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+                if (Tp) stage_tile<NW>(s_tile + plane_ints, Tp, P, sw, sh, xi0 * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+            }
         }
-        cp_async_commit_wait();
         __syncthreads();
         if (dbl && xi0 + C < nxg) {                    // prefetch the next tile into the other buffer
             int* nxt = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
-            stage_tile<NW>(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
-            if (Tp) stage_tile<NW>(nxt + TR * TP, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, TCH, si, w, lane);
+            if (tmaps) { if (tid == 0) tma_stage(nxt, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, (xi0 + C) * step, r0 * step, frame, &s_mbar); }
+            else {
+                stage_tile<NW>(nxt, S, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+                if (Tp) stage_tile<NW>(nxt + plane_ints, Tp, P, sw, sh, (xi0 + C) * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+            }
         }
         // ---- 2. variance normalisation + stage 0 + x-skip: a warp owns R / NW rows of the tile and walks each in
         //         segments of 32 windows; everything that depends on the row only is warp-uniform ----
@@ -674,10 +740,15 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
             const bool row_valid = row < nyg;
             const int y = row_valid ? row * step : 0;
             // the four corners of the squared-integral sum over the window's inner (ow-2) x (oh-2) box, as four row pointers
-            const int32_t* qa = Q + ((y + 1) * P + 1);
-            const int32_t* qb = qa + (ow - 2);
-            const int32_t* qc = Q + ((y + oh - 1) * P + 1);
-            const int32_t* qd = qc + (ow - 2);
+            // (de-interleaved rows, grid step 2: column x + dx of an even x lives at half (dx & 1), index x / 2 + dx / 2, so
+            // adjacent windows read adjacent words)
+            const bool dq = b.deint2 && si;
+            const int half = P >> 1, dxb = ow - 1;
+            const int oa = dq ? half : 1, ob = dq ? (dxb & 1) * half + (dxb >> 1) : dxb;
+            const int32_t* qa = Q + ((y + 1) * P + oa);
+            const int32_t* qb = Q + ((y + 1) * P + ob);
+            const int32_t* qc = Q + ((y + oh - 1) * P + oa);
+            const int32_t* qd = Q + ((y + oh - 1) * P + ob);
             const char* trow = reinterpret_cast<const char*>(s_tile + (rl * step) * TP);
             int run_in = (run_par >> k) & 1;           // only the parity of the run length matters
 #pragma unroll 1
@@ -686,13 +757,14 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                 const int c = 32 * h + lane, xi = xi0 + c;
                 const bool valid = row_valid && xi < nxg;
                 const int x = valid ? xi * step : 0;
+                const int xq = dq ? x >> 1 : x;          // index along the SQ row pointers
                 const char* t = trow + 4 * c;
                 float vnf = 1.f;
                 bool ok = false;
                 {
                     const int32_t* no = c_geom.norm_off[si];
                     const int vs = tile_at(t, no[0]) - tile_at(t, no[1]) - tile_at(t, no[2]) + tile_at(t, no[3]);
-                    const uint32_t vq = (uint32_t)qa[x] - (uint32_t)qb[x] - (uint32_t)qc[x] + (uint32_t)qd[x];
+                    const uint32_t vq = (uint32_t)qa[xq] - (uint32_t)qb[xq] - (uint32_t)qc[xq] + (uint32_t)qd[xq];
                     double nf = area * (double)vq - (double)vs * (double)vs;
                     if (nf > 0.0) {
                         nf = sqrt(nf);
@@ -978,22 +1050,24 @@ static int g_scan_smem[64] = {0};
 // Shared memory of one launch: the tile (x2 planes for tilted cascades), doubled when two buffers still leave
 // room for six blocks per SM next to the static arrays (the asynchronous prefetch of the next tile).
 static size_t scan_smem_bytes(const ScanGeom& g, int si, bool tilted, int* dbl) {
-    const size_t one = (size_t)g.TR[si] * g.TP[si] * sizeof(int) * (tilted ? 2 : 1);
+    const size_t one = (size_t)g.plane_ints[si] * sizeof(int) * (tilted ? 2 : 1);
     *dbl = 2 * one + 7 * 1024 <= 37 * 1024 ? 1 : 0;          // 6 blocks x 37 KB < 228 KB
     if (getenv("UGD_SCAN_SINGLE")) *dbl = 0;
-    return one * (*dbl ? 2 : 1);
+    return one * (*dbl ? 2 : 1) + 128;                       // + room to start the tile buffer on a 128-byte boundary
 }
 
 // The work table is ordered by level and the grid-step-2 levels (scale < 2) come first, so the launch is
 // split in two: each half asks only for the shared memory its own tile layout needs.
-void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
+void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
     if (!nblocks) return;
+    DevBufs b = b0;
     const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr);
     for (int half = 0; half < 2; ++half) {
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
         int dbl = 0;
         const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
+        b.tmaps = half || b0.deint2 ? b0.tmaps : nullptr;     // the grid-step-2 launch has TMA boxes only over de-interleaved rows
         const dim3 grid(n, b.nframes);
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const int variant = wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);

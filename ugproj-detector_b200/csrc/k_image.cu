@@ -260,6 +260,17 @@ __device__ __forceinline__ void st256(uint32_t* p, const uint32_t* v) {
                  "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
 }
 
+// One lane's 16 consecutive columns of an integral row.  Natural layout: two 32-byte stores at column X0.  De-interleaved
+// layout (grid-step-2 levels, DevBufs::deint2): a row is [P/2 even columns][P/2 odd columns] -- what k_scan's two
+// sub-plane tiles and its TMA boxes want -- so the 8 even and the 8 odd columns go out as one 32-byte store each.
+__device__ __forceinline__ void store_row16(uint32_t* row, int X0, int P, bool deint, const uint32_t (&v)[16]) {
+    if (!deint) { st256(row + X0, v); st256(row + X0 + 8, v + 8); return; }
+    const uint32_t ev[8] = {v[0], v[2], v[4], v[6], v[8], v[10], v[12], v[14]};
+    const uint32_t od[8] = {v[1], v[3], v[5], v[7], v[9], v[11], v[13], v[15]};
+    st256(row + (X0 >> 1), ev);
+    st256(row + (P >> 1) + (X0 >> 1), od);
+}
+
 __device__ __forceinline__ uint4 load_px16(const uint8_t* row, int x, int pitch) {
     return x < pitch ? *reinterpret_cast<const uint4*>(row + x) : make_uint4(0u, 0u, 0u, 0u);
 }
@@ -278,11 +289,12 @@ __global__ void __launch_bounds__(32) k_integral_bands(DevBufs b, const WorkItem
     uint32_t* outS = reinterpret_cast<uint32_t*>(b.S + (size_t)frame * b.int_stride + L.int_off) + (size_t)Y0 * P;
     uint32_t* outQ = reinterpret_cast<uint32_t*>(b.SQ + (size_t)frame * b.int_stride + L.int_off) + (size_t)Y0 * P;
     const bool stores = X0 < P;                                            // P and X0 are multiples of 16: all 16 columns or none
+    const bool deint = b.deint2 && L.step == 2;
     uint32_t accS[16], accQ[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) { accS[k] = 0; accQ[k] = 0; }
     if (seg == 0) {                                                        // row 0 of both planes is zero
-        if (stores) { st256(outS + X0, accS); st256(outS + X0 + 8, accS + 8); st256(outQ + X0, accQ); st256(outQ + X0 + 8, accQ + 8); }
+        if (stores) { store_row16(outS, X0, P, deint, accS); store_row16(outQ, X0, P, deint, accQ); }
     } else {
         // output row Y0 = prefix along x of the column sums of all pixel rows above (k_colsum + k_carry, strip = 32 rows)
         const size_t co = (size_t)frame * b.carry_stride + L.carry_off + (size_t)(Y0 / kStripRows) * pitch;
@@ -378,9 +390,7 @@ __global__ void __launch_bounds__(32) k_integral_bands(DevBufs b, const WorkItem
             const uint32_t offS = is - rs + leftS[r], offQ = iq - rq + leftQ[r];
 #pragma unroll
             for (int k = 0; k < 16; ++k) { accS[k] += offS; accQ[k] += offQ; }
-            uint32_t* oS = outS + (size_t)(y + 1) * P + X0;
-            uint32_t* oQ = outQ + (size_t)(y + 1) * P + X0;
-            if (stores) { st256(oS, accS); st256(oS + 8, accS + 8); st256(oQ, accQ); st256(oQ + 8, accQ + 8); }
+            if (stores) { store_row16(outS + (size_t)(y + 1) * P, X0, P, deint, accS); store_row16(outQ + (size_t)(y + 1) * P, X0, P, deint, accQ); }
         }
     }
 }

@@ -49,7 +49,9 @@ constexpr int kTileCols = 64;             // (grid-step-1 levels: 128 columns, 6
 constexpr int kScanWarps = 8;              // warps per scan block
 struct ScanGeom {                          // per layout (step 1 / step 2)
     int cols[2];                           // tile width in windows (kTileCols, or twice that: see tile_cols)
-    int TP[2], TCH[2], TC[2], TR[2];       // tile pitch, half pitch (step 2), columns, rows
+    int TP[2], TCH[2], TC[2], TR[2];       // tile row pitch (ints), columns per sub-plane (step 2: == pitch), columns, rows
+    int OD[2];                             // step 2: ints from the even-column sub-plane to the odd-column one (0 for step 1)
+    int plane_ints[2];                     // ints of one integral plane's tile (multiple of 32: the next plane / buffer stays 128-byte aligned)
     int SH[2];                             // bank shift between consecutive window rows: (step * TP) mod 32
     int32_t norm_off[2][4];                // tile BYTE offsets of the 4 variance-normalisation corners
     int tile_ints;                         // ints of shared memory for the tile
@@ -88,6 +90,8 @@ struct DevBufs {
     // pyramid + integrals
     uint8_t* pyr; size_t pyr_stride;
     int32_t* S; int32_t* SQ; size_t int_stride;
+    int deint2;                                       // S / SQ rows of the grid-step-2 levels are stored [even columns][odd columns] (see store_row16, k_scan)
+    const void* tmaps;                                // TMA tensor maps of the S (and T) planes of this buffer set: [level][plane][half] x 128 B; null = LDGSTS staging
     int32_t* T;                                       // tilted integral, same layout as S; null unless the cascade has tilted features
     uint32_t* carryS; uint32_t* carryQ; size_t carry_stride;
     // window scan
@@ -108,6 +112,7 @@ struct DevBufs {
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
 ScanGeom make_scan_geom(int win_w, int win_h, bool tilted);
+bool scan_tma_box(const ScanGeom& g, int si, uint32_t (&box)[3], uint32_t (&estride)[3]);   // the TMA box of a tile, false if it has none
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
 bool scan_word_offsets(const Cascade& c);                         // per-lane tables in words instead of bytes
