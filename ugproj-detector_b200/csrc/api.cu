@@ -81,6 +81,8 @@ struct ugd_detector {
     // group pipeline of multi-group calls: the image stage (preprocess .. integrals, HBM-bound) of group g+1 runs on
     // img_stream next to the scan stage (k_scan + grouping, issue-bound) of group g; S / SQ / T / mask exist twice
     cudaStream_t img_stream = nullptr;
+    cudaStream_t scan_side = nullptr;                 // the grid-step-2 scan launch runs here, next to the grid-step-1 launch
+    cudaEvent_t ev_scan_fork = nullptr, ev_scan_join = nullptr;
     cudaEvent_t ev_img_done[2] = {nullptr, nullptr}, ev_scan_done[2] = {nullptr, nullptr}, ev_call = nullptr;
     bool set_used[2] = {false, false};
     DevPtr S2, SQ2, T2, mask2;
@@ -312,7 +314,8 @@ int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, i
         CK(upload_scan_constants(d->const_img, st));
         bk.uid = d->casc_uid; bk.dense = d->dense_stages;
     }
-    launch_scan(b, wk, nblocks, nblocks_step2, st);
+    static const bool serial = getenv("UGD_SCAN_SERIAL") != nullptr;
+    launch_scan(b, wk, nblocks, nblocks_step2, st, serial ? nullptr : d->scan_side, d->ev_scan_fork, d->ev_scan_join);
     CK(cudaEventRecord(d->ev_const_use, st));
     if (std::find(bk.users.begin(), bk.users.end(), d) == bk.users.end()) bk.users.push_back(d);
     return UGD_OK;
@@ -911,6 +914,9 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     for (auto& ev : d->ev) cudaEventCreate(&ev);
     for (auto& ev : d->ev_area) cudaEventCreate(&ev);
     cudaEventCreateWithFlags(&d->ev_const_use, cudaEventDisableTiming);
+    cudaStreamCreateWithFlags(&d->scan_side, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&d->ev_scan_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&d->ev_scan_join, cudaEventDisableTiming);
     if ((e = init_kernel_attributes(cuda_device, d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
     }
@@ -940,6 +946,9 @@ void ugd_destroy(ugd_detector* d) {
         us.erase(std::remove(us.begin(), us.end(), d), us.end());
     }
     if (d->ev_const_use) cudaEventDestroy(d->ev_const_use);
+    if (d->scan_side) { cudaStreamSynchronize(d->scan_side); cudaStreamDestroy(d->scan_side); }
+    if (d->ev_scan_fork) cudaEventDestroy(d->ev_scan_fork);
+    if (d->ev_scan_join) cudaEventDestroy(d->ev_scan_join);
     comm_release(d);
     d->shard.send.release(); d->shard.recv.release(); d->shard.packed.release();
     if (d->shard.h_packed) cudaFreeHost(d->shard.h_packed);

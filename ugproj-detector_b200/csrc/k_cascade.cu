@@ -1058,11 +1058,19 @@ static size_t scan_smem_bytes(const ScanGeom& g, int si, bool tilted, int* dbl) 
 
 // The work table is ordered by level and the grid-step-2 levels (scale < 2) come first, so the launch is
 // split in two: each half asks only for the shared memory its own tile layout needs.
-void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
+// With a side stream the two launches run CONCURRENTLY (they touch disjoint levels): the grid-step-1 launch goes first on
+// `st`, the grid-step-2 launch next to it on `side`, so the tail of one fills with the blocks of the other.
+void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side,
+                 cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     if (!nblocks) return;
     DevBufs b = b0;
     const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr);
-    for (int half = 0; half < 2; ++half) {
+    const bool both = nblocks_step2 > 0 && nblocks_step2 < nblocks;
+    const bool fork = side && both;
+    if (fork) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
+    for (int pass = 0; pass < 2; ++pass) {
+        const int half = fork ? 1 - pass : pass;               // concurrent: the large grid-step-1 launch is issued first
+        cudaStream_t launch_st = fork && half == 0 ? side : st;
         const int first = half ? nblocks_step2 : 0, n = half ? nblocks - nblocks_step2 : nblocks_step2;
         if (!n) continue;
         int dbl = 0;
@@ -1072,17 +1080,18 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const int variant = wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
         switch (variant) {
-            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
-            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem, st>>>(b, wk + first, dbl); break;
+            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
         }
     }
+    if (fork) { cudaEventRecord(ev_join, side); cudaStreamWaitEvent(st, ev_join, 0); }
 }
 
 cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_tilted) {

@@ -186,7 +186,8 @@ void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_
 void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
 void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st);
 cudaError_t init_tilted_attributes(int device, int max_w);
-void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st);
+void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side = nullptr,
+                 cudaEvent_t ev_fork = nullptr, cudaEvent_t ev_join = nullptr);
 void launch_group(const DevBufs& b, cudaStream_t st);
 void launch_pack_lists(const uint8_t* recv, size_t msg_bytes, int world, int slot_frames, int cap, int skip_rank, int* packed,
                        size_t rect_off_bytes, cudaStream_t st);
