@@ -81,8 +81,11 @@ struct ugd_detector {
     // group pipeline of multi-group calls: the image stage (preprocess .. integrals, HBM-bound) of group g+1 runs on
     // img_stream next to the scan stage (k_scan + grouping, issue-bound) of group g; S / SQ / T / mask exist twice
     cudaStream_t img_stream = nullptr;
-    cudaStream_t scan_side = nullptr;                 // the grid-step-2 scan launch runs here, next to the grid-step-1 launch
-    cudaEvent_t ev_scan_fork = nullptr, ev_scan_join = nullptr;
+    // per buffer set: the grid-step-2 scan launch runs on scan_side[set], next to the grid-step-1 launch; in multi-group calls
+    // the scan stage of set 1 has its own stream (scan2), so consecutive groups overlap and no launch tail leaves SMs idle
+    cudaStream_t scan_side[2] = {nullptr, nullptr}, scan2 = nullptr;
+    cudaEvent_t ev_scan_fork[2] = {nullptr, nullptr}, ev_scan_join[2] = {nullptr, nullptr}, ev_set1 = nullptr;
+    DevPtr raw2, rawsum2, rawcount2, grp2, out2, outcount2, counters2;
     cudaEvent_t ev_img_done[2] = {nullptr, nullptr}, ev_scan_done[2] = {nullptr, nullptr}, ev_call = nullptr;
     bool set_used[2] = {false, false};
     DevPtr S2, SQ2, T2, mask2;
@@ -127,7 +130,10 @@ struct ugd_detector {
     DevPtr lg_nodes, lg_thr24, lg_parent, lg_next, lg_child, lg_img, lg_S, lg_SQ;
     const LegacyDev* last_lg = nullptr;
     ScanConstImage const_img;                         // host image of this detector's __constant__ data
-    cudaEvent_t ev_const_use = nullptr;               // recorded after every k_scan launch of this detector
+    cudaEvent_t ev_const_use[2] = {nullptr, nullptr}; // recorded after every k_scan launch of this detector (one per scan stream)
+    bool const_used[2] = {false, false};
+    cudaEvent_t ev_bank_upload = nullptr;             // this detector's image was (re)uploaded on one of its scan streams ...
+    bool upload_wait[2] = {false, false};             // ... and the other one has to wait for that copy before it scans
     std::string err;
     int sm_count = 148;
 };
@@ -304,19 +310,27 @@ int upload_cascade(ugd_detector* d) {
 }
 
 // Makes this detector's image the resident one (see ConstBank), launches the scan and records the last-use event.
-int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st) {
+int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, int set) {
     std::lock_guard<std::mutex> lk(g_const_mu);
     ConstBank& bk = g_bank[d->device & 63];
     if (bk.uid != d->casc_uid || bk.dense != d->dense_stages) {
         for (ugd_detector* u : bk.users)
-            if (u != d) CK(cudaStreamWaitEvent(st, u->ev_const_use, 0));
+            if (u != d)
+                for (int i = 0; i < 2; ++i)
+                    if (u->const_used[i]) CK(cudaStreamWaitEvent(st, u->ev_const_use[i], 0));
         bk.users.clear();
         CK(upload_scan_constants(d->const_img, st));
         bk.uid = d->casc_uid; bk.dense = d->dense_stages;
+        CK(cudaEventRecord(d->ev_bank_upload, st));
+        d->upload_wait[1 - set] = true; d->upload_wait[set] = false;
+    } else if (d->upload_wait[set]) {                  // the image arrived through this detector's other scan stream
+        CK(cudaStreamWaitEvent(st, d->ev_bank_upload, 0));
+        d->upload_wait[set] = false;
     }
     static const bool serial = getenv("UGD_SCAN_SERIAL") != nullptr;
-    launch_scan(b, wk, nblocks, nblocks_step2, st, serial ? nullptr : d->scan_side, d->ev_scan_fork, d->ev_scan_join);
-    CK(cudaEventRecord(d->ev_const_use, st));
+    launch_scan(b, wk, nblocks, nblocks_step2, st, serial ? nullptr : d->scan_side[set], d->ev_scan_fork[set], d->ev_scan_join[set]);
+    CK(cudaEventRecord(d->ev_const_use[set], st));
+    d->const_used[set] = true;
     if (std::find(bk.users.begin(), bk.users.end(), d) == bk.users.end()) bk.users.push_back(d);
     return UGD_OK;
 }
@@ -341,6 +355,13 @@ int ensure_buffers(ugd_detector* d, const Plan& p, int nframes, bool need_bgr, i
         CK(d->S2.reserve(F * p.int_ints * 4 + 256));
         CK(d->SQ2.reserve(F * p.int_ints * 4 + 256));
         if (d->casc->has_tilted) CK(d->T2.reserve(F * p.int_ints * 4 + 256));
+        CK(d->raw2.reserve(F * d->rawcap * sizeof(ugd_rect)));
+        CK(d->rawsum2.reserve(F * d->rawcap * sizeof(double)));
+        CK(d->rawcount2.reserve(F * 4));
+        CK(d->grp2.reserve(F * 11 * (size_t)d->rawcap * 4));
+        CK(d->out2.reserve(F * (size_t)outcap * sizeof(ugd_rect)));
+        CK(d->outcount2.reserve(F * 4));
+        CK(d->counters2.reserve(F * kCtrPerFrame * 8));
     }
     CK(d->carryS.reserve(F * p.carry_ints * 4 + 256));
     CK(d->carryQ.reserve(F * p.carry_ints * 4 + 256));
@@ -559,15 +580,16 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.carryS = d->carryS.as<uint32_t>(); b.carryQ = d->carryQ.as<uint32_t>(); b.carry_stride = p.carry_ints;
     b.pos_stride = p.pos_entries;
     b.tile_min = d->tile_min;
-    b.raw = d->raw.as<ugd_rect>(); b.rawsum = d->rawsum.as<double>(); b.rawcap = d->rawcap; b.rawcount = d->rawcount.as<int>();
+    b.raw = (second ? d->raw2 : d->raw).as<ugd_rect>(); b.rawsum = (second ? d->rawsum2 : d->rawsum).as<double>(); b.rawcap = d->rawcap;
+    b.rawcount = (second ? d->rawcount2 : d->rawcount).as<int>();
     b.stage_map = d->want_map ? d->stage_map.as<int16_t>() : nullptr;
-    b.grp_scratch = d->grp.as<int>(); b.grp_stride = 11 * (size_t)d->rawcap;
-    b.out = d->out.as<ugd_rect>(); b.outcap = cap; b.outcount = d->outcount.as<int>();
+    b.grp_scratch = (second ? d->grp2 : d->grp).as<int>(); b.grp_stride = 11 * (size_t)d->rawcap;
+    b.out = (second ? d->out2 : d->out).as<ugd_rect>(); b.outcap = cap; b.outcount = (second ? d->outcount2 : d->outcount).as<int>();
     const bool legacy = d->prm.legacy_24 != 0;
     b.min_neighbors = legacy && d->prm.min_neighbors != 0 ? std::max(d->prm.min_neighbors, 1) : d->prm.min_neighbors;
     b.no_clip = legacy ? 1 : 0; b.gray14 = legacy ? 1 : 0;
-    b.counters = d->counters.as<unsigned long long>();
-    cudaStream_t st = d->stream;                      // scan stage (and everything, without the group pipeline)
+    b.counters = (second ? d->counters2 : d->counters).as<unsigned long long>();
+    cudaStream_t st = second ? d->scan2 : d->stream;  // scan stage (and everything, without the group pipeline); set 1 has its own stream
     cudaStream_t si = ovl ? d->img_stream : st;       // image stage
 
     if (ovl && d->set_used[set]) CK(cudaStreamWaitEvent(si, d->ev_scan_done[set], 0));   // the set's last reader (group g-2) is done
@@ -600,7 +622,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     } else {
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)p.wk_scan.size() && p.levels[p.wk_scan[n2].level].step == 2) ++n2;
-        if ((rc = scan_with_constants(d, b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st))) return rc;
+        if ((rc = scan_with_constants(d, b, dp->wk_scan.as<WorkItem>(), (int)p.wk_scan.size(), n2, st, second ? 1 : 0))) return rc;
     }
     mark(d, 8);
     launch_group(b, st);
@@ -678,6 +700,7 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
 void drain(ugd_detector* d) {
     if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
     if (d->img_stream) cudaStreamSynchronize(d->img_stream);
+    if (d->scan2) cudaStreamSynchronize(d->scan2);
     if (d->stream) cudaStreamSynchronize(d->stream);
     d->pending.active = false;
 }
@@ -718,6 +741,7 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
         d->set_used[0] = d->set_used[1] = false;
         CK(cudaEventRecord(d->ev_call, d->stream));                   // the image stream starts after whatever the caller queued before
         CK(cudaStreamWaitEvent(d->img_stream, d->ev_call, 0));
+        CK(cudaStreamWaitEvent(d->scan2, d->ev_call, 0));
     }
     int g = 0;
     for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++g) {
@@ -752,6 +776,10 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
         if ((rc = run_group(d, dp, dev, stride, is_bgr, nf, defer ? nullptr : out + (size_t)f0 * cap, cap, defer ? nullptr : counts + f0, f0, defer,
                             overlap ? (g & 1) : -1))) return rc;
         if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], in_stream));      // the image stage was the last reader of the staging buffer
+    }
+    if (overlap && g > 1) {                            // the groups of set 1 ran on their own stream: the call ends when both have
+        CK(cudaEventRecord(d->ev_set1, d->scan2));
+        CK(cudaStreamWaitEvent(d->stream, d->ev_set1, 0));
     }
     if (defer) {
         d->pending.active = true; d->pending.nframes = nframes; d->pending.cap = cap; d->pending.plan = dp;
@@ -913,10 +941,15 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
     for (auto& ev : d->ev) cudaEventCreate(&ev);
     for (auto& ev : d->ev_area) cudaEventCreate(&ev);
-    cudaEventCreateWithFlags(&d->ev_const_use, cudaEventDisableTiming);
-    cudaStreamCreateWithFlags(&d->scan_side, cudaStreamNonBlocking);
-    cudaEventCreateWithFlags(&d->ev_scan_fork, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&d->ev_scan_join, cudaEventDisableTiming);
+    cudaStreamCreateWithFlags(&d->scan2, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&d->ev_set1, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&d->ev_bank_upload, cudaEventDisableTiming);
+    for (int i = 0; i < 2; ++i) {
+        cudaEventCreateWithFlags(&d->ev_const_use[i], cudaEventDisableTiming);
+        cudaStreamCreateWithFlags(&d->scan_side[i], cudaStreamNonBlocking);
+        cudaEventCreateWithFlags(&d->ev_scan_fork[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&d->ev_scan_join[i], cudaEventDisableTiming);
+    }
     if ((e = init_kernel_attributes(cuda_device, d->casc->win_w, d->casc->win_h, d->casc->has_tilted)) != cudaSuccess) {
         fprintf(stderr, "ugdet: kernel attributes: %s\n", cudaGetErrorString(e)); ugd_destroy(up.release()); return UGD_ERR_CUDA;
     }
@@ -940,15 +973,22 @@ void ugd_destroy(ugd_detector* d) {
     cudaSetDevice(d->device);
     if (d->stream) cudaStreamSynchronize(d->stream);
     if (d->img_stream) cudaStreamSynchronize(d->img_stream);
+    if (d->scan2) cudaStreamSynchronize(d->scan2);
     {   // the streams are idle: nothing of this detector reads the constant bank any more
         std::lock_guard<std::mutex> lk(g_const_mu);
         auto& us = g_bank[d->device & 63].users;
         us.erase(std::remove(us.begin(), us.end(), d), us.end());
     }
-    if (d->ev_const_use) cudaEventDestroy(d->ev_const_use);
-    if (d->scan_side) { cudaStreamSynchronize(d->scan_side); cudaStreamDestroy(d->scan_side); }
-    if (d->ev_scan_fork) cudaEventDestroy(d->ev_scan_fork);
-    if (d->ev_scan_join) cudaEventDestroy(d->ev_scan_join);
+    for (int i = 0; i < 2; ++i) {
+        if (d->ev_const_use[i]) cudaEventDestroy(d->ev_const_use[i]);
+        if (d->scan_side[i]) { cudaStreamSynchronize(d->scan_side[i]); cudaStreamDestroy(d->scan_side[i]); }
+        if (d->ev_scan_fork[i]) cudaEventDestroy(d->ev_scan_fork[i]);
+        if (d->ev_scan_join[i]) cudaEventDestroy(d->ev_scan_join[i]);
+    }
+    if (d->scan2) { cudaStreamSynchronize(d->scan2); cudaStreamDestroy(d->scan2); }
+    if (d->ev_set1) cudaEventDestroy(d->ev_set1);
+    if (d->ev_bank_upload) cudaEventDestroy(d->ev_bank_upload);
+    d->raw2.release(); d->rawsum2.release(); d->rawcount2.release(); d->grp2.release(); d->out2.release(); d->outcount2.release(); d->counters2.release();
     comm_release(d);
     d->shard.send.release(); d->shard.recv.release(); d->shard.packed.release();
     if (d->shard.h_packed) cudaFreeHost(d->shard.h_packed);
