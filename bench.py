@@ -398,9 +398,9 @@ class Runner:
 
 
 def launches_per_group(runner, counters):
-    """Kernels of ours per launch group: resize, colsum, carry, integral bands, scan (one launch per grid-step class
+    """Kernels of ours per launch group: resize+colsum, carry, integral bands, scan (one launch per grid-step class
     present), group init / link / finish; + area, preprocess, equalize on the BGR path."""
-    n = 4 + 3
+    n = 3 + 3
     sc, lw, lh, stp = runner.det.plan_info(*(runner.scan or (runner.w, runner.h)))
     n += len(set(int(s) for s in stp))
     if runner.scan:
@@ -475,8 +475,7 @@ def main():
         win_per_frame = ctr["windows_evaluated"] / max(ctr["frames"], 1)
         # algorithmic bytes per frame (DESIGN.md "Kernels and rooflines")
         alg = {
-            "k_resize": src_px + level_px,                         # 1 B/source px read once + 1 B/level px written
-            "k_colsum": level_px,                                  # 1 B/level px read (carry rows are noise)
+            "k_resize": src_px + level_px,                         # 1 B/source px read once + 1 B/level px written (+ the strip column sums: noise)
             "k_integral": level_px + 8 * int_entries,              # 1 B read + two int32 planes written
             "k_scan": 0.0,                                         # L1/shared-bound, see roofline below
             "k_area": 3 * (w * h + src_px) if scan else 0.0,       # BGR: 3 B read per source px + 3 B written per scan px
@@ -499,19 +498,21 @@ def main():
                 v.update({"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak})
         # the image stage as ONE unit: pyramid + both integral planes, whatever kernels it takes (algorithmic bytes:
         # source read once, planes written once; the pyramid itself is an intermediate, not an output of the path)
-        img_ms = sum(kern[k]["ms_per_launch"] for k in ("k_resize", "k_colsum", "k_carry", "k_integral") if k in kern)
-        int_ms = sum(kern[k]["ms_per_launch"] for k in ("k_colsum", "k_carry", "k_integral") if k in kern)
+        img_ms = sum(kern[k]["ms_per_launch"] for k in ("k_resize", "k_carry", "k_integral") if k in kern)
+        int_ms = sum(kern[k]["ms_per_launch"] for k in ("k_carry", "k_integral") if k in kern)   # (the strip column sums are computed inside k_resize)
         key = f"{args.cascade} {w}x{h} group {GROUP_}"
         stage = {}
         if img_ms:
             g1 = (src_px + 8 * int_entries) * GROUP_ / (img_ms * 1e-3) / 1e9
-            stage["image_stage"] = {"what": "pyramid resize + S/SQ integrals of one launch group, all kernels", "ms": img_ms,
+            tb1, tsrc1 = traffic_record("image_stage", key)
+            stage["image_stage"] = {"traffic": tb1, "traffic_source": tsrc1,"what": "pyramid resize + S/SQ integrals of one launch group, all kernels", "ms": img_ms,
                                     "algorithmic_bytes": (src_px + 8 * int_entries) * GROUP_, "achieved": g1, "peak": hbm_peak,
                                     "unit": "GB/s", "frac": g1 / hbm_peak}
         if int_ms:
             g2 = (level_px + 8 * int_entries) * GROUP_ / (int_ms * 1e-3) / 1e9
             tb, tsrc = traffic_record("integral", key)
-            stage["integral_unit"] = {"what": "S/SQ integrals of one launch group (every launch of the integral)", "ms": int_ms,
+            stage["integral_unit"] = {"what": "S/SQ integrals of one launch group: k_carry + k_integral_bands (the strip column sums are "
+                                              "produced by the fused resize kernel)", "ms": int_ms,
                                       "algorithmic_bytes": (level_px + 8 * int_entries) * GROUP_, "achieved": g2, "peak": hbm_peak,
                                       "unit": "GB/s", "frac": g2 / hbm_peak, "traffic": tb, "traffic_source": tsrc}
         casc_ms = kern["k_scan"]["ms_per_launch"] if "k_scan" in kern else 0.0   # both scan launches of a group

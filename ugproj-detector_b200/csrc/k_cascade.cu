@@ -1053,11 +1053,23 @@ static size_t scan_smem_bytes(const ScanGeom& g, int si, bool tilted, int* dbl) 
     const size_t one = (size_t)g.plane_ints[si] * sizeof(int) * (tilted ? 2 : 1);
     *dbl = 2 * one + 7 * 1024 <= 37 * 1024 ? 1 : 0;          // 6 blocks x 37 KB < 228 KB
     if (getenv("UGD_SCAN_SINGLE")) *dbl = 0;
-    return one * (*dbl ? 2 : 1) + 128;                       // + room to start the tile buffer on a 128-byte boundary
+    return one * (*dbl ? 2 : 1);                             // (+ the alignment pad of the variant, see scan_align_pad)
 }
 
 // The work table is ordered by level and the grid-step-2 levels (scale < 2) come first, so the launch is
 // split in two: each half asks only for the shared memory its own tile layout needs.
+// TMA wants the tile buffer on a 128-byte boundary; the dynamic region starts right behind the kernel's static shared
+// arrays, so the pad is (128 - static size mod 128) mod 128 -- asked for exactly, because the grid-step-2 tile fills its
+// sixth of the SM's shared memory to within a few dozen bytes.
+template <class K>
+static size_t scan_align_pad(K kernel) {
+    static const size_t pad = [&] {                    // (one static per kernel variant)
+        cudaFuncAttributes a{};
+        return cudaFuncGetAttributes(&a, kernel) != cudaSuccess ? (size_t)128 : (128 - a.sharedSizeBytes % 128) % 128;
+    }();
+    return pad;
+}
+
 // With a side stream the two launches run CONCURRENTLY (they touch disjoint levels): the grid-step-1 launch goes first on
 // `st`, the grid-step-2 launch next to it on `side`, so the tail of one fills with the blocks of the other.
 void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side,
@@ -1080,15 +1092,15 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const int variant = wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
         switch (variant) {
-            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
-            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem, launch_st>>>(b, wk + first, dbl); break;
+            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, true, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, true, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, true, 64>), launch_st>>>(b, wk + first, dbl); break;
+            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 128>), launch_st>>>(b, wk + first, dbl); break;
+            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 128>), launch_st>>>(b, wk + first, dbl); break;
+            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128>), launch_st>>>(b, wk + first, dbl); break;
         }
     }
     if (fork) { cudaEventRecord(ev_join, side); cudaStreamWaitEvent(st, ev_join, 0); }
@@ -1097,7 +1109,7 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
 cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_tilted) {
     const ScanGeom g = make_scan_geom(win_w, win_h, has_tilted);
     int dbl;
-    const int scan_smem = (int)std::max(scan_smem_bytes(g, 0, has_tilted, &dbl), scan_smem_bytes(g, 1, has_tilted, &dbl));
+    const int scan_smem = (int)std::max(scan_smem_bytes(g, 0, has_tilted, &dbl), scan_smem_bytes(g, 1, has_tilted, &dbl)) + 128;   // + alignment pad
     std::lock_guard<std::mutex> lk(g_attr_mu);
     int& granted = g_scan_smem[device & 63];
     if (scan_smem > granted) {
