@@ -241,6 +241,24 @@ int  ugd_get_level_tilted(ugd_detector* d, int level, int32_t* T);
  * relates it to the nominal 128 B/clk at the device's rated clock. */
 int  ugd_measure_lds_peak(int cuda_device, double* gbytes_per_s, double* bytes_per_clk_per_sm);
 
+/* Integral pass without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  d_img: 8-bit image in DEVICE memory (h rows of w bytes, stride_bytes apart); d_S / d_SQ: DEVICE
+ * planes of (h+1) x (w+1) int32, tight, receiving the same values as ugd_get_level's S and SQ (sum and squared sum,
+ * wrapping int32, zero first row and column).  The work is enqueued on cuda_stream (a cudaStream_t; NULL = the default
+ * stream) of device cuda_device, which is left current; the call does not synchronise.
+ *   - The scratch of the pass (per-strip column sums) is a file-scope static __device__ array of 4 MiB: every GPU that
+ *     loads the library holds it until the process exits.  Limit: w <= UGD_NOALLOC_MAX_W, h <= UGD_NOALLOC_MAX_H;
+ *     anything larger returns UGD_ERR_CAPACITY (and says so on stderr).
+ *   - No cudaMalloc, cudaFree or allocating library routine is called: three kernel launches, plus, on the first call
+ *     per device, one cudaGetSymbolAddress (make that first call outside a graph capture).
+ *   - Every call shares the array, which keeps the last call's contents; each call overwrites all it reads, so no
+ *     clear is needed, but CALLS THAT OVERLAP ON THE GPU RACE: keep them on one stream or order them with events. */
+#define UGD_NOALLOC_MAX_W 4096
+#define UGD_NOALLOC_MAX_H 4096
+int  ugd_integral_noalloc(int cuda_device, const uint8_t* d_img, int w, int h, size_t stride_bytes, int32_t* d_S,
+                          int32_t* d_SQ, void* cuda_stream);
+
 const char* ugd_strerror(int code);
 const char* ugd_last_error(const ugd_detector* d);   /* detail of the detector's last failure */
 const char* ugd_version(void);

@@ -1,0 +1,7 @@
+#!/bin/bash
+# the no-allocation entry point: its test alone in a fresh process, then the whole GPU suite (it is collected last)
+cd /root/repo
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/noalloc_alone.log 2>&1; echo "alone rc=$?" | tee -a gpurun_out/noalloc_alone.log
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/noalloc_suite.log 2>&1; echo "suite rc=$?" | tee -a gpurun_out/noalloc_suite.log
+tail -n 5 gpurun_out/noalloc_alone.log gpurun_out/noalloc_suite.log

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libugdet.so")
-SOURCES = ["api.cu", "k_image.cu", "k_cascade.cu", "k_group.cu", "k_area.cu", "k_probe.cu", "k_legacy.cu", "cascade_xml.cc", "config_ini.cc", "plan.cc"]
+SOURCES = ["api.cu", "k_image.cu", "k_cascade.cu", "k_group.cu", "k_area.cu", "k_probe.cu", "k_legacy.cu", "k_noalloc.cu", "cascade_xml.cc", "config_ini.cc", "plan.cc"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--fmad=false",                      # every float op rounds exactly as written (bit-exact with the oracle)
