@@ -161,6 +161,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     std::unique_ptr<DevPlan> dp(new DevPlan);
     const Cascade& c = *d->casc;
     build_plan(w, h, c.win_w, c.win_h, d->prm.scale_factor, d->prm.min_w, d->prm.min_h, d->prm.max_w, d->prm.max_h, dp->host);
+    build_scan_work(make_scan_geom(c.win_w, c.win_h, c.has_tilted), dp->host.levels, dp->host.wk_scan);   // tile height depends on the level's grid step
     int rc;
     if ((rc = upload(d, dp->levels, dp->host.levels))) return rc;
     if ((rc = upload(d, dp->xtab, dp->host.xtab))) return rc;

@@ -63,13 +63,24 @@ static int tile_cols(int si, int win_w, int win_h, bool tilted) {
     return (tc + 7) * tr * 4 <= 25 * 1024 ? 2 * kTileCols : kTileCols;
 }
 
+// Tile height in windows.  The wide (128-column) tiles of the grid-step-1 levels are also 32 rows high: 128 candidate
+// windows per bank class instead of 64 even the per-class survivor counts out further (rounds x nodes of the in-tile stages
+// -7 % on the oracle's stage maps), every warp gets twice the rounds per stage (fewer warps idle at the end-of-stage
+// barriers) and the halo rows of the S patch are shared by twice as many window rows (52 tile rows for 32 instead of 36 for 16).
+static int tile_rows(int si, int win_w, int win_h, bool tilted) {
+    if (tile_cols(si, win_w, win_h, tilted) != 2 * kTileCols || getenv("UGD_SCAN_R16")) return kTileRows;
+    const int tc = (2 * kTileCols - 1) + win_w + 1, tr = (2 * kTileRows - 1) + win_h + 1;
+    return (tc + 7) * tr * 4 <= 36 * 1024 ? 2 * kTileRows : kTileRows;
+}
+
 ScanGeom make_scan_geom(int win_w, int win_h, bool tilted) {
     ScanGeom g{};
     for (int si = 0; si < 2; ++si) {
         const int step = si + 1;
         g.cols[si] = tile_cols(si, win_w, win_h, tilted);
+        g.rows[si] = tile_rows(si, win_w, win_h, tilted);
         g.TC[si] = (g.cols[si] - 1) * step + win_w + 1;
-        g.TR[si] = (kTileRows - 1) * step + win_h + 1;
+        g.TR[si] = (g.rows[si] - 1) * step + win_h + 1;
         if (si == 0) {
             int tp = g.TC[0];
             while (!good_shift(tp & 31)) ++tp;
@@ -93,6 +104,12 @@ static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     //
     return 4 * (si ? y * g.TCH[1] + (x & 1) * g.OD[1] + (x >> 1) : y * g.TP[0] + x);
 }
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y) { return tile_off(g, si, x, y); }
+// One scan block per g.rows[step - 1] grid rows of a level (the plan's generic table assumes kScanRows everywhere).
+void build_scan_work(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk) {
+    wk.clear();
+    for (int l = 0; l < (int)levels.size(); ++l)
+        for (int r = 0; r < levels[l].nyg; r += g.rows[levels[l].step - 1]) wk.push_back({l, r});
+}
 // TMA box of a tile: step 1 = (pitch, rows, 1); step 2 = (sub-plane columns, rows, 1), fetched once per sub-plane.
 // cuTensorMapEncodeTiled takes at most 256 elements per box dimension.
 bool scan_tma_box(const ScanGeom& g, int si, uint32_t (&box)[3], uint32_t (&estride)[3]) {
@@ -611,12 +628,11 @@ __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict_
 // Warps per block (NW): 16 warps on the same 16 x 128 tile (three blocks per SM, same 48 resident warps) measured 9.5 %
 // slower than 8 (9.78 vs 8.93 ms): half as many rounds per warp leaves fewer window pairs, and twice as many warps
 // wait at every end-of-stage barrier.
-#ifndef UGD_QUEUE_GROUP
-#define UGD_QUEUE_GROUP 1
-#endif
-constexpr int kQueueGroup = UGD_QUEUE_GROUP;           // windows per warp that share a node fetch in the late-stage queue (exact stump cascades)
 #ifndef UGD_SCAN_MINBLOCKS
 #define UGD_SCAN_MINBLOCKS 6
+#endif
+#ifndef UGD_SCAN_MINBLOCKS_TALL
+#define UGD_SCAN_MINBLOCKS_TALL 4                       // 32-row tiles: 50 KB of shared memory per block, four blocks per SM
 #endif
 
 // The survivors of one bank class: bit rl * (C / 32) + h of the mask is the window in tile row rl, column segment h
@@ -624,42 +640,41 @@ constexpr int kQueueGroup = UGD_QUEUE_GROUP;           // windows per warp that 
 template <int NMW>
 struct Live {
     unsigned w[NMW];
-    __device__ __forceinline__ int count() const { return NMW == 1 ? __popc(w[0]) : __popc(w[0]) + __popc(w[1]); }
-    __device__ __forceinline__ bool any() const { return NMW == 1 ? w[0] != 0 : (w[0] | w[1]) != 0; }
+    __device__ __forceinline__ int count() const {
+        int n = 0;
+#pragma unroll
+        for (int i = 0; i < NMW; ++i) n += __popc(w[i]);
+        return n;
+    }
     __device__ __forceinline__ void skip(int n) {      // drop the n lowest live windows
-        if (NMW == 2) {
-            const int p = __popc(w[0]);
-            const bool over = n >= p;
-            unsigned v = over ? w[1] : w[0];
-            for (int i = over ? n - p : n; i > 0 && v; --i) v &= v - 1;
-            if (over) { w[0] = 0; w[1] = v; } else w[0] = v;
-        } else {
-            for (int i = 0; i < n; ++i) w[0] &= w[0] - 1;
+#pragma unroll
+        for (int i = 0; i < NMW; ++i) {
+            const int p = __popc(w[i]);
+            if (n >= p) { w[i] = 0; n -= p; }
+            else { for (; n > 0; --n) w[i] &= w[i] - 1; }
         }
     }
     __device__ __forceinline__ bool pop(int& bit) {    // take the lowest live window; bit = 0 when none is left
-        const bool lo = NMW == 1 || w[0] != 0;
-        unsigned v = lo ? w[0] : w[NMW - 1];
-        const bool act = v != 0;
-        bit = act ? __ffs((int)v) - 1 + (lo ? 0 : 32) : 0;
-        v &= v - 1;
-        if (lo) w[0] = v; else w[NMW - 1] = v;
+        bool act = false;
+        bit = 0;
+#pragma unroll
+        for (int i = 0; i < NMW; ++i)
+            if (!act && w[i]) { bit = __ffs((int)w[i]) - 1 + 32 * i; w[i] &= w[i] - 1; act = true; }
         return act;
     }
 };
 
-template <int MODE, bool WORDS, int C, int NW = kScanWarps>
-__global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarps / NW : 1536 / (NW * 32)) k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
-    constexpr int R = kTileRows;
+template <int MODE, bool WORDS, int C, int R = kTileRows, int NW = kScanWarps>
+__global__ void __launch_bounds__(NW * 32, MODE ? (R == kTileRows ? UGD_SCAN_MINBLOCKS : UGD_SCAN_MINBLOCKS_TALL) * kScanWarps / NW : 1536 / (NW * 32))
+k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
-    static_assert((C == 64 || C == 128) && R == 16 && R % NW == 0, "32 or 64 windows per bank class");
+    static_assert((C == 64 || C == 128) && (R == 16 || R == 32) && R % NW == 0, "32, 64 or 128 windows per bank class");
     extern __shared__ __align__(16) unsigned char s_dyn[];
     // TMA wants its shared destination on 128 bytes: the launch asks for 128 bytes more and the tile buffer starts at the next boundary
     int* const s_tiles = reinterpret_cast<int*>(s_dyn + ((128u - (smem_u32(s_dyn) & 127u)) & 127u));
     __shared__ __align__(8) unsigned long long s_mbar;
     __shared__ float s_vnf[R * C];
     __shared__ unsigned s_alive[3][NMW][32];           // rotating survivor masks, NMW words per bank class
-    __shared__ uint16_t s_list[R * C];                 // survivors of the in-tile stages (window ids)
     __shared__ int s_pop;
     __shared__ unsigned int s_ctr[5];                  // evaluated, lowvar, near, weak, queued
 
@@ -712,6 +727,7 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
     for (int xi0 = 0; xi0 < nxg; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96 * NMW; i += NW * 32) (&s_alive[0][0][0])[i] = 0;
+        if (tid == 0) s_pop = 0;                       // the late-stage queue's class counter (phase 4)
         // ---- 1. the S tile (and, for cascades with tilted features, the T tile behind it) ----
         if (tmaps) {
             if (!dbl && tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, xi0 * step, r0 * step, frame, &s_mbar);
@@ -865,24 +881,33 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                     if (pass0) { emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c0) * step, (r0 + rl0) * step, sum0); if (map) map[(r0 + rl0) * nxg_pad + xi0 + c0] = (int16_t)nstages; }
                     if (pass1) { emit_raw(b, frame, scale, rect_w, rect_h, (xi0 + c1) * step, (r0 + rl1) * step, sum1); if (map) map[(r0 + rl1) * nxg_pad + xi0 + c1] = (int16_t)nstages; }
                 } else {
-                    unsigned pb[NMW];
-#pragma unroll
-                    for (int i = 0; i < NMW; ++i) pb[i] = 0;
-                    if (pass0) pb[NMW == 1 ? 0 : bit0 >> 5] |= 1u << (bit0 & 31);
-                    if (pass1) pb[NMW == 1 ? 0 : bit1 >> 5] |= 1u << (bit1 & 31);
-#pragma unroll
-                    for (int i = 0; i < NMW; ++i)
-                        if (pb[i]) atomicOr(&s_alive[nxt][i][lane], pb[i]);
+                    if (NMW == 1) {                       // one mask word per class: both windows in one atomic
+                        const unsigned pb = (pass0 ? 1u << bit0 : 0u) | (pass1 ? 1u << bit1 : 0u);
+                        if (pb) atomicOr(&s_alive[nxt][0][lane], pb);
+                    } else {
+                        if (pass0) atomicOr(&s_alive[nxt][bit0 >> 5][lane], 1u << (bit0 & 31));
+                        if (pass1) atomicOr(&s_alive[nxt][bit1 >> 5][lane], 1u << (bit1 & 31));
+                    }
                 }
             }
             __syncthreads();
             cur = nxt; ++s;
         }
-        // ---- 4. the few survivors of the in-tile stages: block-local work queue.  The 32 lanes of a warp evaluate 32 weak
-        //         classifiers of a stage against the tile in shared memory (node data from global memory through L1).
-        //         Exact stump cascades: a warp takes kQueueGroup windows at a time and applies every node it fetches to all
-        //         of them, so the node fetch (four loads, the coefficient unpacking) is paid once per group ----
+        // ---- 4. the few survivors of the in-tile stages: block-local work queue.  A warp takes one window at a time from a
+        //         shared counter and its 32 lanes evaluate 32 weak classifiers of a stage against the tile in shared memory
+        //         (node data from global memory through L1); a warp reduction forms the stage sum ----
         if (total > 0 && s < nstages) {
+            const uint4* __restrict__ nA = b.nodeTA[si];
+            const uint4* __restrict__ nB = b.nodeTB[si];
+            if (MODE == 1) {
+            // The survivor list (window ids) lives in the two mask buffers that are dead by now -- everything of s_alive but
+            // the block of `cur` -- so it costs no shared memory of its own; it holds CAP entries, and the rare tile with
+            // more survivors than that (a tile full of faces) is drained in passes of CAP.
+            uint16_t* const lst = reinterpret_cast<uint16_t*>(&s_alive[0][0][0]);
+            constexpr int BLK = NMW * 64, CAP = 2 * BLK;                       // uint16 entries per mask buffer / in the list
+            const int lskip = cur * BLK;                                       // list slot e sits at e, or behind cur's block
+            for (int lo = 0; lo < total; lo += CAP) {
+            const int hi = min(total, lo + CAP);
             if (w == 0) {
                 const int cnt = m.count();
                 int incl = cnt;
@@ -895,33 +920,34 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                 Live<NMW> mm = m;
                 int bit;
                 while (mm.pop(bit)) {
-                    const int rl = bit >> LSEG, c = ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
-                    s_list[pos++] = (uint16_t)(rl * C + c);
+                    if (pos >= lo && pos < hi) {
+                        const int rl = bit >> LSEG, c = ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
+                        const int e = pos - lo;
+                        lst[e < lskip ? e : e + BLK] = (uint16_t)(rl * C + c);
+                    }
+                    ++pos;
                 }
-                if (lane == 0) { s_pop = 0; s_ctr[4] += (unsigned)total; }
+                if (lane == 0) { s_pop = lo; if (lo == 0) s_ctr[4] += (unsigned)total; }
             }
             __syncthreads();
-            const uint4* __restrict__ nA = b.nodeTA[si];
-            const uint4* __restrict__ nB = b.nodeTB[si];
-            if (MODE == 1) {
-                constexpr int KQ = kQueueGroup;
+                constexpr int KQ = 1;                  // (windows per pop that share the node fetches: 2, 3, 4 measured 3-8 % slower)
                 for (;;) {
                     int i0 = 0;
                     if (lane == 0) i0 = atomicAdd(&s_pop, KQ);
                     i0 = __shfl_sync(0xffffffffu, i0, 0);
-                    if (i0 >= total) break;
+                    if (i0 >= hi) break;
                     uint32_t pb2[KQ];
                     float vn[KQ];
                     int wid[KQ];
                     unsigned alive = 0;                 // bit k: window k of the group is still in the cascade (warp-uniform)
 #pragma unroll
                     for (int k = 0; k < KQ; ++k) {
-                        wid[k] = s_list[min(i0 + k, total - 1)];
+                        { const int e = min(i0 + k, hi - 1) - lo; wid[k] = lst[e < lskip ? e : e + BLK]; }
                         vn[k] = s_vnf[wid[k]];
                         const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + ((wid[k] / C) * step) * TP + (wid[k] & (C - 1)));
                         const uint32_t pw = WORDS ? pbase >> 2 : pbase;
                         pb2[k] = pw | pw << 16;
-                        if (i0 + k < total) alive |= 1u << k;
+                        if (i0 + k < hi) alive |= 1u << k;
                     }
                     for (int st = s; st < nstages && alive; ++st) {
                         const int n0 = b.stage_first_node[st], nt = b.stage_ntrees[st];
@@ -961,13 +987,42 @@ __global__ void __launch_bounds__(NW * 32, MODE ? UGD_SCAN_MINBLOCKS * kScanWarp
                         }
                     }
                 }
+            if (hi < total) __syncthreads();           // the list is rebuilt for the next pass
+            }
             } else {
+            // Tree cascades: no list and no barrier in front of the queue -- queue entry i is the (i - excl)-th live window
+            // of the one class whose range [excl, incl) of the running sum of the per-class survivor counts holds i; every
+            // warp finds it in the masks by itself (s_pop was zeroed at the top of the tile)
+            if (tid == 0) s_ctr[4] += (unsigned)total;
+            auto nth_window = [&](int i) -> int {      // window id (tile row * C + column) of queue entry i, warp-uniform
+                Live<NMW> mm;
+#pragma unroll
+                for (int j = 0; j < NMW; ++j) mm.w[j] = s_alive[cur][j][lane];
+                const int cnt = mm.count();
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                const unsigned own = __ballot_sync(0xffffffffu, i >= incl - cnt && i < incl);
+                const int src = __ffs((int)own) - 1;
+                int id = 0;
+                if (lane == src) {
+                    mm.skip(i - (incl - cnt));
+                    int bit;
+                    mm.pop(bit);
+                    const int rl = bit >> LSEG;
+                    id = rl * C + ((lane - SH * rl) & 31) + ((bit & (SEG - 1)) << 5);
+                }
+                return __shfl_sync(0xffffffffu, id, src);
+            };
             for (;;) {
                 int i = 0;
                 if (lane == 0) i = atomicAdd(&s_pop, 1);
                 i = __shfl_sync(0xffffffffu, i, 0);
                 if (i >= total) break;
-                const int id = s_list[i], rl = id / C, c = id & (C - 1);
+                const int id = nth_window(i), rl = id / C, c = id & (C - 1);
                 const float vnf = s_vnf[id];
                 const uint32_t pbase = (uint32_t)__cvta_generic_to_shared(s_tile + (rl * step) * TP + c);
                 const uint32_t pw = WORDS ? pbase >> 2 : pbase;
@@ -1090,7 +1145,8 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         b.tmaps = half || b0.deint2 ? b0.tmaps : nullptr;     // the grid-step-2 launch has TMA boxes only over de-interleaved rows
         const dim3 grid(n, b.nframes);
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
-        const int variant = wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
+        const bool tall = g.rows[half ? 0 : 1] == 2 * kTileRows;          // only ever with wide tiles
+        const int variant = tall ? 9 + b.fast_scan : wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
         switch (variant) {
             case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 64>), launch_st>>>(b, wk + first, dbl); break;
             case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, true, 64>), launch_st>>>(b, wk + first, dbl); break;
@@ -1100,7 +1156,10 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
             case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, true, 64>), launch_st>>>(b, wk + first, dbl); break;
             case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 128>), launch_st>>>(b, wk + first, dbl); break;
             case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 128>), launch_st>>>(b, wk + first, dbl); break;
-            default: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128>), launch_st>>>(b, wk + first, dbl); break;
+            case 8: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128>), launch_st>>>(b, wk + first, dbl); break;
+            case 9: k_scan<0, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
+            case 10: k_scan<1, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
+            default: k_scan<2, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
         }
     }
     if (fork) { cudaEventRecord(ev_join, side); cudaStreamWaitEvent(st, ev_join, 0); }
@@ -1113,9 +1172,10 @@ cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_ti
     std::lock_guard<std::mutex> lk(g_attr_mu);
     int& granted = g_scan_smem[device & 63];
     if (scan_smem > granted) {
-        const void* variants[9] = {(const void*)k_scan<0, false, 64>, (const void*)k_scan<0, true, 64>, (const void*)k_scan<1, false, 64>,
-                                   (const void*)k_scan<1, true, 64>, (const void*)k_scan<2, false, 64>, (const void*)k_scan<2, true, 64>,
-                                   (const void*)k_scan<0, false, 128>, (const void*)k_scan<1, false, 128>, (const void*)k_scan<2, false, 128>};
+        const void* variants[12] = {(const void*)k_scan<0, false, 64>, (const void*)k_scan<0, true, 64>, (const void*)k_scan<1, false, 64>,
+                                    (const void*)k_scan<1, true, 64>, (const void*)k_scan<2, false, 64>, (const void*)k_scan<2, true, 64>,
+                                    (const void*)k_scan<0, false, 128>, (const void*)k_scan<1, false, 128>, (const void*)k_scan<2, false, 128>,
+                                    (const void*)k_scan<0, false, 128, 32>, (const void*)k_scan<1, false, 128, 32>, (const void*)k_scan<2, false, 128, 32>};
         for (const void* f : variants) {
             cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
             if (e != cudaSuccess) return e;

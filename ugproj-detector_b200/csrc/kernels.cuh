@@ -49,6 +49,7 @@ constexpr int kTileCols = 64;             // (grid-step-1 levels: 128 columns, 6
 constexpr int kScanWarps = 8;              // warps per scan block
 struct ScanGeom {                          // per layout (step 1 / step 2)
     int cols[2];                           // tile width in windows (kTileCols, or twice that: see tile_cols)
+    int rows[2];                           // tile height in windows = grid rows per scan block (kTileRows, or twice that: see tile_rows)
     int TP[2], TCH[2], TC[2], TR[2];       // tile row pitch (ints), columns per sub-plane (step 2: == pitch), columns, rows
     int OD[2];                             // step 2: ints from the even-column sub-plane to the odd-column one (0 for step 1)
     int plane_ints[2];                     // ints of one integral plane's tile (multiple of 32: the next plane / buffer stays 128-byte aligned)
@@ -112,6 +113,7 @@ struct DevBufs {
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
 ScanGeom make_scan_geom(int win_w, int win_h, bool tilted);
+void build_scan_work(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk);   // block -> (level, first grid row)
 bool scan_tma_box(const ScanGeom& g, int si, uint32_t (&box)[3], uint32_t (&estride)[3]);   // the TMA box of a tile, false if it has none
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
