@@ -40,7 +40,8 @@ W, H = 1280, 720
 CASCADE = "alt"
 FRAMES_PER_STEP = 256          # 236 MB of input per step (> 126 MB L2); 4 launch groups of 64
 GROUP = 64
-DISTINCT = 32                  # distinct synthetic frames per rank (seeds 1000 * rank + i), tiled to FRAMES_PER_STEP
+DISTINCT = 64                  # distinct synthetic frames (seeds 0 .. DISTINCT-1), tiled to FRAMES_PER_STEP; rank r starts ROTATE * r frames in
+ROTATE = 5                     # so every rank does the same work per step (weak scaling) on a differently ordered stream
 CAP = 64                       # rect slots per frame gathered to rank 0
 REF_SAMPLE = 8                 # frames per step of the reference arm (a bounded sample of the step's frames)
 METRIC = "720p frames/sec (frontalface_alt)"
@@ -114,7 +115,8 @@ def workload_config(cascade_file, w, h, sf, ms, nF, group, world, win, scan=None
     tail = " (BASELINE configs[0]/[1] frame+params)" if (w, h, sf, ms) == (1280, 720, 1.1, 30) and not scan else ""
     return {"workload": head + f"scale {sf}, minNeighbors 2, minSize {ms}x{ms}" + tail,
             "frames_per_step_per_gpu": nF, "launch_group": group, "levels": levels,
-            "frames": f"seeds 1000*rank + i, i < {min(distinct, nF)}, tiled to {nF} per rank per step (SURVEY A.7 generator)",
+            "frames": f"seeds 0..{min(distinct, nF) - 1} (SURVEY A.7 generator), tiled to {nF} per rank per step; rank r starts {ROTATE}*r frames in "
+                      f"(same work on every rank, different order)",
             "l2": f"inputs larger than L2: {nF * w * h * (3 if scan else 1) / 1e6:.0f} MB of frames per step, "
                   f"{group * (level_px + 8 * int_entries) / 1e6:.0f} MB of integrals per launch group",
             "parallelism": f"frames sharded over {world} rank(s), lists gathered to rank 0 (NCCL inside the library)"}
@@ -222,7 +224,7 @@ def run_reference(args, rank, world):
     w, h = map(int, args.size.split("x"))
     nF = args.frames
     sf, ms = args.scale_factor, (args.min_size, args.min_size)
-    frames = make_frames(synth, w, h, min(DISTINCT, nF), seed0=0)          # == rank 0's frames of the repo arm (seeds 1000*0 + i)
+    frames = make_frames(synth, w, h, min(DISTINCT, nF), seed0=0)          # == rank 0's frames of the repo arm (seeds i, no rotation)
     cv2.setNumThreads(os.cpu_count() or 1)
     path = cv2_ref.cascade_path(args.cascade)
     cc = cv2_ref.load(path)
@@ -268,10 +270,11 @@ class Runner:
             env["sharding"].init_comm(self.det, env["rank"], env["world"])
         rank = env["rank"]
         if scan:
-            base = np.stack([synth.bgr_frame(w, h, synth.default_nfaces(w, h), 1000 * rank + i) for i in range(self.distinct)])
-            frames_np = np.ascontiguousarray(np.concatenate([base] * ((nF + len(base) - 1) // len(base)))[:nF])
+            base = np.stack([synth.bgr_frame(w, h, synth.default_nfaces(w, h), i) for i in range(self.distinct)])
         else:
-            frames_np = make_frames(synth, w, h, nF, seed0=1000 * rank, distinct=self.distinct)
+            base = synth.gray_batch(w, h, self.distinct, seed0=0)
+        base = np.roll(base, -ROTATE * rank, axis=0)        # rank r's frame j is distinct frame (j + ROTATE * r) mod distinct
+        frames_np = np.ascontiguousarray(np.concatenate([base] * ((nF + len(base) - 1) // len(base)))[:nF])
         self.pageable = frames_np                            # plain numpy allocation: pageable, like a cv::Mat
         self.host = torch.from_numpy(frames_np).pin_memory()
         self.dev = self.host.cuda(non_blocking=False)
@@ -379,12 +382,13 @@ class Runner:
         single = ug.Detector(self.casc, ug.default_params(scale_factor=self.sf, min_size=self.ms), device=env["local"],
                              max_size=(self.w, self.h), max_batch=per_rank)
         checked, mism = 0, []
+        base = synth.gray_batch(self.w, self.h, self.distinct, seed0=0)
         for r in range(1, env["world"]):
             if len(result[r]) != self.nF:
                 mism.append({"rank": r, "error": f"{len(result[r])} lists gathered, want {self.nF}"})
                 continue
-            fr = synth.gray_batch(self.w, self.h, per_rank, seed0=1000 * r)
-            want = single.detect_batch(fr, cap=CAP)
+            fr = np.roll(base, -ROTATE * r, axis=0)[:per_rank]
+            want = single.detect_batch(np.ascontiguousarray(fr), cap=CAP)
             for i in range(per_rank):
                 for j in range(i, self.nF, self.distinct):
                     checked += 1

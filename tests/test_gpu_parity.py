@@ -221,6 +221,32 @@ def test_scaled_detection_matches_reference_pipeline(dets, synth, orc, cv2ref):
         assert rectset(got[f]) == rectset(det.detect_bgr(small))
 
 
+def test_scaled_fused_decimation_images(ug, synth, orc, cv2ref):
+    """The 2x2 decimation runs inside k_preprocess (no scan-size BGR frame is written): the equalised, masked gray image
+    and the skin mask it leaves are those of the reference pipeline on the cv2-resized frame (detector.cc:13-22 after
+    face_tracker.cc:112-114), byte for byte; sizes the fused form does not take (3x3 factor, scan width not a multiple of
+    4, rational factor) go through k_area and give the same kind of agreement."""
+    import cv2
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    oc = orc.OracleCascade.load(cv2ref.cascade_path("alt"))
+    for (W, H), (sw, sh) in (((1280, 720), (640, 360)), ((1284, 720), (642, 360)), ((960, 540), (320, 180)), ((1280, 720), (854, 480))):
+        det = ug.Detector(casc, ug.default_params(), max_size=(sw, sh), max_batch=2)
+        frames = np.stack([synth.bgr_frame(W, H, 6, 900 + i) for i in range(3)])         # 3 frames > max_batch 2
+        got = det.detect_batch_scaled(frames, (sw, sh))
+        last_group_first = 2                                                             # frame 0 of the last launch group
+        small = cv2.resize(frames[last_group_first], (sw, sh), interpolation=cv2.INTER_AREA)
+        ycc = cv2.cvtColor(small, cv2.COLOR_BGR2YCrCb)
+        mask = cv2.inRange(ycc, (0, 133, 77), (255, 173, 127))
+        gray = cv2.equalizeHist(cv2.cvtColor(small, cv2.COLOR_BGR2GRAY)) & mask
+        g, m = det.preprocessed(sw, sh)
+        assert np.array_equal(m, mask), (W, H, sw, sh)
+        assert np.array_equal(g, gray), (W, H, sw, sh)
+        for f in range(3):
+            want, _ = orc.detect_faces(oc, cv2.resize(frames[f], (sw, sh), interpolation=cv2.INTER_AREA))
+            assert rectset(got[f]) == rectset(want), (W, H, sw, sh, f)
+        det.close()
+
+
 def test_edge_cases(dets, synth, ug):
     casc, det = dets["alt"]
     assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance

@@ -60,5 +60,31 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def build_variant(name: str, defines: list[str]) -> str:
+    """A differently compiled copy of the library (e.g. -DUGD_CHECKED=1: device-side bounds checks on every access to the
+    scan tiles) as build/libugdet_<name>.so; load it with UGD_LIB=<path>.  The product build is untouched."""
+    objdir = os.path.join(HERE, "build", name)
+    os.makedirs(objdir, exist_ok=True)
+    out = os.path.join(HERE, "build", f"libugdet_{name}.so")
+    objs = []
+    for s in SOURCES:
+        o = os.path.join(objdir, s + ".o")
+        cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-c", os.path.join(CSRC, s), "-o", o]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError(f"nvcc failed on {s}")
+        objs.append(o)
+    r = subprocess.run([_nvcc(), "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a"], capture_output=True, text=True)
+    if r.returncode:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("link failed")
+    return out
+
+
 if __name__ == "__main__":
+    if "--checked" in sys.argv:
+        print(build_variant("checked", ["UGD_CHECKED=1"]))
+        sys.exit(0)
+
     print(build(force="--force" in sys.argv, verbose=True))

@@ -77,6 +77,9 @@ struct ugd_detector {
     int dense_stages = 1, dense_nodes = 0, rawcap = 8192, tile_min = 32;
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};   // host-input pipeline
+    // ugd_detect_batch_scaled with a 2x2 decimation: the full-size frames of the group being enqueued (k_preprocess decimates
+    // them itself, see launch_preprocess) and the event to record once that kernel -- their last reader -- is in the stream
+    const uint8_t* area2_src = nullptr; size_t area2_row_stride = 0, area2_frame_stride = 0; cudaEvent_t area2_consumed = nullptr;
     DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
     // group pipeline of multi-group calls: the image stage (preprocess .. integrals, HBM-bound) of group g+1 runs on
     // img_stream next to the scan stage (k_scan + grouping, issue-bound) of group g; S / SQ / T / mask exist twice
@@ -565,6 +568,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     b.use_skin = is_bgr ? 1 : 0;
     if (is_bgr) {
         b.bgr = dev_frames; b.bgr_stride = frame_stride;
+        b.area2_src = d->area2_src; b.area2_row_stride = d->area2_row_stride; b.area2_frame_stride = d->area2_frame_stride;
         b.src_gray = b.gray_eq; b.src_stride = b.px_stride; b.src_pitch = p.w;
     } else {
         b.src_gray = dev_frames; b.src_stride = frame_stride; b.src_pitch = p.w;
@@ -598,6 +602,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     if (is_bgr) {
         CK(cudaMemsetAsync(b.hist, 0, (size_t)nframes * 256 * 4, si));
         launch_preprocess(b, si);
+        if (d->area2_consumed) CK(cudaEventRecord(d->area2_consumed, si));
     }
     mark(d, 1);
     if (is_bgr) launch_equalize(b, si);
@@ -1101,11 +1106,24 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
             }
             src = in;
         }
-        if (d->profiling) cudaEventRecord(d->ev_area[0], d->stream);
-        launch_area(area_args(*ap, src, (size_t)src_w * 3, stight, d->bgr.as<uint8_t>(), dstride), 3, nf, d->stream);
-        if (d->profiling) cudaEventRecord(d->ev_area[1], d->stream);
-        if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));      // the input buffer is free once k_area has run
-        if ((rc = run_group(d, dp, d->bgr.as<uint8_t>(), dstride, true, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, pipelined))) return rc;
+        // A 2x2 decimation (the shipped cfg: 1280x720 -> 640x360) is done inside k_preprocess: no k_area launch, the scan-size
+        // BGR frame is never written
+        static const bool no_fuse = getenv("UGD_NO_AREA_FUSE") != nullptr;
+        const bool fuse = !no_fuse && ap->host.fast && ap->host.ix == 2 && ap->host.iy == 2 &&
+                          preprocess_can_fuse_area2(src, (size_t)src_w * 3, stight, scan_w);
+        if (fuse) {
+            d->area2_src = src; d->area2_row_stride = (size_t)src_w * 3; d->area2_frame_stride = stight;
+            d->area2_consumed = pipelined ? d->ev_consumed[g & 1] : nullptr;
+        } else {
+            if (d->profiling) cudaEventRecord(d->ev_area[0], d->stream);
+            launch_area(area_args(*ap, src, (size_t)src_w * 3, stight, d->bgr.as<uint8_t>(), dstride), 3, nf, d->stream);
+            if (d->profiling) cudaEventRecord(d->ev_area[1], d->stream);
+            if (pipelined) CK(cudaEventRecord(d->ev_consumed[g & 1], d->stream));  // the input buffer is free once k_area has run
+        }
+        rc = run_group(d, dp, d->bgr.as<uint8_t>(), dstride, true, nf, out + (size_t)f0 * cap, cap, counts + f0, f0, pipelined);
+        d->area2_src = nullptr; d->area2_consumed = nullptr;
+        if (rc) return rc;
+        if (fuse) continue;
         if (d->profiling) {                            // run_group synchronised the stream
             float ms = 0;
             cudaEventElapsedTime(&ms, d->ev_area[0], d->ev_area[1]);

@@ -292,7 +292,26 @@ __device__ __forceinline__ int near_thr(double sum, double thr, double eps) { re
 // `t` points at a window's origin inside the shared tile; node data is warp-uniform and comes from the constant bank
 // through the uniform datapath (LDCU.128: four offsets, or {thr, meta, delta}, per instruction); the node pointer is
 // walked, never recomputed.  K windows per lane share every node fetch.
-__device__ __forceinline__ int tile_at(const char* t, int off) { return *reinterpret_cast<const int*>(t + off); }
+// -DUGD_CHECKED=1 (python _build.py --checked; tools/r02_checked.sh): every read of the scan tiles is checked against the
+// block's dynamic shared-memory window and every read of the squared-integral plane against the level's plane, and a miss
+// traps -- the bounds half of what compute-sanitizer's memcheck would say about this kernel (the tool is closed on the
+// GPU pool this was developed on).
+#ifndef UGD_CHECKED
+#define UGD_CHECKED 0
+#endif
+__device__ __forceinline__ void chk_tile(uint32_t saddr) {
+#if UGD_CHECKED
+    extern __shared__ __align__(16) unsigned char s_dyn_chk[];
+    uint32_t size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(size));
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(s_dyn_chk);
+    if (saddr < base || saddr + 4 > base + size || (saddr & 3u)) __trap();
+#endif
+}
+__device__ __forceinline__ int tile_at(const char* t, int off) {
+    chk_tile((uint32_t)__cvta_generic_to_shared(t + off));
+    return *reinterpret_cast<const int*>(t + off);
+}
 __device__ __forceinline__ int coef_of(const int4& c, int j) {
     const int w = j < 4 ? c.x : j < 8 ? c.y : c.z;
     return (int)(int8_t)(w >> (8 * (j & 3)));
@@ -498,6 +517,7 @@ __device__ __forceinline__ void emit_raw(const DevBufs& b, int frame, float scal
 // Node data: merged corner lists whose BYTE offsets (from the window's origin) were computed at load time
 // for each memory layout; two offsets share a 32-bit word, so one add of (base | base << 16) rebases both.
 __device__ __forceinline__ int lds32(uint32_t addr) {
+    chk_tile(addr);
     int v;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
@@ -780,6 +800,13 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
                 {
                     const int32_t* no = c_geom.norm_off[si];
                     const int vs = tile_at(t, no[0]) - tile_at(t, no[1]) - tile_at(t, no[2]) + tile_at(t, no[3]);
+#if UGD_CHECKED
+                    {
+                        const long long plane = (long long)(sh + 1) * P;
+                        const long long ia = qa + xq - Q, ib = qb + xq - Q, ic = qc + xq - Q, id = qd + xq - Q;
+                        if (ia < 0 || ib < 0 || ic < 0 || id < 0 || ia >= plane || ib >= plane || ic >= plane || id >= plane) __trap();
+                    }
+#endif
                     const uint32_t vq = (uint32_t)qa[xq] - (uint32_t)qb[xq] - (uint32_t)qc[xq] + (uint32_t)qd[xq];
                     double nf = area * (double)vq - (double)vs * (double)vs;
                     if (nf > 0.0) {

@@ -13,16 +13,25 @@ __device__ __forceinline__ uint32_t sat8(int v) { return (uint32_t)min(max(v, 0)
 // ------------------------------------------------------------------------------------------------
 // K1  BGR -> gray (a4) + YCrCb skin mask (a2,a3) + 256-bin histogram of gray (first half of a5).
 // 4 pixels per thread per iteration: 12 B in, 4 B + 4 B out.
+// AREA2 = true fuses the 2x2 INTER_AREA decimation of SURVEY 8(f) N1 in front (reference face_tracker.cc:112-114 with
+// scan.frame_size = half the frame, as conf/apink.mrchu.720p.cfg has it): the thread reads the 2 x 8 source pixels under
+// its four scan-frame pixels (three 8-byte loads per row, a warp reads 768 contiguous bytes) and the decimated BGR
+// frame is never written.
+// Histogram: one private 256-bin copy per warp, shared-memory atomics.  (Tried: a private histogram of 8-bit counters per
+// THREAD -- 64 KB, bank-conflict-free plain load-add-store, summed with DP4A at the end -- to get rid of the atomics:
+// 0.078 ms against 0.068 ms for this form on 64 fused 720p frames; zeroing and summing 64 KB per 8192 pixels costs more
+// than the atomics do, and with 32768 pixels per CTA the grid gets too coarse.)
 // ------------------------------------------------------------------------------------------------
 constexpr int kPreIters = 8;   // quads per thread -> 8192 pixels per CTA, 256 global atomics per CTA
 
+template <bool AREA2>
 __global__ void __launch_bounds__(256) k_preprocess(DevBufs b) {
     __shared__ uint32_t sh[8][256];                         // per-warp private histograms
     const int frame = blockIdx.y, tid = threadIdx.x, warp = tid >> 5;
     for (int i = tid; i < 8 * 256; i += 256) (&sh[0][0])[i] = 0;
     __syncthreads();
     const int n = b.w * b.h;
-    const uint8_t* src = b.bgr + (size_t)frame * b.bgr_stride;
+    const uint8_t* src = AREA2 ? b.area2_src + (size_t)frame * b.area2_frame_stride : b.bgr + (size_t)frame * b.bgr_stride;
     uint8_t* gray = b.gray_raw + (size_t)frame * b.px_stride;
     uint8_t* mask = b.mask + (size_t)frame * b.px_stride;
     const int lo0 = b.skin_lo[0], lo1 = b.skin_lo[1], lo2 = b.skin_lo[2];
@@ -32,7 +41,23 @@ __global__ void __launch_bounds__(256) k_preprocess(DevBufs b) {
         int p0 = q * 4;
         if (p0 >= n) break;
         uint8_t px[12];
-        if (p0 + 4 <= n) {
+        if (AREA2) {
+            // b.w is a multiple of 4 here (launch_preprocess checks): a quad never straddles scan-frame rows
+            const int y = p0 / b.w, x = p0 - y * b.w;
+            const uint2* r0 = reinterpret_cast<const uint2*>(src + (size_t)(2 * y) * b.area2_row_stride + (size_t)x * 6);
+            const uint2* r1 = reinterpret_cast<const uint2*>(src + (size_t)(2 * y + 1) * b.area2_row_stride + (size_t)x * 6);
+            uint8_t t0[24], t1[24];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                reinterpret_cast<uint2*>(t0)[k] = __ldg(r0 + k);
+                reinterpret_cast<uint2*>(t1)[k] = __ldg(r1 + k);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    px[3 * k + c] = (uint8_t)(((int)t0[6 * k + c] + t0[6 * k + 3 + c] + t1[6 * k + c] + t1[6 * k + 3 + c] + 2) >> 2);
+        } else if (p0 + 4 <= n) {
             const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src) + (size_t)q * 3;
             uint32_t a = s32[0], c = s32[1], d = s32[2];
             *reinterpret_cast<uint32_t*>(px) = a;
@@ -69,11 +94,17 @@ __global__ void __launch_bounds__(256) k_preprocess(DevBufs b) {
     if (t) atomicAdd(&b.hist[(size_t)frame * 256 + tid], t);
 }
 
+// The fused decimation needs whole quads per scan-frame row and 8-byte aligned source rows.
+bool preprocess_can_fuse_area2(const uint8_t* src, size_t row_stride, size_t frame_stride, int scan_w) {
+    return scan_w % 4 == 0 && reinterpret_cast<uintptr_t>(src) % 8 == 0 && row_stride % 8 == 0 && frame_stride % 8 == 0;
+}
+
 void launch_preprocess(const DevBufs& b, cudaStream_t st) {
     int n = b.w * b.h;
     int per_cta = 256 * 4 * kPreIters;
     dim3 grid((n + per_cta - 1) / per_cta, b.nframes);
-    k_preprocess<<<grid, 256, 0, st>>>(b);
+    if (b.area2_src) k_preprocess<true><<<grid, 256, 0, st>>>(b);
+    else k_preprocess<false><<<grid, 256, 0, st>>>(b);
 }
 
 // ------------------------------------------------------------------------------------------------

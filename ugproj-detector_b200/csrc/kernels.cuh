@@ -83,6 +83,7 @@ struct DevBufs {
     const int32_t* tree_first_node; const int32_t* stage_first_node;
     // frames
     const uint8_t* bgr; size_t bgr_stride;            // input BGR frames (device)
+    const uint8_t* area2_src; size_t area2_row_stride, area2_frame_stride;   // non-null: full-size BGR frames, decimated 2x2 (INTER_AREA) inside k_preprocess; bgr is then unused
     uint8_t* gray_raw; uint8_t* gray_eq; uint8_t* mask; size_t px_stride;   // per-frame planes
     const uint8_t* src_gray; size_t src_stride; int src_pitch;             // what the pyramid is built from
     uint32_t* hist;                                   // [nframes][256]
@@ -182,6 +183,7 @@ void build_legacy_cascade(const Cascade& c, LegacyCascadeHost& out);
 void launch_legacy(const LegacyArgs& a, const LegacyPlan& p, int nframes, cudaStream_t st);
 
 void launch_preprocess(const DevBufs& b, cudaStream_t st);
+bool preprocess_can_fuse_area2(const uint8_t* src, size_t row_stride, size_t frame_stride, int scan_w);
 void launch_equalize(const DevBufs& b, cudaStream_t st);
 void launch_resize_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);   // pyramid + per-strip column sums
 void launch_carry(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st);
