@@ -10,6 +10,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cuda.h>       // CUtensorMap and its enums only: cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint, libcuda is not linked
@@ -81,6 +82,11 @@ struct ugd_detector {
     // them itself, see launch_preprocess) and the event to record once that kernel -- their last reader -- is in the stream
     const uint8_t* area2_src = nullptr; size_t area2_row_stride = 0, area2_frame_stride = 0; cudaEvent_t area2_consumed = nullptr;
     DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
+    // Host frames in PAGEABLE memory (what a cv::Mat is, face_tracker.cc:112-114): cudaMemcpyAsync would bounce them through
+    // the driver's staging buffer on the calling thread, one chunk at a time, and the kernels of the next group could not be
+    // enqueued meanwhile.  Multi-group calls instead copy each group into one of two pinned buffers of the detector with a
+    // few host threads (memcpy at memory speed) and issue a truly asynchronous copy from there.
+    uint8_t* pin[2] = {nullptr, nullptr}; size_t pin_bytes = 0;
     // group pipeline of multi-group calls: the image stage (preprocess .. integrals, HBM-bound) of group g+1 runs on
     // img_stream next to the scan stage (k_scan + grouping, issue-bound) of group g; S / SQ / T / mask exist twice
     cudaStream_t img_stream = nullptr;
@@ -711,6 +717,47 @@ void drain(ugd_detector* d) {
     d->pending.active = false;
 }
 
+// True when `p` is ordinary (pageable) host memory: not pinned, not registered, not managed.
+bool is_pageable_host(const void* p) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+// memcpy with a few threads (a single thread moves ~10 GB/s; the H2D link takes 55)
+void parallel_memcpy(uint8_t* dst, const uint8_t* src, size_t bytes) {
+    static const int nthreads = [] { const char* e = getenv("UGD_COPY_THREADS"); int n = e ? atoi(e) : 4; return std::max(1, std::min(n, 16)); }();
+    if (nthreads == 1 || bytes < (4u << 20)) { memcpy(dst, src, bytes); return; }
+    const size_t chunk = (bytes / nthreads + 4095) & ~(size_t)4095;
+    std::vector<std::thread> th;
+    for (int t = 1; t < nthreads; ++t) {
+        const size_t o = (size_t)t * chunk;
+        if (o >= bytes) break;
+        th.emplace_back([=] { memcpy(dst + o, src + o, std::min(chunk, bytes - o)); });
+    }
+    memcpy(dst, src, std::min(chunk, bytes));
+    for (auto& t : th) t.join();
+}
+
+// One group of tight host frames -> device staging rows of `dpitch` bytes, on the copy stream.  Pageable frames go through
+// pinned buffer `bi` of the detector (free again once ev_copied[bi], the copy of two groups ago, has completed).
+int copy_group_h2d(ugd_detector* d, uint8_t* dst, size_t dpitch, const uint8_t* src, size_t tight, int nf, int bi, int g, bool pageable) {
+    if (pageable) {
+        const size_t need = (size_t)d->max_batch * tight;
+        if (d->pin_bytes < need) {
+            CK(cudaStreamSynchronize(d->copy_stream));
+            for (int i = 0; i < 2; ++i) { if (d->pin[i]) cudaFreeHost(d->pin[i]); d->pin[i] = nullptr; }
+            d->pin_bytes = 0;
+            for (int i = 0; i < 2; ++i) CK(cudaHostAlloc((void**)&d->pin[i], need, cudaHostAllocDefault));
+            d->pin_bytes = need;
+        } else if (g >= 2) CK(cudaEventSynchronize(d->ev_copied[bi]));
+        parallel_memcpy(d->pin[bi], src, (size_t)nf * tight);
+        src = d->pin[bi];
+    }
+    CK(cudaMemcpy2DAsync(dst, dpitch, src, tight, tight, nf, cudaMemcpyHostToDevice, d->copy_stream));
+    return UGD_OK;
+}
+
 int detect_common(ugd_detector* d, const void* frames, bool is_device, bool is_bgr, int nframes, int w, int h,
                   size_t host_row_stride, ugd_rect* out, int cap, int* counts, bool async_submit = false) {
     const int rc = detect_body(d, frames, is_device, is_bgr, nframes, w, h, host_row_stride, out, cap, counts, async_submit);
@@ -741,6 +788,8 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
     static const bool no_overlap = getenv("UGD_NO_OVERLAP") != nullptr;
     const bool overlap = !no_overlap && !d->profiling && !d->want_map && !d->prm.legacy_24 && nframes > d->max_batch;
     const bool defer = pipelined || async_submit || overlap;
+    static const bool no_pin_ring = getenv("UGD_NO_PIN_RING") != nullptr;
+    const bool pageable = pipelined && !no_pin_ring && is_pageable_host(frames);
     if (pipelined) CK(d->stage2.reserve((size_t)d->max_batch * st_stride + 256));
     cudaStream_t in_stream = overlap ? d->img_stream : d->stream;      // the stream that consumes the input frames
     if (overlap) {
@@ -769,7 +818,7 @@ int detect_body(ugd_detector* d, const void* frames, bool is_device, bool is_bgr
             if (pipelined) {
                 const int bi = g & 1;
                 if (g >= 2) CK(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[bi], 0));   // staging[bi] free again
-                CK(cudaMemcpy2DAsync(staging, st_stride, src + (size_t)f0 * tight, tight, tight, nf, cudaMemcpyHostToDevice, d->copy_stream));
+                if ((rc = copy_group_h2d(d, staging, st_stride, src + (size_t)f0 * tight, tight, nf, bi, g, pageable))) return rc;
                 CK(cudaEventRecord(d->ev_copied[bi], d->copy_stream));
                 CK(cudaStreamWaitEvent(in_stream, d->ev_copied[bi], 0));
             } else if (tight_host) {
@@ -977,6 +1026,8 @@ int ugd_create(const ugd_cascade* c, const ugd_params* p, int cuda_device, int m
 void ugd_destroy(ugd_detector* d) {
     if (!d) return;
     cudaSetDevice(d->device);
+    if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
+    for (int i = 0; i < 2; ++i) if (d->pin[i]) cudaFreeHost(d->pin[i]);
     if (d->stream) cudaStreamSynchronize(d->stream);
     if (d->img_stream) cudaStreamSynchronize(d->img_stream);
     if (d->scan2) cudaStreamSynchronize(d->scan2);
@@ -1087,6 +1138,8 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
     // host frames in more than one group: the H2D copy of group g+1 overlaps the kernels of group g (two input buffers)
     const bool pipelined = !is_device && !d->profiling && nframes > d->max_batch;
     const size_t in_stride = round_up((size_t)d->max_batch * stight, 256);
+    static const bool no_pin_ring = getenv("UGD_NO_PIN_RING") != nullptr;
+    const bool pageable = pipelined && !no_pin_ring && is_pageable_host(frames);
     if (!is_device) CK(d->src_full.reserve((pipelined ? 2 : 1) * in_stride + 256));
     int g = 0;
     for (int f0 = 0; f0 < nframes; f0 += d->max_batch, ++g) {
@@ -1098,7 +1151,7 @@ int ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, 
             if (pipelined) {
                 const int bi = g & 1;
                 if (g >= 2) CK(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[bi], 0));
-                CK(cudaMemcpyAsync(in, src, (size_t)nf * stight, cudaMemcpyHostToDevice, d->copy_stream));
+                if ((rc = copy_group_h2d(d, in, stight, src, stight, nf, bi, g, pageable))) return rc;
                 CK(cudaEventRecord(d->ev_copied[bi], d->copy_stream));
                 CK(cudaStreamWaitEvent(d->stream, d->ev_copied[bi], 0));
             } else {
