@@ -177,6 +177,16 @@ int  ugd_wait_batch(ugd_detector* d, ugd_rect* out, int* counts);
  * scan_w/scan_h <= 0 means "no resize" (structure.cc:64-65).  Decimation only. */
 int  ugd_detect_batch_scaled(ugd_detector* d, const void* frames, int is_device, int nframes, int src_w, int src_h,
                              int scan_w, int scan_h, ugd_rect* out, int cap, int* counts);
+/* The face patches the tracker keeps per detection -- `cv::Mat img_face(curr_frame, *it); Face f(curr_index, *it, img_face);`
+ * (src/tracker/face_tracker.cc:296-302; Face's copy constructor copies the pixels, src/structure.h:137-146) -- cut out of
+ * DEVICE-resident frames, for hosts whose frames never visit host memory (decoded on the GPU).
+ * dev_frames: nframes tight frames of w*h*channels bytes in device memory; rects / counts: as returned by ugd_detect_batch
+ * (cap slots per frame; rects must lie inside the frame, which the detect calls guarantee).  out (host) receives the patches
+ * back to back, each row-major and tight (width*height*channels bytes), frame by frame in list order; offsets[f*cap+i] is the
+ * byte offset of patch i of frame f; *total the bytes needed.  out_cap < *total returns UGD_ERR_CAPACITY with *total set and
+ * nothing copied (call again with room). */
+int  ugd_crop_faces(ugd_detector* d, const void* dev_frames, int nframes, int w, int h, int channels, const ugd_rect* rects,
+                    const int* counts, int cap, uint8_t* out, size_t out_cap, size_t* offsets, size_t* total);
 /* The resize alone (host in, host out; 1 or 3 channels), for parity tests against cv2.resize(INTER_AREA). */
 int  ugd_resize_area(ugd_detector* d, const uint8_t* src, int src_w, int src_h, int channels, size_t stride_bytes,
                      uint8_t* dst, int dst_w, int dst_h);

@@ -247,6 +247,36 @@ def test_scaled_fused_decimation_images(ug, synth, orc, cv2ref):
         det.close()
 
 
+def test_crop_faces_from_device_frames(ug, synth, cv2ref):
+    """SURVEY 8(f) N2, second half: the face patches of face_tracker.cc:296-302 (`cv::Mat img_face(curr_frame, rect)`, copied
+    by Face's copy constructor, structure.h:137-146) cut out of device-resident frames == numpy slices of the same frames,
+    byte for byte; BGR and gray, an empty list in the middle, and the two-call size query of the C ABI."""
+    import ctypes as C
+    import torch
+    casc = ug.Cascade(cv2ref.cascade_path("alt"))
+    det = ug.Detector(casc, ug.default_params(), max_size=(640, 360), max_batch=2)
+    for channels in (3, 1):
+        frames = [synth.bgr_frame(640, 360, 5, 700 + i) if channels == 3 else synth.gray_frame(640, 360, 5, 710 + i) for i in range(3)]
+        frames[1] = np.zeros_like(frames[1])                                            # no detections on this one
+        host = np.stack(frames)
+        dev = torch.from_numpy(host).cuda()
+        lists = det.detect_batch_device(dev.data_ptr(), channels == 3, 3, 640, 360, cap=32)
+        assert lists.total() > 0 and len(lists[1]) == 0
+        crops = det.crop_faces(dev.data_ptr(), 3, 640, 360, channels, lists)
+        for f in range(3):
+            assert len(crops[f]) == len(lists[f])
+            for (x, y, w, h), patch in zip(lists[f].tolist(), crops[f]):
+                assert np.array_equal(patch, host[f][y:y + h, x:x + w])
+        # a buffer that is too small: nothing copied, the size reported
+        cap = lists.rects.shape[1]
+        offs = np.zeros(3 * cap, np.uint64); total = C.c_size_t(); small = np.zeros(16, np.uint8)
+        rc = ug.lib().ugd_crop_faces(det._h, C.c_void_p(dev.data_ptr()), 3, 640, 360, channels, lists.rects.ctypes.data_as(C.c_void_p),
+                                     lists.counts.astype(np.int32).ctypes.data_as(C.c_void_p), cap, small.ctypes.data_as(C.c_void_p),
+                                     C.c_size_t(16), offs.ctypes.data_as(C.c_void_p), C.byref(total))
+        assert rc == ug.ERR_CAPACITY and total.value == sum(int(w) * int(h) * channels for l in lists for (_, _, w, h) in l.tolist())
+    det.close()
+
+
 def test_edge_cases(dets, synth, ug):
     casc, det = dets["alt"]
     assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance

@@ -10,6 +10,8 @@ B="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-configs"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches.csv $B > /dev/null 2>&1; echo "launch list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_resize|k_carry|k_integral' --launch-skip 9 -c 3 -o gpurun_out/r02_image_kernels -f $B > /dev/null 2>&1; echo "ncu image rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_scan --launch-skip 6 -c 2 -o gpurun_out/r02_k_scan -f $B > /dev/null 2>&1; echo "ncu scan rc=$?"
+B2="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-configs --cascade alt2 --scan-size 640x360"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_preprocess|k_equalize' --launch-skip 6 -c 2 -o gpurun_out/r02_bgr_kernels -f $B2 > /dev/null 2>&1; echo "ncu bgr rc=$?"
 python - <<'PY'
 import json
 d=json.load(open('gpurun_out/r02_bench_1gpu.json'))

@@ -300,6 +300,31 @@ class Detector:
                                                _p(out), cap, _p(cnt)))
         return RectLists(out, cnt)
 
+    def crop_faces(self, dev_ptr: int, n: int, w: int, h: int, channels: int, lists: "RectLists"):
+        """Face patches of device-resident frames (== the cv::Mat ROI copies of face_tracker.cc:296-302):
+        list (per frame) of lists of [height, width(, 3)] uint8 arrays, in the order of `lists`."""
+        cap = lists.rects.shape[1]
+        rects = np.ascontiguousarray(lists.rects[lists.start:lists.start + n])
+        counts = np.ascontiguousarray(lists.counts[lists.start:lists.start + n].astype(np.int32))
+        offs = np.zeros(n * cap, np.uint64)
+        total = C.c_size_t()
+        rc = lib().ugd_crop_faces(self._h, C.c_void_p(dev_ptr), n, w, h, channels, _p(rects), _p(counts), cap, None, C.c_size_t(0),
+                                  _p(offs), C.byref(total))
+        if rc not in (OK, ERR_CAPACITY):
+            self._ck(rc)
+        buf = np.zeros(max(total.value, 1), np.uint8)
+        self._ck(lib().ugd_crop_faces(self._h, C.c_void_p(dev_ptr), n, w, h, channels, _p(rects), _p(counts), cap, _p(buf),
+                                      C.c_size_t(buf.size), _p(offs), C.byref(total)))
+        out = []
+        for f in range(n):
+            row = []
+            for i in range(min(int(counts[f]), cap)):
+                x, y, rw, rh = (int(v) for v in rects[f, i])
+                o = int(offs[f * cap + i])
+                row.append(buf[o:o + rw * rh * channels].reshape((rh, rw, 3) if channels == 3 else (rh, rw)).copy())
+            out.append(row)
+        return out
+
     def resize_area(self, img: np.ndarray, dw: int, dh: int) -> np.ndarray:
         """cv2.resize(img, (dw, dh), interpolation=INTER_AREA) on the device (decimation only)."""
         img = np.ascontiguousarray(img, np.uint8)

@@ -82,6 +82,7 @@ struct ugd_detector {
     // them itself, see launch_preprocess) and the event to record once that kernel -- their last reader -- is in the stream
     const uint8_t* area2_src = nullptr; size_t area2_row_stride = 0, area2_frame_stride = 0; cudaEvent_t area2_consumed = nullptr;
     DevPtr stage2;                                    // second input staging buffer (the first is bgr / gray_in)
+    DevPtr crop_items, crop_out;                      // ugd_crop_faces: patch descriptors, packed patches
     // Host frames in PAGEABLE memory (what a cv::Mat is, face_tracker.cc:112-114): cudaMemcpyAsync would bounce them through
     // the driver's staging buffer on the calling thread, one chunk at a time, and the kernels of the next group could not be
     // enqueued meanwhile.  Multi-group calls instead copy each group into one of two pinned buffers of the detector with a
@@ -1068,7 +1069,7 @@ void ugd_destroy(ugd_detector* d) {
     if (d->img_stream) cudaStreamDestroy(d->img_stream);
     for (int i = 0; i < 2; ++i) { if (d->ev_img_done[i]) cudaEventDestroy(d->ev_img_done[i]); if (d->ev_scan_done[i]) cudaEventDestroy(d->ev_scan_done[i]); }
     if (d->ev_call) cudaEventDestroy(d->ev_call);
-    d->stage2.release();
+    d->stage2.release(); d->crop_items.release(); d->crop_out.release();
     if (d->own_stream) cudaStreamDestroy(d->own_stream);
     delete d;
 }
@@ -1115,6 +1116,41 @@ int ugd_resize_area(ugd_detector* d, const uint8_t* src, int sw, int sh, int cha
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(dst, d->area_dst.p, dbytes, cudaMemcpyDeviceToHost, d->stream));
     CK(cudaStreamSynchronize(d->stream));
+    return UGD_OK;
+}
+
+int ugd_crop_faces(ugd_detector* d, const void* dev_frames, int nframes, int w, int h, int channels, const ugd_rect* rects,
+                   const int* counts, int cap, uint8_t* out, size_t out_cap, size_t* offsets, size_t* total) {
+    if (!d || !dev_frames || !rects || !counts || !offsets || !total || nframes < 0 || cap <= 0 || w <= 0 || h <= 0 ||
+        (channels != 1 && channels != 3))
+        return UGD_ERR_ARG;
+    std::vector<CropItem> items;
+    size_t bytes = 0;
+    for (int f = 0; f < nframes; ++f) {
+        const int n = std::min(counts[f], cap);
+        for (int i = 0; i < n; ++i) {
+            const ugd_rect& r = rects[(size_t)f * cap + i];
+            if (r.x < 0 || r.y < 0 || r.width <= 0 || r.height <= 0 || r.x + r.width > w || r.y + r.height > h) {
+                d->err = "ugd_crop_faces: a rectangle reaches outside the frame";     // (detect calls return clipped rects)
+                return UGD_ERR_ARG;
+            }
+            offsets[(size_t)f * cap + i] = bytes;
+            items.push_back({f, r.x, r.y, r.width, r.height, 0, (uint64_t)bytes});
+            bytes += (size_t)r.width * r.height * channels;
+        }
+    }
+    *total = bytes;
+    if (bytes == 0) return UGD_OK;
+    if (!out || out_cap < bytes) { d->err = "ugd_crop_faces: output buffer smaller than *total"; return UGD_ERR_CAPACITY; }
+    CK(cudaSetDevice(d->device));
+    CK(d->crop_items.reserve(items.size() * sizeof(CropItem)));
+    CK(d->crop_out.reserve(bytes));
+    CK(cudaMemcpyAsync(d->crop_items.p, items.data(), items.size() * sizeof(CropItem), cudaMemcpyHostToDevice, d->stream));
+    launch_crop(static_cast<const uint8_t*>(dev_frames), (size_t)w * h * channels, (size_t)w * channels, channels,
+                d->crop_items.as<CropItem>(), (int)items.size(), d->crop_out.as<uint8_t>(), d->stream);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, d->crop_out.p, bytes, cudaMemcpyDeviceToHost, d->stream));
+    CK(cudaStreamSynchronize(d->stream));          // `items` is a local: the copies above must be done before it goes
     return UGD_OK;
 }
 

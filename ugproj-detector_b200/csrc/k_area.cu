@@ -87,6 +87,28 @@ __global__ void __launch_bounds__(256) k_area(AreaArgs a) {
     for (int c = 0; c < CN; ++c) dst[c] = (uint8_t)min(max(__float2int_rn(sum[c]), 0), 255);
 }
 
+// Face patches (second half): what `cv::Mat img_face(curr_frame, *it)` + the copy in Face's copy
+// constructor produce on the host (reference face_tracker.cc:296-302, structure.h:137-146), cut out of device-resident
+// frames.  One block per patch; a row of a patch is contiguous in the frame, so the copy is row-wise and coalesced.
+__global__ void __launch_bounds__(256) k_crop(const uint8_t* __restrict__ frames, size_t frame_stride, size_t row_stride, int channels,
+                                              const CropItem* __restrict__ items, uint8_t* __restrict__ out) {
+    const CropItem it = items[blockIdx.x];
+    const uint8_t* src = frames + (size_t)it.frame * frame_stride + (size_t)it.y * row_stride + (size_t)it.x * channels;
+    uint8_t* dst = out + it.offset;
+    const int row_bytes = it.w * channels;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int y = warp; y < it.h; y += 8) {
+        const uint8_t* s = src + (size_t)y * row_stride;
+        uint8_t* d = dst + (size_t)y * row_bytes;
+        for (int i = lane; i < row_bytes; i += 32) d[i] = s[i];
+    }
+}
+
+void launch_crop(const uint8_t* frames, size_t frame_stride, size_t row_stride, int channels, const CropItem* items, int nitems,
+                 uint8_t* out, cudaStream_t st) {
+    if (nitems) k_crop<<<nitems, 256, 0, st>>>(frames, frame_stride, row_stride, channels, items, out);
+}
+
 void launch_area(const AreaArgs& a, int channels, int nframes, cudaStream_t st) {
     const dim3 grid((a.dw + 255) / 256, a.dh, nframes);
     if (channels == 3) k_area<3><<<grid, 256, 0, st>>>(a);

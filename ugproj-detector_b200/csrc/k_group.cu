@@ -154,46 +154,61 @@ __global__ void __launch_bounds__(256) k_group(DevBufs b) {
         __syncthreads();
     }
 
-    // ---- clip to the image (A.5 last line), drop empties; then the skin-coverage test (detector.cc:33-42) ----
+    // ---- clip to the image (A.5 last line), drop empties; then the skin-coverage test (detector.cc:33-42).  Survivors are
+    //      flagged in `clist` (dead by now) instead of being compacted one by one: without the skin test a thread takes a
+    //      rectangle (cascades that fire on thousands of windows keep hundreds of them); with it the block sums the mask
+    //      under one rectangle at a time ----
     const int nk = s_nkept;
     const uint8_t* mask = b.mask + (size_t)frame * b.px_stride;
-    for (int k = 0; k < nk; ++k) {
-        ugd_rect r = kept[k];
-        const ugd_rect unclipped = r;
-        const int x0 = max(r.x, 0), y0 = max(r.y, 0), x1 = min(r.x + r.width, b.w), y1 = min(r.y + r.height, b.h);
-        bool ok = x1 > x0 && y1 > y0;
-        r.x = x0; r.y = y0; r.width = x1 - x0; r.height = y1 - y0;
-        if (ok && b.use_skin) {
-            unsigned long long sum = 0;
-            for (int yy = warp; yy < r.height; yy += 8) {
-                const uint8_t* row = mask + (size_t)(y0 + yy) * b.w + x0;
-                for (int xx = lane; xx < r.width; xx += 32) sum += row[xx];
+    if (!b.use_skin) {
+        for (int k = tid; k < nk; k += 256) {
+            ugd_rect r = kept[k];
+            const int x0 = max(r.x, 0), y0 = max(r.y, 0), x1 = min(r.x + r.width, b.w), y1 = min(r.y + r.height, b.h);
+            const bool ok = x1 > x0 && y1 > y0;
+            if (!b.no_clip) { r.x = x0; r.y = y0; r.width = x1 - x0; r.height = y1 - y0; kept[k] = r; }   // (2.4 legacy mode does not clip)
+            clist[k] = ok ? 1 : 0;
+            if (ok) atomicAdd(&s_nfinal, 1);
+        }
+    } else {
+        for (int k = 0; k < nk; ++k) {
+            ugd_rect r = kept[k];
+            const int x0 = max(r.x, 0), y0 = max(r.y, 0), x1 = min(r.x + r.width, b.w), y1 = min(r.y + r.height, b.h);
+            bool ok = x1 > x0 && y1 > y0;                   // block-uniform
+            if (ok) {
+                unsigned long long sum = 0;
+                for (int yy = warp; yy < y1 - y0; yy += 8) {
+                    const uint8_t* row = mask + (size_t)(y0 + yy) * b.w + x0;
+                    for (int xx = lane; xx < x1 - x0; xx += 32) sum += row[xx];
+                }
+#pragma unroll
+                for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+                if (lane == 0) s_red[warp] = sum;
+                __syncthreads();
+                sum = 0;
+#pragma unroll
+                for (int wv = 0; wv < 8; ++wv) sum += s_red[wv];
+                // cv::mean = sum * (1/N); norm of a 1-channel mean is the mean itself
+                const double mean = __dmul_rn((double)sum, __ddiv_rn(1.0, __dmul_rn((double)(x1 - x0), (double)(y1 - y0))));
+                ok = !(__ddiv_rn(mean, 256.0) < 0.8);
+                __syncthreads();                            // s_red is reused by the next rectangle
             }
-#pragma unroll
-            for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-            __syncthreads();
-            if (lane == 0) s_red[warp] = sum;
-            __syncthreads();
-            sum = 0;
-#pragma unroll
-            for (int wv = 0; wv < 8; ++wv) sum += s_red[wv];
-            // cv::mean = sum * (1/N); norm of a 1-channel mean is the mean itself
-            const double mean = __dmul_rn((double)sum, __ddiv_rn(1.0, __dmul_rn((double)r.width, (double)r.height)));
-            ok = !(__ddiv_rn(mean, 256.0) < 0.8);
+            if (tid == 0) {
+                if (!b.no_clip) { r.x = x0; r.y = y0; r.width = x1 - x0; r.height = y1 - y0; kept[k] = r; }   // (the mask mean is over the part inside)
+                clist[k] = ok ? 1 : 0;
+                if (ok) ++s_nfinal;
+            }
         }
-        __syncthreads();
-        if (tid == 0) {
-            if (ok) { kept[s_nfinal] = b.no_clip ? unclipped : r; ++s_nfinal; }       // (2.4 legacy mode does not clip; the mask mean is over the part inside)
-        }
-        __syncthreads();
     }
-    // ---- canonical order (rank sort; cv2's own order depends on thread timing) ----
+    __syncthreads();
+    // ---- canonical order (rank sort over the flagged rectangles; cv2's own order depends on thread timing) ----
     const int nf = s_nfinal;
     ugd_rect* out = b.out + (size_t)frame * b.outcap;
-    for (int i = tid; i < nf; i += 256) {
+    for (int i = tid; i < nk; i += 256) {
+        if (!clist[i]) continue;
         const ugd_rect ri = kept[i];
         int rank = 0;
-        for (int j = 0; j < nf; ++j) {
+        for (int j = 0; j < nk; ++j) {
+            if (!clist[j]) continue;
             const ugd_rect rj = kept[j];
             if (rect_less(rj, ri) || (!rect_less(ri, rj) && j < i)) ++rank;
         }

@@ -150,6 +150,9 @@ struct AreaArgs {
 };
 bool build_area_plan(int sw, int sh, int dw, int dh, AreaPlanHost& p);
 void launch_area(const AreaArgs& a, int channels, int nframes, cudaStream_t st);
+struct CropItem { int32_t frame, x, y, w, h, pad_; uint64_t offset; };      // one face patch: source rect, byte offset in the packed output
+void launch_crop(const uint8_t* frames, size_t frame_stride, size_t row_stride, int channels, const CropItem* items, int nitems,
+                 uint8_t* out, cudaStream_t st);
 
 // ---- OpenCV-2.4 compatibility mode (k_legacy.cu) ----
 struct LegacyLevel {
