@@ -650,6 +650,9 @@ __device__ __forceinline__ void stage_tile(int* tile, const int32_t* __restrict_
 // Warps per block (NW): 16 warps on the same 16 x 128 tile (three blocks per SM, same 48 resident warps) measured 9.5 %
 // slower than 8 (9.78 vs 8.93 ms): half as many rounds per warp leaves fewer window pairs, and twice as many warps
 // wait at every end-of-stage barrier.
+#ifndef UGD_PAIR_MIN_ROWS
+#define UGD_PAIR_MIN_ROWS 2                          // rows per warp from which stage 0 takes the rows two at a time (see phase 2 of k_scan)
+#endif
 #ifndef UGD_SCAN_MINBLOCKS
 #define UGD_SCAN_MINBLOCKS 6
 #endif
@@ -771,86 +774,103 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
             }
         }
         // ---- 2. variance normalisation + stage 0 + x-skip: a warp owns R / NW rows of the tile and walks each in
-        //         segments of 32 windows; everything that depends on the row only is warp-uniform ----
+        //         segments of 32 windows; everything that depends on the row only is warp-uniform.  With four rows per
+        //         warp (32-row tiles) the rows are taken two at a time: a lane holds the windows (row a, column c) and
+        //         (row b, column c), and stage 0 runs on both at once -- they share every node fetch, like the pairs of
+        //         the later stages ----
+        constexpr int RPW = R / NW, KP = (MODE != 0 && RPW % 2 == 0 && RPW >= UGD_PAIR_MIN_ROWS) ? 2 : 1;
 #pragma unroll 1
-        for (int k = 0; k < R / NW; ++k) {
-            const int rl = w + k * NW, row = r0 + rl;
-            const bool row_valid = row < nyg;
-            const int y = row_valid ? row * step : 0;
+        for (int k = 0; k < RPW; k += KP) {
+            int rl[KP], row[KP], y[KP], run_in[KP];
+            bool row_valid[KP];
+            const int32_t *qa[KP], *qb[KP], *qc[KP], *qd[KP];
+            const char* trow[KP];
             // the four corners of the squared-integral sum over the window's inner (ow-2) x (oh-2) box, as four row pointers
             // (de-interleaved rows, grid step 2: column x + dx of an even x lives at half (dx & 1), index x / 2 + dx / 2, so
             // adjacent windows read adjacent words)
             const bool dq = b.deint2 && si;
             const int half = P >> 1, dxb = ow - 1;
             const int oa = dq ? half : 1, ob = dq ? (dxb & 1) * half + (dxb >> 1) : dxb;
-            const int32_t* qa = Q + ((y + 1) * P + oa);
-            const int32_t* qb = Q + ((y + 1) * P + ob);
-            const int32_t* qc = Q + ((y + oh - 1) * P + oa);
-            const int32_t* qd = Q + ((y + oh - 1) * P + ob);
-            const char* trow = reinterpret_cast<const char*>(s_tile + (rl * step) * TP);
-            int run_in = (run_par >> k) & 1;           // only the parity of the run length matters
+#pragma unroll
+            for (int j = 0; j < KP; ++j) {
+                rl[j] = w + (k + j) * NW; row[j] = r0 + rl[j];
+                row_valid[j] = row[j] < nyg;
+                y[j] = row_valid[j] ? row[j] * step : 0;
+                qa[j] = Q + ((y[j] + 1) * P + oa);
+                qb[j] = Q + ((y[j] + 1) * P + ob);
+                qc[j] = Q + ((y[j] + oh - 1) * P + oa);
+                qd[j] = Q + ((y[j] + oh - 1) * P + ob);
+                trow[j] = reinterpret_cast<const char*>(s_tile + (rl[j] * step) * TP);
+                run_in[j] = (run_par >> (k + j)) & 1;  // only the parity of the run length matters
+            }
 #pragma unroll 1
             for (int h = 0; h < SEG; ++h) {
                 if (xi0 + 32 * h >= nxg) break;        // warp-uniform: segment past the end of the row
                 const int c = 32 * h + lane, xi = xi0 + c;
-                const bool valid = row_valid && xi < nxg;
-                const int x = valid ? xi * step : 0;
+                const bool in_row = xi < nxg;
+                const int x = in_row ? xi * step : 0;
                 const int xq = dq ? x >> 1 : x;          // index along the SQ row pointers
-                const char* t = trow + 4 * c;
-                float vnf = 1.f;
-                bool ok = false;
-                {
+                const char* t[KP];
+                float vnf[KP];
+                bool ok[KP];
+#pragma unroll
+                for (int j = 0; j < KP; ++j) {
+                    t[j] = trow[j] + 4 * c;
+                    vnf[j] = 1.f;
+                    ok[j] = false;
                     const int32_t* no = c_geom.norm_off[si];
-                    const int vs = tile_at(t, no[0]) - tile_at(t, no[1]) - tile_at(t, no[2]) + tile_at(t, no[3]);
+                    const int vs = tile_at(t[j], no[0]) - tile_at(t[j], no[1]) - tile_at(t[j], no[2]) + tile_at(t[j], no[3]);
 #if UGD_CHECKED
                     {
                         const long long plane = (long long)(sh + 1) * P;
-                        const long long ia = qa + xq - Q, ib = qb + xq - Q, ic = qc + xq - Q, id = qd + xq - Q;
+                        const long long ia = qa[j] + xq - Q, ib = qb[j] + xq - Q, ic = qc[j] + xq - Q, id = qd[j] + xq - Q;
                         if (ia < 0 || ib < 0 || ic < 0 || id < 0 || ia >= plane || ib >= plane || ic >= plane || id >= plane) __trap();
                     }
 #endif
-                    const uint32_t vq = (uint32_t)qa[xq] - (uint32_t)qb[xq] - (uint32_t)qc[xq] + (uint32_t)qd[xq];
+                    const uint32_t vq = (uint32_t)qa[j][xq] - (uint32_t)qb[j][xq] - (uint32_t)qc[j][xq] + (uint32_t)qd[j][xq];
                     double nf = area * (double)vq - (double)vs * (double)vs;
                     if (nf > 0.0) {
                         nf = sqrt(nf);
-                        vnf = (float)(1.0 / nf);
-                        ok = area * (double)vnf < 1e-1;
+                        vnf[j] = (float)(1.0 / nf);
+                        ok[j] = area * (double)vnf[j] < 1e-1;
                     }
-                    if (!ok) vnf = 1.f;
+                    if (!ok[j]) vnf[j] = 1.f;
                 }
-                double sum;
-                if (MODE) {
-                    const char* t1[1] = {t}; const float v1[1] = {vnf}; double s1[1];
-                    stage_eval<MODE, 1>(0, dn, t1, v1, s1);
-                    sum = s1[0];
-                } else sum = tile_stage_generic(0, dn, t, vnf);
-                const bool pass0 = !(sum < thr0d);
-                // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
-                // ending at i-1 has even length (a failure is only seen at evaluated positions)
-                const bool f0 = valid && ok && !pass0;
-                const unsigned F = __ballot_sync(0xffffffffu, f0);
-                const unsigned inv = ~F & below;
-                const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in);
-                run_in = ((F == 0xffffffffu) ? run_in + 32 : __clz((int)~F)) & 1;
-                const bool evaluated = valid && !(run & 1);
-                const bool varok = evaluated && ok;
-                const bool alive = varok && pass0;
-                cA += (evaluated ? 1u : 0u) + ((evaluated && !ok) ? 0x10000u : 0u);
-                cB += ((varok && near_thr(sum, thr0d, eps0)) ? 1u : 0u) + (varok ? 0x10000u : 0u);
-                if (map) {
-                    if (valid && !alive) map[row * nxg_pad + xi] = !evaluated ? kMapSkip : !ok ? kMapLowVar : (int16_t)0;
-                }
-                s_vnf[rl * C + c] = vnf;
-                if (alive) {
-                    if (nstages == 1) {                // one-stage cascade: accepted right here
-                        emit_raw(b, frame, scale, rect_w, rect_h, x, y, sum);
-                        if (map) map[row * nxg_pad + xi] = 1;
-                    } else {
-                        atomicOr(&s_alive[0][(rl * SEG + h) >> 5][(c + SH * rl) & 31], 1u << ((rl * SEG + h) & 31));
+                double sum[KP];
+                if (MODE) stage_eval<MODE ? MODE : 1, KP>(0, dn, t, vnf, sum);
+                else sum[0] = tile_stage_generic(0, dn, t[0], vnf[0]);
+#pragma unroll
+                for (int j = 0; j < KP; ++j) {
+                    const bool valid = row_valid[j] && in_row;
+                    const bool pass0 = !(sum[j] < thr0d);
+                    // x-skip rule in closed form: position i is evaluated iff the run of stage-0 failures
+                    // ending at i-1 has even length (a failure is only seen at evaluated positions)
+                    const bool f0 = valid && ok[j] && !pass0;
+                    const unsigned F = __ballot_sync(0xffffffffu, f0);
+                    const unsigned inv = ~F & below;
+                    const int run = inv ? (lane - 1 - (31 - __clz((int)inv))) : (lane + run_in[j]);
+                    run_in[j] = ((F == 0xffffffffu) ? run_in[j] + 32 : __clz((int)~F)) & 1;
+                    const bool evaluated = valid && !(run & 1);
+                    const bool varok = evaluated && ok[j];
+                    const bool alive = varok && pass0;
+                    cA += (evaluated ? 1u : 0u) + ((evaluated && !ok[j]) ? 0x10000u : 0u);
+                    cB += ((varok && near_thr(sum[j], thr0d, eps0)) ? 1u : 0u) + (varok ? 0x10000u : 0u);
+                    if (map) {
+                        if (valid && !alive) map[row[j] * nxg_pad + xi] = !evaluated ? kMapSkip : !ok[j] ? kMapLowVar : (int16_t)0;
+                    }
+                    s_vnf[rl[j] * C + c] = vnf[j];
+                    if (alive) {
+                        if (nstages == 1) {                // one-stage cascade: accepted right here
+                            emit_raw(b, frame, scale, rect_w, rect_h, x, y[j], sum[j]);
+                            if (map) map[row[j] * nxg_pad + xi] = 1;
+                        } else {
+                            atomicOr(&s_alive[0][(rl[j] * SEG + h) >> 5][(c + SH * rl[j]) & 31], 1u << ((rl[j] * SEG + h) & 31));
+                        }
                     }
                 }
             }
-            run_par = (run_par & ~(1u << k)) | ((unsigned)run_in << k);
+#pragma unroll
+            for (int j = 0; j < KP; ++j) run_par = (run_par & ~(1u << (k + j))) | ((unsigned)run_in[j] << (k + j));
         }
         __syncthreads();
         // ---- 3. stage by stage on the per-class survivor masks ----
