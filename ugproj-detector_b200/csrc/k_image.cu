@@ -188,33 +188,36 @@ __global__ void __launch_bounds__(kResizeThreads) k_resize_colsum(DevBufs b, con
     const WorkItem it = wk[blockIdx.x];
     const LevelInfo& L = b.levels[it.level];
     const int strip = it.first & 0xffff, chunk = it.first >> 16;
-    const int quads = L.img_pitch >> 2;
-    const int qx = chunk * kResizeThreads + threadIdx.x;
-    if (qx >= quads) return;
     const int frame = blockIdx.y;
     const int sw = L.sw, pitch = L.img_pitch, spitch = b.src_pitch;
-    const uint4 xe4 = __ldg(reinterpret_cast<const uint4*>(b.xtab + L.xtab_off) + qx);
-    const uint32_t xe[4] = {xe4.x, xe4.y, xe4.z, xe4.w};
+    // A warp owns 128 consecutive output columns; lane l takes columns l, l + 32, l + 64, l + 96 of them, so that the 32
+    // lanes of every load instruction read NEIGHBOURING source pixels (32 x scale bytes: one or two L1 wavefronts instead
+    // of the four to six that columns 4 apart cost -- the kernel is bound by L1 wavefronts, ncu 87 % of peak before)
+    const int c0 = chunk * (4 * kResizeThreads) + (threadIdx.x >> 5) * 128 + (threadIdx.x & 31);
+    if (c0 - (int)(threadIdx.x & 31) >= pitch) return;      // the whole warp lies in the row padding
+    const uint32_t* xtab = b.xtab + L.xtab_off;
     const uint8_t* src = b.src_gray + (size_t)frame * b.src_stride;
     const uint8_t* col[4];
     int cx1[4];
-    bool live[4];
+    bool live[4], inpitch[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        col[k] = src + (xe[k] & 0xffffu);
-        cx1[k] = (int)(xe[k] >> 16);
-        live[k] = qx * 4 + k < sw;                          // columns of the row padding stay 0
+        const int c = c0 + 32 * k;
+        inpitch[k] = c < pitch;
+        const uint32_t xe = inpitch[k] ? __ldg(xtab + c) : 0u;
+        col[k] = src + (xe & 0xffffu);
+        cx1[k] = (int)(xe >> 16);
+        live[k] = c < sw;                                   // columns of the row padding stay 0
     }
     const uint32_t* ytab = b.ytab + L.ytab_off;
     const int v0 = strip * kStripRows, v1 = min(v0 + kStripRows, L.sh);
-    uint8_t* dst = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + (size_t)v0 * pitch + qx * 4;
+    uint8_t* dst = b.pyr + (size_t)frame * b.pyr_stride + L.img_off + (size_t)v0 * pitch + c0;
     uint32_t s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
 #pragma unroll 2
     for (int v = v0; v < v1; ++v, dst += pitch) {
         const uint32_t ye = __ldg(ytab + v);
         const int cy1 = (int)(ye >> 16), cy0 = 256 - cy1;
         const size_t roff = (size_t)(ye & 0xffffu) * spitch;
-        uint32_t outv = 0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const uint8_t* r0 = col[k] + roff;
@@ -223,14 +226,14 @@ __global__ void __launch_bounds__(kResizeThreads) k_resize_colsum(DevBufs b, con
             const int t0 = (int)__ldg(r0) * cx0 + (int)__ldg(r0 + 1) * cx1[k];
             const int t1 = (int)__ldg(r1) * cx0 + (int)__ldg(r1 + 1) * cx1[k];
             const uint32_t pv = live[k] ? (uint32_t)(t0 * cy0 + t1 * cy1 + 32768) >> 16 : 0u;
-            outv |= pv << (8 * k);
+            if (inpitch[k]) dst[32 * k] = (uint8_t)pv;
             s[k] += pv; q[k] += pv * pv;
         }
-        *reinterpret_cast<uint32_t*>(dst) = outv;
     }
-    const size_t o = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * pitch + qx * 4;
-    *reinterpret_cast<uint4*>(b.carryS + o) = make_uint4(s[0], s[1], s[2], s[3]);
-    *reinterpret_cast<uint4*>(b.carryQ + o) = make_uint4(q[0], q[1], q[2], q[3]);
+    const size_t o = (size_t)frame * b.carry_stride + L.carry_off + (size_t)strip * pitch + c0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (inpitch[k]) { b.carryS[o + 32 * k] = s[k]; b.carryQ[o + 32 * k] = q[k]; }
 }
 
 void launch_resize_colsum(const DevBufs& b, const WorkItem* wk, int nblocks, cudaStream_t st) {
