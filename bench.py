@@ -403,12 +403,14 @@ class Runner:
 
 def launches_per_group(runner, counters):
     """Kernels of ours per launch group: resize+colsum, carry, integral bands, scan (one launch per grid-step class
-    present), group init / link / finish; + area, preprocess, equalize on the BGR path."""
+    present), group init / link / finish; + (area,) preprocess, equalize on the BGR path."""
     n = 3 + 3
     sc, lw, lh, stp = runner.det.plan_info(*(runner.scan or (runner.w, runner.h)))
     n += len(set(int(s) for s in stp))
     if runner.scan:
-        n += 3
+        sw, sh = runner.scan
+        fused = (2 * sw, 2 * sh) == (runner.w, runner.h) and sw % 4 == 0     # the 2x2 decimation runs inside k_preprocess: no k_area launch
+        n += 2 if fused else 3
     return n
 
 
