@@ -138,6 +138,28 @@ def test_inexact_stage_sums_follow_file_order(ug, orc, cv2ref, synth, tmp_path):
         det.close()
 
 
+@pytest.mark.parametrize("name", ["alt", "alt2"])
+def test_queue_takes_every_survivor_of_stage_0(ug, orc, cv2ref, synth, name):
+    """dense_stages = 1 sends every window that passes stage 0 (three quarters of the grid: thousands per tile) to the
+    block-local queue: the survivor list of stump cascades then overflows the dead mask buffers it lives in and is drained
+    in passes, tree cascades pick every window out of the masks; both on the 128 x 32 and the 64 x 16 tiles of a 1280x720
+    frame.  Per-window decisions and final-stage sums against the oracle."""
+    casc = ug.Cascade(cv2ref.cascade_path(name))
+    oc = orc.OracleCascade.load(cv2ref.cascade_path(name))
+    g = synth.gray_frame(1280, 720, 8, 77)
+    det = ug.Detector(casc, ug.default_params(dense_stages=1, max_raw_per_frame=1 << 16), max_size=(1280, 720), max_batch=1)
+    det.set_stage_map(True)
+    got = det.detect_gray(g)
+    raw, sums = det.raw()
+    ctr = det.counters()
+    oraw, osums, octr, omap = orc.detect_raw(oc, g, want_map=True)
+    assert np.array_equal(det.stage_map(), omap)
+    assert sorted(zip(map(tuple, raw.tolist()), sums.tolist())) == sorted(zip(map(tuple, oraw.tolist()), osums.tolist())) and len(raw) > 0
+    assert ctr["queued"] == int((omap >= 1).sum())                  # every stage-0 survivor went through the queue
+    assert rectset(got) == rectset(orc.detect_multiscale(oc, g)[0])
+    det.close()
+
+
 def test_truncated_lists_are_reported_not_cut(ug, cv2ref, synth):
     """more rectangles than `cap` is UGD_ERR_TRUNCATED with the true counts, and the wrappers fetch again."""
     import ctypes as C
