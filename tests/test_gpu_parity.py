@@ -277,6 +277,58 @@ def test_crop_faces_from_device_frames(ug, synth, cv2ref):
     det.close()
 
 
+def test_randomized_call_sequences(dets, synth, orc, cv2ref):
+    """Forty calls in a random order over the four shared detectors: frame sizes that make the plans, the buffers and the TMA
+    tensor maps grow, shrink and come back; gray and BGR; single frames, batches below and above max_batch (one launch group,
+    the group pipeline), device-resident batches, the submit/wait form and the fused decimation -- every list against the oracle.
+    State that survives a call (plan cache, buffer sets, constant bank, pinned staging) is what this is after."""
+    import cv2
+    import torch
+    rng = np.random.default_rng(20260101)
+    ocs = {n: orc.OracleCascade.load(cv2ref.cascade_path(n)) for n in CASCADES}
+    sizes = [(320, 180), (333, 217), (480, 270), (640, 360), (200, 400), (96, 64)]
+    for it in range(40):
+        name = CASCADES[int(rng.integers(len(CASCADES)))]
+        _, det = dets[name]
+        oc = ocs[name]
+        w, h = sizes[int(rng.integers(len(sizes)))]
+        kind = ["gray1", "bgr1", "gray_batch", "bgr_batch", "device", "submit", "scaled"][int(rng.integers(7))]
+        seed = 3000 + it
+        if kind == "gray1":
+            g = synth.gray_frame(w, h, 3, seed)
+            assert rectset(det.detect_gray(g)) == rectset(orc.detect_multiscale(oc, g)[0]), (it, name, kind, w, h)
+        elif kind == "bgr1":
+            f = synth.bgr_frame(w, h, 3, seed)
+            assert rectset(det.detect_bgr(f)) == rectset(orc.detect_faces(oc, f)[0]), (it, name, kind, w, h)
+        elif kind in ("gray_batch", "device", "submit"):
+            n = int(rng.integers(1, 10))                                                  # max_batch is 4
+            fr = np.stack([synth.gray_frame(w, h, 3, seed * 16 + i) for i in range(n)])
+            if kind == "gray_batch":
+                got = det.detect_batch(fr)
+            elif kind == "device":
+                dev = torch.from_numpy(fr).cuda()
+                got = det.detect_batch_device(dev.data_ptr(), False, n, w, h)
+            else:
+                det.submit_batch(fr)
+                got = det.wait_batch()
+            for i in range(n):
+                assert rectset(got[i]) == rectset(orc.detect_multiscale(oc, fr[i])[0]), (it, name, kind, w, h, i)
+        elif kind == "bgr_batch":
+            n = int(rng.integers(1, 7))
+            fr = np.stack([synth.bgr_frame(w, h, 3, seed * 16 + i) for i in range(n)])
+            got = det.detect_batch(fr)
+            for i in range(n):
+                assert rectset(got[i]) == rectset(orc.detect_faces(oc, fr[i])[0]), (it, name, kind, w, h, i)
+        else:
+            n = int(rng.integers(1, 7))
+            W2, H2 = (2 * w, 2 * h) if rng.integers(2) else (3 * w, 3 * h)                 # fused 2x2, or k_area
+            fr = np.stack([synth.bgr_frame(W2, H2, 3, seed * 16 + i) for i in range(n)])
+            got = det.detect_batch_scaled(fr, (w, h))
+            for i in range(n):
+                small = cv2.resize(fr[i], (w, h), interpolation=cv2.INTER_AREA)
+                assert rectset(got[i]) == rectset(orc.detect_faces(oc, small)[0]), (it, name, kind, w, h, i)
+
+
 def test_edge_cases(dets, synth, ug):
     casc, det = dets["alt"]
     assert len(det.detect_gray(np.zeros((360, 640), np.uint8))) == 0          # flat: all low variance
