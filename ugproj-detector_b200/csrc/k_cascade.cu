@@ -1006,7 +1006,9 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
                         for (int t = lane; t < nt; t += 32) {
                             const int n = n0 + t;
                             const uint4 A = __ldg(nA + n), B = __ldg(nB + n), Cq = __ldg(b.nodeC + n);
-                            const uint32_t nc = __ldg(b.nodeM + n) & 255u;
+                            // corner count from the coefficient bytes (a used slot never has coefficient 0; counts are 6, 8, 9 or 12):
+                            // one load fewer per node than fetching it from nodeM
+                            const uint32_t nc = (Cq.x & 0xff00u) ? 12u : (Cq.x & 0xffu) ? 9u : (B.w & 0xff0000u) ? 8u : 6u;
                             const float nthr = __uint_as_float(Cq.y);
                             const double delta = __hiloint2double((int)Cq.w, (int)Cq.z);      // (left - right) * 128, see add_if_lt
 #pragma unroll
