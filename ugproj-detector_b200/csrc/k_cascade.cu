@@ -1,22 +1,22 @@
 // Window scan and cascade stage evaluation for sm_100a.
 //
-//   k_scan : one block (8 warps) = 16 grid rows of one level of one frame, walking the rows left to
-//            right in tiles of 64 x 16 windows.  Per tile:
-//              1. the patch of the integral image S under the tile is staged in shared memory
-//                 (coalesced loads; for grid step 2 even/odd columns are de-interleaved so that
-//                 x-adjacent windows always sit in consecutive banks);
-//              2. row by row, every lane computes the variance normalisation and stage 0 of its own
-//                 window; the oracle's sequential x-skip rule is resolved in closed form with one
-//                 ballot and a run length carried along the row in a register;
-//              3. survivors are kept as 32 bit masks, one per BANK CLASS q = (col + SH*row) mod 32
-//                 (the bank of the window's origin in the tile; each class has exactly 32 candidate
-//                 windows).  A warp-round takes the j-th live window of every class: lane q always
-//                 works on a window of class q, so every corner load of a round is free of bank
-//                 conflicts whatever the survivor pattern is.  Rounds are dealt to the 8 warps;
-//                 passing windows set their bit in the next stage's masks (shared-memory atomicOr,
-//                 one address per lane) -- this is the ballot/popc compaction of the design, done
-//                 per bank class.  Node data is broadcast from __constant__ as merged corner lists
-//                 (6/8/9 LDS + IMAD per weak classifier);
+//   k_scan : one block (8 warps) = 32 grid rows of one level of one frame on the grid-step-1 levels (tiles of 128 x 32
+//            windows, 128 candidate windows per bank class) or 16 grid rows on the grid-step-2 levels, two-plane
+//            (tilted) tiles and large windows (tiles of 64 x 16), walking the rows left to right.  Per tile:
+//              1. the patch of the integral image S under the tile is staged in shared memory by TMA (one
+//                 cp.async.bulk.tensor box per plane; for grid step 2 the planes are stored with even / odd columns
+//                 de-interleaved, so that x-adjacent windows always sit in consecutive banks and both halves are plain
+//                 boxes);
+//              2. a warp takes its rows two at a time: every lane computes the variance normalisation of its two windows
+//                 (same column, two rows) and runs stage 0 on both at once; the oracle's sequential x-skip rule is resolved
+//                 in closed form, per row, with one ballot and a run length carried along the row in a register;
+//              3. survivors are kept as bit masks, one per BANK CLASS q = (col + SH*row) mod 32 (the bank of the window's
+//                 origin in the tile).  A warp-round takes the j-th live window of every class: lane q always works on a
+//                 window of class q, so every corner load of a round is free of bank conflicts whatever the survivor
+//                 pattern is.  Rounds are dealt to the 8 warps, two rounds (two windows per lane) share every node fetch;
+//                 passing windows set their bit in the next stage's masks (shared-memory atomicOr, one address per
+//                 lane) -- this is the ballot/popc compaction of the design, done per bank class.  Node data is
+//                 broadcast from __constant__ as merged corner lists (6/8/9 LDS per weak classifier and window);
 //              4. this goes on for the `dense_stages` first stages, or until fewer than `tile_min` windows
 //                 are left in the tile;
 //              5. the few windows that are left are finished by a block-local work queue: each warp pops
