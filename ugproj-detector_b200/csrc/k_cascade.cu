@@ -1006,9 +1006,9 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
                         for (int t = lane; t < nt; t += 32) {
                             const int n = n0 + t;
                             const uint4 A = __ldg(nA + n), B = __ldg(nB + n), Cq = __ldg(b.nodeC + n);
-                            // corner count from the coefficient bytes (a used slot never has coefficient 0; counts are 6, 8, 9 or 12):
-                            // one load fewer per node than fetching it from nodeM
-                            const uint32_t nc = (Cq.x & 0xff00u) ? 12u : (Cq.x & 0xffu) ? 9u : (B.w & 0xff0000u) ? 8u : 6u;
+                            // slots to walk (6, 8, 9 or 12) from the coefficient bytes already loaded -- an unused slot has coefficient 0,
+                            // a padded one inside the walked range is harmless -- instead of one more load from nodeM
+                            const uint32_t nc = (Cq.x >> 8) ? 12u : Cq.x ? 9u : (B.w >> 16) ? 8u : 6u;
                             const float nthr = __uint_as_float(Cq.y);
                             const double delta = __hiloint2double((int)Cq.w, (int)Cq.z);      // (left - right) * 128, see add_if_lt
 #pragma unroll
