@@ -259,6 +259,7 @@ class Runner:
         import torch
         self.env, self.torch = env, torch
         ug, synth, cv2_ref = env["ug"], env["synth"], env["cv2_ref"]
+        self.synth = synth
         self.cascade, self.w, self.h, self.sf, self.ms, self.nF, self.scan = cascade, w, h, sf, (ms, ms), nF, scan
         self.group = min(group, nF)
         self.distinct = min(distinct, nF)
@@ -300,6 +301,26 @@ class Runner:
 
     def step_pageable(self):
         return self._run(self.pageable.ctypes.data, False)
+
+    def single_frame_latency(self, n=60):
+        """One frame per call, the way the reference's tracker calls detectFaces (face_tracker.cc:295): wall-clock time of the
+        synchronous ugd_detect_gray / ugd_detect_bgr call on a pageable frame, median of n calls after 10 warm-up calls."""
+        out = {}
+        w, h = self.scan or (self.w, self.h)
+        frames = {"detect_gray_ms": self.synth.gray_frame(w, h, self.synth.default_nfaces(w, h), 7),
+                  "detect_bgr_ms": self.synth.bgr_frame(w, h, self.synth.default_nfaces(w, h), 7)}
+        for key, f in frames.items():
+            fn = self.det.detect_gray if f.ndim == 2 else self.det.detect_bgr
+            for _ in range(10):
+                fn(f)
+            ts = []
+            for _ in range(n):
+                t0 = time.perf_counter()
+                fn(f)
+                ts.append((time.perf_counter() - t0) * 1e3)
+            out[key] = statistics.median(ts)
+        out["frame"] = f"{w}x{h}, pageable host memory, one synchronous call per frame"
+        return out
 
     def timed(self, fn, steps, warmup, sample_clocks=False):
         torch, env = self.torch, self.env
@@ -463,6 +484,7 @@ def main():
         for k, (t, l) in det.kernel_times().items():
             ktimes[k][0] += t; ktimes[k][1] += l
     det.set_profiling(False)
+    latency = R.single_frame_latency() if rank == 0 else None
 
     line = None
     failed = False
@@ -580,6 +602,7 @@ def main():
             "e2e_pageable": {"value": fps_page, "unit": "frames/s", "ms_per_step": ms_page / n_page, "steps": n_page,
                              "host_memory": "pageable (a plain allocation, what the tracker's cv::Mat is: face_tracker.cc:112-114)"},
             "gpu_launches": (groups * lpg + (1 if world > 1 else 0)) * args.steps,
+            "single_frame_latency": latency,
             "parity": parity,
             "roofline": roof, "roofline_hbm": roof_hbm, "stages": stage, "kernels": kern,
             "cpu_baseline": cpu, "clocks": clocks,

@@ -723,6 +723,10 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     const unsigned below = lane ? (0xffffffffu >> (32 - lane)) : 0u;
     int16_t* map = (b.stage_map && frame == 0) ? b.stage_map + pos_off : nullptr;
     if (tid < 5) s_ctr[tid] = 0;
+#if UGD_CHECKED
+    // self-test hook of the checked build (tools/r02_checked.sh): UGD_SCAN_KMIN=12345 asks for one read a megabyte past the tile
+    if (b.scan_kmin == 12345 && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) (void)tile_at(reinterpret_cast<const char*>(s_tiles), 1 << 20);
+#endif
     unsigned run_par = 0;                              // per owned row: parity of the stage-0 failure run ending just before the next segment
     // per-lane tallies, reduced once at the end of the block: evaluated | low variance << 16,  near a threshold | passed the
     // variance test << 16 (a lane sees at most a few hundred windows of a block: 16 bits each are plenty)
