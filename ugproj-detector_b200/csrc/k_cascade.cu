@@ -75,12 +75,12 @@ static int tile_rows(int si, int win_w, int win_h, bool tilted) {
     return (tc + 7) * tr * 4 <= 36 * 1024 ? 2 * kTileRows : kTileRows;
 }
 
-ScanGeom make_scan_geom(int win_w, int win_h, bool tilted) {
+ScanGeom make_scan_geom(int win_w, int win_h, bool tilted, bool short_tiles) {
     ScanGeom g{};
     for (int si = 0; si < 2; ++si) {
         const int step = si + 1;
         g.cols[si] = tile_cols(si, win_w, win_h, tilted);
-        g.rows[si] = tile_rows(si, win_w, win_h, tilted);
+        g.rows[si] = short_tiles ? kTileRows : tile_rows(si, win_w, win_h, tilted);
         g.TC[si] = (g.cols[si] - 1) * step + win_w + 1;
         g.TR[si] = (g.rows[si] - 1) * step + win_h + 1;
         if (si == 0) {
@@ -713,8 +713,11 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     const uint32_t pos_off = Lg.pos_off;
     const int si = step - 1;
     const DNodeL* __restrict__ dn = c_dn[si];
-    const int TP = c_geom.TP[si], OD = c_geom.OD[si], TC = c_geom.TC[si], TR = c_geom.TR[si], SH = c_geom.SH[si];
-    const int plane_ints = c_geom.plane_ints[si];
+    // (tile rows and plane size follow from R, not from the constant image: calls with a handful of frames run the step-1 levels on
+    //  16-row tiles for latency, with the same image -- see launch_scan)
+    const int TP = c_geom.TP[si], OD = c_geom.OD[si], TC = c_geom.TC[si], SH = c_geom.SH[si];
+    const int TR = (R - 1) * step + b.win_h + 1;
+    const int plane_ints = si ? c_geom.plane_ints[1] : (TR * TP + 31) / 32 * 32;
     const int r0 = it.first;
     const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
     const int32_t* Q = b.SQ + (size_t)frame * b.int_stride + Lg.int_off;
@@ -1182,11 +1185,15 @@ static size_t scan_align_pad(K kernel) {
 
 // With a side stream the two launches run CONCURRENTLY (they touch disjoint levels): the grid-step-1 launch goes first on
 // `st`, the grid-step-2 launch next to it on `side`, so the tail of one fills with the blocks of the other.
+// `short_tiles`: a call with only a few frames has too few blocks for their length -- a block walks its rows from end to end, and a
+// one-frame call lasts as long as its longest block -- so the grid-step-1 levels then run on 16-row tiles (twice the blocks,
+// half as long; `wk` must be the matching work table).  Those tiles have no tensor maps (the maps describe the 32-row box): plain
+// staging loads.
 void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side,
-                 cudaEvent_t ev_fork, cudaEvent_t ev_join) {
+                 cudaEvent_t ev_fork, cudaEvent_t ev_join, bool short_tiles) {
     if (!nblocks) return;
     DevBufs b = b0;
-    const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr);
+    const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr, short_tiles);
     const bool both = nblocks_step2 > 0 && nblocks_step2 < nblocks;
     const bool fork = side && both;
     if (fork) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
@@ -1198,6 +1205,7 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         int dbl = 0;
         const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
         b.tmaps = half || b0.deint2 ? b0.tmaps : nullptr;     // the grid-step-2 launch has TMA boxes only over de-interleaved rows
+        if (half && short_tiles && g.rows[0] != make_scan_geom(b.win_w, b.win_h, b.T != nullptr).rows[0]) b.tmaps = nullptr;
         const dim3 grid(n, b.nframes);
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const bool tall = g.rows[half ? 0 : 1] == 2 * kTileRows;          // only ever with wide tiles
