@@ -162,7 +162,7 @@ def test_queue_takes_every_survivor_of_stage_0(ug, orc, cv2ref, synth, name):
 
 @pytest.mark.parametrize("name", ["alt", "alt2"])
 def test_stage_map_720p_in_a_batch(ug, orc, cv2ref, synth, name):
-    """Calls with fewer than 150 scan blocks (one small frame) run the grid-step-1 levels on 16-row tiles (latency), everything
+    """Calls with fewer than 100 scan blocks (one small frame) run the grid-step-1 levels on 16-row tiles (latency), everything
     else on the 32-row tiles.  The same frame six times in one launch group: per-window decisions (frame 0) against the oracle,
     all six lists equal to the one-frame call's."""
     casc = ug.Cascade(cv2ref.cascade_path(name))

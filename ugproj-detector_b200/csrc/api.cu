@@ -638,7 +638,7 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     } else {
         // A handful of frames: too few blocks for their length (a one-frame call lasts as long as its longest block), so the
         // grid-step-1 levels run on 16-row tiles -- twice the blocks, each half as long
-        static const int short_below = getenv("UGD_SHORT_TILES_BELOW") ? atoi(getenv("UGD_SHORT_TILES_BELOW")) : 150;   // (blocks of the call with 32-row tiles; measured: one 640x360 frame 0.49 -> 0.43 ms, one 1280x720 frame (233 blocks) 0.79 -> 0.91 ms)
+        static const int short_below = getenv("UGD_SHORT_TILES_BELOW") ? atoi(getenv("UGD_SHORT_TILES_BELOW")) : 100;   // (blocks of the call with 32-row tiles; measured: one 640x360 frame 0.49 -> 0.43 ms, one 1280x720 frame (144 blocks) 0.79 -> 0.91 ms)
         const bool short_tiles = (long long)nframes * (long long)p.wk_scan.size() < short_below && !dp->host_wk_scan_short.empty();
         const std::vector<WorkItem>& wk = short_tiles ? dp->host_wk_scan_short : p.wk_scan;
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
