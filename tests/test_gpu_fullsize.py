@@ -162,23 +162,25 @@ def test_queue_takes_every_survivor_of_stage_0(ug, orc, cv2ref, synth, name):
 
 @pytest.mark.parametrize("name", ["alt", "alt2"])
 def test_stage_map_720p_in_a_batch(ug, orc, cv2ref, synth, name):
-    """Calls with fewer than 100 scan blocks (one small frame) run the grid-step-1 levels on 16-row tiles (latency), everything
-    else on the 32-row tiles.  The same frame six times in one launch group: per-window decisions (frame 0) against the oracle,
-    all six lists equal to the one-frame call's."""
+    """Small calls (below 6000 row-walking scan blocks: every one-frame call) run one scan block per tile, with the x-skip state
+    at the tile's left edge from a backward pass over stage 0; large groups walk whole rows.  The same frame in a group of 44
+    (6336 blocks) takes the row-walking path: per-window decisions (frame 0) against the oracle, every list equal to the
+    one-frame call's (the chunked path)."""
     casc = ug.Cascade(cv2ref.cascade_path(name))
     oc = orc.OracleCascade.load(cv2ref.cascade_path(name))
     g = synth.gray_frame(1280, 720, 8, 2000)
-    det = ug.Detector(casc, ug.default_params(max_raw_per_frame=1 << 16), max_size=(1280, 720), max_batch=6)
+    det = ug.Detector(casc, ug.default_params(max_raw_per_frame=1 << 16), max_size=(1280, 720), max_batch=44)
     single = det.detect_gray(g)
     det.set_stage_map(True)
-    lists = det.detect_batch(np.stack([g] * 6))
+    lists = det.detect_batch(np.stack([g] * 44))
     smap = det.stage_map()
     raw, sums = det.raw()
     oraw, osums, octr, omap = orc.detect_raw(oc, g, want_map=True)
     assert np.array_equal(smap, omap)
     assert sorted(zip(map(tuple, raw.tolist()), sums.tolist())) == sorted(zip(map(tuple, oraw.tolist()), osums.tolist()))
-    for f in range(6):
+    for f in range(44):
         assert rectset(lists[f]) == rectset(single)
+    assert len(single) > 0
     det.close()
 
 

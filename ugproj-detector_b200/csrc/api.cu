@@ -39,14 +39,14 @@ struct DevPtr {                       // grow-only device allocation
 struct DevPlan {                      // a Plan plus its device copies
     Plan host;
     DevPtr levels, xtab, ytab, wk_resize, wk_carry, wk_bands, wk_scan;
-    DevPtr wk_scan_short; std::vector<WorkItem> host_wk_scan_short;   // the scan's work table for 16-row tiles everywhere (calls with few frames)
+    DevPtr wk_scan_chunk; std::vector<WorkItem> host_wk_scan_chunk;   // one block per (row band, tile): calls with few frames
     // TMA tensor maps of the integral planes, one table per buffer set; rebuilt when the planes move or grow
     DevPtr tmaps[2];
     const void* tm_S[2] = {nullptr, nullptr}; const void* tm_T[2] = {nullptr, nullptr};
     int tm_frames[2] = {0, 0};
     bool tm_ok[2] = {false, false};
     void release() { levels.release(); xtab.release(); ytab.release(); wk_resize.release();
-                     wk_carry.release(); wk_bands.release(); wk_scan.release(); wk_scan_short.release(); tmaps[0].release(); tmaps[1].release(); }
+                     wk_carry.release(); wk_bands.release(); wk_scan.release(); wk_scan_chunk.release(); tmaps[0].release(); tmaps[1].release(); }
 };
 
 struct DevAreaPlan {                  // INTER_AREA tables for one (source size -> scan size) pair
@@ -173,7 +173,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     const Cascade& c = *d->casc;
     build_plan(w, h, c.win_w, c.win_h, d->prm.scale_factor, d->prm.min_w, d->prm.min_h, d->prm.max_w, d->prm.max_h, dp->host);
     build_scan_work(make_scan_geom(c.win_w, c.win_h, c.has_tilted), dp->host.levels, dp->host.wk_scan);   // tile height depends on the level's grid step
-    build_scan_work(make_scan_geom(c.win_w, c.win_h, c.has_tilted, true), dp->host.levels, dp->host_wk_scan_short);
+    build_scan_work_chunked(make_scan_geom(c.win_w, c.win_h, c.has_tilted), dp->host.levels, dp->host_wk_scan_chunk);
     int rc;
     if ((rc = upload(d, dp->levels, dp->host.levels))) return rc;
     if ((rc = upload(d, dp->xtab, dp->host.xtab))) return rc;
@@ -182,7 +182,7 @@ int get_plan(ugd_detector* d, int w, int h, DevPlan** out) {
     if ((rc = upload(d, dp->wk_carry, dp->host.wk_carry))) return rc;
     if ((rc = upload(d, dp->wk_bands, dp->host.wk_bands))) return rc;
     if ((rc = upload(d, dp->wk_scan, dp->host.wk_scan))) return rc;
-    if ((rc = upload(d, dp->wk_scan_short, dp->host_wk_scan_short))) return rc;
+    if ((rc = upload(d, dp->wk_scan_chunk, dp->host_wk_scan_chunk))) return rc;
     if (c.has_tilted) CK(init_tilted_attributes(d->device, dp->host.max_level_w));
     CK(cudaStreamSynchronize(d->stream));      // host vectors stay alive in dp->host, but keep it simple
     *out = dp.get();
@@ -324,7 +324,7 @@ int upload_cascade(ugd_detector* d) {
 }
 
 // Makes this detector's image the resident one (see ConstBank), launches the scan and records the last-use event.
-int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, int set, bool short_tiles) {
+int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, int set) {
     std::lock_guard<std::mutex> lk(g_const_mu);
     ConstBank& bk = g_bank[d->device & 63];
     if (bk.uid != d->casc_uid || bk.dense != d->dense_stages) {
@@ -342,7 +342,7 @@ int scan_with_constants(ugd_detector* d, const DevBufs& b, const WorkItem* wk, i
         d->upload_wait[set] = false;
     }
     static const bool serial = getenv("UGD_SCAN_SERIAL") != nullptr;
-    launch_scan(b, wk, nblocks, nblocks_step2, st, serial ? nullptr : d->scan_side[set], d->ev_scan_fork[set], d->ev_scan_join[set], short_tiles);
+    launch_scan(b, wk, nblocks, nblocks_step2, st, serial ? nullptr : d->scan_side[set], d->ev_scan_fork[set], d->ev_scan_join[set]);
     CK(cudaEventRecord(d->ev_const_use[set], st));
     d->const_used[set] = true;
     if (std::find(bk.users.begin(), bk.users.end(), d) == bk.users.end()) bk.users.push_back(d);
@@ -636,15 +636,19 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
     if (legacy) {
         if ((rc = run_legacy_scan(d, b, nframes, st))) return rc;
     } else {
-        // A handful of frames: too few blocks for their length (a one-frame call lasts as long as its longest block), so the
-        // grid-step-1 levels run on 16-row tiles -- twice the blocks, each half as long
-        static const int short_below = getenv("UGD_SHORT_TILES_BELOW") ? atoi(getenv("UGD_SHORT_TILES_BELOW")) : 100;   // (blocks of the call with 32-row tiles; measured: one 640x360 frame 0.49 -> 0.43 ms, one 1280x720 frame (144 blocks) 0.79 -> 0.91 ms)
-        const bool short_tiles = (long long)nframes * (long long)p.wk_scan.size() < short_below && !dp->host_wk_scan_short.empty();
-        const std::vector<WorkItem>& wk = short_tiles ? dp->host_wk_scan_short : p.wk_scan;
+        // Too few blocks for their length -- a block that walks its rows from end to end makes a one-frame call last as long as
+        // its longest block, and a group of small frames ends in a long tail -- so calls below 6000 row-walking blocks run one
+        // block per (row band, TILE): the x-skip state at the left edge of a tile comes from a short backward pass over stage 0
+        // (k_scan, chunked mode).  Measured, chunked against row-walking: one 1280x720 frame 0.44 / 0.81 ms per call, 32 such
+        // frames 3.92 / 4.10 ms, 64 frames 640x360 2.10 / 2.35 ms; 64 frames 1280x720 (9216 blocks) 7.08 / 7.06, 1080p and 4K
+        // groups 3 to 6 % slower chunked (the backward pass and the extra tile staging are not free).
+        static const int chunk_below = getenv("UGD_CHUNK_BELOW") ? atoi(getenv("UGD_CHUNK_BELOW")) : 6000;
+        const bool chunked = !dp->host_wk_scan_chunk.empty() && (long long)nframes * (long long)p.wk_scan.size() < chunk_below;
+        const std::vector<WorkItem>& wk = chunked ? dp->host_wk_scan_chunk : p.wk_scan;
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)wk.size() && p.levels[wk[n2].level].step == 2) ++n2;
-        if ((rc = scan_with_constants(d, b, (short_tiles ? dp->wk_scan_short : dp->wk_scan).as<WorkItem>(), (int)wk.size(), n2, st, second ? 1 : 0,
-                                      short_tiles))) return rc;
+        b.scan_chunked = chunked ? 1 : 0;
+        if ((rc = scan_with_constants(d, b, (chunked ? dp->wk_scan_chunk : dp->wk_scan).as<WorkItem>(), (int)wk.size(), n2, st, second ? 1 : 0))) return rc;
     }
     mark(d, 8);
     launch_group(b, st);

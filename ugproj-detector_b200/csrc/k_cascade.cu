@@ -75,12 +75,12 @@ static int tile_rows(int si, int win_w, int win_h, bool tilted) {
     return (tc + 7) * tr * 4 <= 36 * 1024 ? 2 * kTileRows : kTileRows;
 }
 
-ScanGeom make_scan_geom(int win_w, int win_h, bool tilted, bool short_tiles) {
+ScanGeom make_scan_geom(int win_w, int win_h, bool tilted) {
     ScanGeom g{};
     for (int si = 0; si < 2; ++si) {
         const int step = si + 1;
         g.cols[si] = tile_cols(si, win_w, win_h, tilted);
-        g.rows[si] = short_tiles ? kTileRows : tile_rows(si, win_w, win_h, tilted);
+        g.rows[si] = tile_rows(si, win_w, win_h, tilted);
         g.TC[si] = (g.cols[si] - 1) * step + win_w + 1;
         g.TR[si] = (g.rows[si] - 1) * step + win_h + 1;
         if (si == 0) {
@@ -106,6 +106,16 @@ static inline int32_t tile_off(const ScanGeom& g, int si, int x, int y) {     //
     return 4 * (si ? y * g.TCH[1] + (x & 1) * g.OD[1] + (x >> 1) : y * g.TP[0] + x);
 }
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y) { return tile_off(g, si, x, y); }
+// Chunked form (calls with few frames): one scan block per (row band, tile) -- first = row | tile index << 16.
+void build_scan_work_chunked(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk) {
+    wk.clear();
+    for (int l = 0; l < (int)levels.size(); ++l) {
+        const int si = levels[l].step - 1;
+        if (levels[l].nyg > 0xffff || (levels[l].nxg + g.cols[si] - 1) / g.cols[si] > 0x7fff) { wk.clear(); return; }   // does not fit the packing: no chunked mode
+        for (int r = 0; r < levels[l].nyg; r += g.rows[si])
+            for (int t = 0; t * g.cols[si] < levels[l].nxg; ++t) wk.push_back({l, r | t << 16});
+    }
+}
 // One scan block per g.rows[step - 1] grid rows of a level (the plan's generic table assumes kScanRows everywhere).
 void build_scan_work(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk) {
     wk.clear();
@@ -689,8 +699,8 @@ struct Live {
     }
 };
 
-template <int MODE, bool WORDS, int C, int R = kTileRows, int NW = kScanWarps>
-__global__ void __launch_bounds__(NW * 32, MODE ? (R == kTileRows ? UGD_SCAN_MINBLOCKS : UGD_SCAN_MINBLOCKS_TALL) * kScanWarps / NW : 1536 / (NW * 32))
+template <int MODE, bool WORDS, int C, int R = kTileRows, int NW = kScanWarps, bool CHUNK = false>
+__global__ void __launch_bounds__(NW * 32, CHUNK ? 4 : MODE ? (R == kTileRows ? UGD_SCAN_MINBLOCKS : UGD_SCAN_MINBLOCKS_TALL) * kScanWarps / NW : 1536 / (NW * 32))
 k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     constexpr int SEG = C / 32, LSEG = SEG == 2 ? 1 : 2, NMW = R * C / 1024;   // column segments per row, survivor mask words per class
     static_assert((C == 64 || C == 128) && (R == 16 || R == 32) && R % NW == 0, "32, 64 or 128 windows per bank class");
@@ -713,12 +723,12 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     const uint32_t pos_off = Lg.pos_off;
     const int si = step - 1;
     const DNodeL* __restrict__ dn = c_dn[si];
-    // (tile rows and plane size follow from R, not from the constant image: calls with a handful of frames run the step-1 levels on
-    //  16-row tiles for latency, with the same image -- see launch_scan)
     const int TP = c_geom.TP[si], OD = c_geom.OD[si], TC = c_geom.TC[si], SH = c_geom.SH[si];
     const int TR = (R - 1) * step + b.win_h + 1;
     const int plane_ints = si ? c_geom.plane_ints[1] : (TR * TP + 31) / 32 * 32;
-    const int r0 = it.first;
+    // chunked mode (calls with few frames, see launch_scan): the block takes ONE tile of its row band, not the whole row
+    constexpr bool chunked = CHUNK;                    // (its own instantiations: the backward pass below costs the row-walking variants registers)
+    const int r0 = chunked ? (it.first & 0xffff) : it.first;
     const int32_t* S = b.S + (size_t)frame * b.int_stride + Lg.int_off;
     const int32_t* Q = b.SQ + (size_t)frame * b.int_stride + Lg.int_off;
     const int ow = b.win_w, oh = b.win_h, D = b.dense_stages, nstages = b.nstages;
@@ -749,14 +759,72 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     if (tmaps && tid == 0) mbar_init(&s_mbar, 1);
     int* s_tile = s_tiles;
     __syncthreads();
+    const int x_begin = chunked ? (it.first >> 16) * C : 0, x_end = chunked ? min(nxg, x_begin + C) : nxg;
+    if (chunked && x_begin > 0) {
+        // The x-skip rule needs, per row, the parity of the run of stage-0 failures that ends just left of the chunk.  Walk
+        // back 32 positions at a time (their tile is staged like any other; only stage 0 runs, nothing is recorded) until every
+        // row has met a position that does not fail: 32 failures in a row leave the parity as it is.
+        constexpr int RPW0 = R / NW;
+        unsigned unresolved = (1u << RPW0) - 1u;
+        for (int xb = x_begin - 32;; xb -= 32) {
+            __syncthreads();                           // the tile buffer is free
+            if (tmaps) {
+                if (tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, xb * step, r0 * step, frame, &s_mbar);
+                mbar_wait(&s_mbar, mphase);
+                mphase ^= 1u;
+            } else {
+                stage_tile<NW>(s_tile, S, P, sw, sh, xb * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+                if (Tp) stage_tile<NW>(s_tile + plane_ints, Tp, P, sw, sh, xb * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+            }
+            __syncthreads();
+            const bool dq = b.deint2 && si;
+            const int half = P >> 1, dxb = ow - 1;
+            const int oa = dq ? half : 1, ob = dq ? (dxb & 1) * half + (dxb >> 1) : dxb;
+#pragma unroll 1
+            for (int k = 0; k < RPW0; ++k) {
+                if (!(unresolved >> k & 1)) continue;  // warp-uniform
+                const int rl = w + k * NW, row = r0 + rl;
+                const bool row_valid = row < nyg;
+                const int y = row_valid ? row * step : 0;
+                const int x = (xb + lane) * step, xq = dq ? x >> 1 : x;
+                const char* t = reinterpret_cast<const char*>(s_tile + (rl * step) * TP) + 4 * lane;
+                const int32_t* no = c_geom.norm_off[si];
+                const int vs = tile_at(t, no[0]) - tile_at(t, no[1]) - tile_at(t, no[2]) + tile_at(t, no[3]);
+                const uint32_t vq = (uint32_t)Q[(y + 1) * P + oa + xq] - (uint32_t)Q[(y + 1) * P + ob + xq] -
+                                    (uint32_t)Q[(y + oh - 1) * P + oa + xq] + (uint32_t)Q[(y + oh - 1) * P + ob + xq];
+                float vnf = 1.f;
+                bool ok = false;
+                double nf = area * (double)vq - (double)vs * (double)vs;
+                if (nf > 0.0) {
+                    nf = sqrt(nf);
+                    vnf = (float)(1.0 / nf);
+                    ok = area * (double)vnf < 1e-1;
+                }
+                if (!ok) vnf = 1.f;
+                double sum;
+                if (MODE) {
+                    const char* t1[1] = {t}; const float v1[1] = {vnf}; double s1[1];
+                    stage_eval<MODE ? MODE : 1, 1>(0, dn, t1, v1, s1);
+                    sum = s1[0];
+                } else sum = tile_stage_generic(0, dn, t, vnf);
+                const unsigned F = __ballot_sync(0xffffffffu, row_valid && ok && sum < thr0d);
+                if (F != 0xffffffffu || xb == 0) {
+                    if (F != 0xffffffffu) run_par ^= (unsigned)(__clz((int)~F) & 1) << k;
+                    unresolved &= ~(1u << k);
+                }
+            }
+            if (!__syncthreads_or(unresolved != 0u)) break;
+        }
+        __syncthreads();
+    }
     if (dbl) {
-        if (tmaps) { if (tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, 0, r0 * step, frame, &s_mbar); }
+        if (tmaps) { if (tid == 0) tma_stage(s_tile, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, x_begin * step, r0 * step, frame, &s_mbar); }
         else {
-            stage_tile<NW>(s_tile, S, P, sw, sh, 0, r0 * step, TR, TC, TP, OD, si, w, lane);
-            if (Tp) stage_tile<NW>(s_tile + plane_ints, Tp, P, sw, sh, 0, r0 * step, TR, TC, TP, OD, si, w, lane);
+            stage_tile<NW>(s_tile, S, P, sw, sh, x_begin * step, r0 * step, TR, TC, TP, OD, si, w, lane);
+            if (Tp) stage_tile<NW>(s_tile + plane_ints, Tp, P, sw, sh, x_begin * step, r0 * step, TR, TC, TP, OD, si, w, lane);
         }
     }
-    for (int xi0 = 0; xi0 < nxg; xi0 += C) {
+    for (int xi0 = x_begin; xi0 < x_end; xi0 += C) {
         __syncthreads();                               // previous tile fully consumed
         for (int i = tid; i < 96 * NMW; i += NW * 32) (&s_alive[0][0][0])[i] = 0;
         if (tid == 0) s_pop = 0;                       // the late-stage queue's class counter (phase 4)
@@ -772,7 +840,7 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
             }
         }
         __syncthreads();
-        if (dbl && xi0 + C < nxg) {                    // prefetch the next tile into the other buffer
+        if (dbl && xi0 + C < x_end) {                  // prefetch the next tile into the other buffer
             int* nxt = s_tile == s_tiles ? s_tiles + buf_ints : s_tiles;
             if (tmaps) { if (tid == 0) tma_stage(nxt, tmaps, it.level, planes, plane_ints, si, OD, tma_bytes, (xi0 + C) * step, r0 * step, frame, &s_mbar); }
             else {
@@ -1185,15 +1253,11 @@ static size_t scan_align_pad(K kernel) {
 
 // With a side stream the two launches run CONCURRENTLY (they touch disjoint levels): the grid-step-1 launch goes first on
 // `st`, the grid-step-2 launch next to it on `side`, so the tail of one fills with the blocks of the other.
-// `short_tiles`: a call with only a few frames has too few blocks for their length -- a block walks its rows from end to end, and a
-// one-frame call lasts as long as its longest block -- so the grid-step-1 levels then run on 16-row tiles (twice the blocks,
-// half as long; `wk` must be the matching work table).  Those tiles have no tensor maps (the maps describe the 32-row box): plain
-// staging loads.
 void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side,
-                 cudaEvent_t ev_fork, cudaEvent_t ev_join, bool short_tiles) {
+                 cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     if (!nblocks) return;
     DevBufs b = b0;
-    const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr, short_tiles);
+    const ScanGeom g = make_scan_geom(b.win_w, b.win_h, b.T != nullptr);
     const bool both = nblocks_step2 > 0 && nblocks_step2 < nblocks;
     const bool fork = side && both;
     if (fork) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
@@ -1205,25 +1269,32 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         int dbl = 0;
         const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
         b.tmaps = half || b0.deint2 ? b0.tmaps : nullptr;     // the grid-step-2 launch has TMA boxes only over de-interleaved rows
-        if (half && short_tiles && g.rows[0] != make_scan_geom(b.win_w, b.win_h, b.T != nullptr).rows[0]) b.tmaps = nullptr;
         const dim3 grid(n, b.nframes);
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const bool tall = g.rows[half ? 0 : 1] == 2 * kTileRows;          // only ever with wide tiles
         const int variant = tall ? 9 + b.fast_scan : wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);
+#define UGD_LAUNCH_SCAN(M, W, CC, RR)                                                                                                  \
+    do {                                                                                                                               \
+        if (b.scan_chunked)                                                                                                            \
+            k_scan<M, W, CC, RR, kScanWarps, true><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<M, W, CC, RR, kScanWarps, true>), launch_st>>>(b, wk + first, dbl); \
+        else                                                                                                                           \
+            k_scan<M, W, CC, RR><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<M, W, CC, RR>), launch_st>>>(b, wk + first, dbl);  \
+    } while (0)
         switch (variant) {
-            case 0: k_scan<0, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 1: k_scan<0, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, true, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 2: k_scan<1, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 3: k_scan<1, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, true, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 4: k_scan<2, false, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 5: k_scan<2, true, 64><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, true, 64>), launch_st>>>(b, wk + first, dbl); break;
-            case 6: k_scan<0, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 128>), launch_st>>>(b, wk + first, dbl); break;
-            case 7: k_scan<1, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 128>), launch_st>>>(b, wk + first, dbl); break;
-            case 8: k_scan<2, false, 128><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128>), launch_st>>>(b, wk + first, dbl); break;
-            case 9: k_scan<0, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<0, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
-            case 10: k_scan<1, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<1, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
-            default: k_scan<2, false, 128, 32><<<grid, kScanWarps * 32, smem + scan_align_pad(k_scan<2, false, 128, 32>), launch_st>>>(b, wk + first, dbl); break;
+            case 0: UGD_LAUNCH_SCAN(0, false, 64, 16); break;
+            case 1: UGD_LAUNCH_SCAN(0, true, 64, 16); break;
+            case 2: UGD_LAUNCH_SCAN(1, false, 64, 16); break;
+            case 3: UGD_LAUNCH_SCAN(1, true, 64, 16); break;
+            case 4: UGD_LAUNCH_SCAN(2, false, 64, 16); break;
+            case 5: UGD_LAUNCH_SCAN(2, true, 64, 16); break;
+            case 6: UGD_LAUNCH_SCAN(0, false, 128, 16); break;
+            case 7: UGD_LAUNCH_SCAN(1, false, 128, 16); break;
+            case 8: UGD_LAUNCH_SCAN(2, false, 128, 16); break;
+            case 9: UGD_LAUNCH_SCAN(0, false, 128, 32); break;
+            case 10: UGD_LAUNCH_SCAN(1, false, 128, 32); break;
+            default: UGD_LAUNCH_SCAN(2, false, 128, 32); break;
         }
+#undef UGD_LAUNCH_SCAN
     }
     if (fork) { cudaEventRecord(ev_join, side); cudaStreamWaitEvent(st, ev_join, 0); }
 }
@@ -1235,10 +1306,11 @@ cudaError_t init_kernel_attributes(int device, int win_w, int win_h, bool has_ti
     std::lock_guard<std::mutex> lk(g_attr_mu);
     int& granted = g_scan_smem[device & 63];
     if (scan_smem > granted) {
-        const void* variants[12] = {(const void*)k_scan<0, false, 64>, (const void*)k_scan<0, true, 64>, (const void*)k_scan<1, false, 64>,
-                                    (const void*)k_scan<1, true, 64>, (const void*)k_scan<2, false, 64>, (const void*)k_scan<2, true, 64>,
-                                    (const void*)k_scan<0, false, 128>, (const void*)k_scan<1, false, 128>, (const void*)k_scan<2, false, 128>,
-                                    (const void*)k_scan<0, false, 128, 32>, (const void*)k_scan<1, false, 128, 32>, (const void*)k_scan<2, false, 128, 32>};
+#define UGD_BOTH(M, W, CC, RR) (const void*)k_scan<M, W, CC, RR>, (const void*)k_scan<M, W, CC, RR, kScanWarps, true>
+        const void* variants[24] = {UGD_BOTH(0, false, 64, 16), UGD_BOTH(0, true, 64, 16), UGD_BOTH(1, false, 64, 16), UGD_BOTH(1, true, 64, 16),
+                                    UGD_BOTH(2, false, 64, 16), UGD_BOTH(2, true, 64, 16), UGD_BOTH(0, false, 128, 16), UGD_BOTH(1, false, 128, 16),
+                                    UGD_BOTH(2, false, 128, 16), UGD_BOTH(0, false, 128, 32), UGD_BOTH(1, false, 128, 32), UGD_BOTH(2, false, 128, 32)};
+#undef UGD_BOTH
         for (const void* f : variants) {
             cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, scan_smem);
             if (e != cudaSuccess) return e;

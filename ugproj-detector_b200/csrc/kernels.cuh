@@ -99,6 +99,7 @@ struct DevBufs {
     // window scan
     size_t pos_stride;                                // padded grid positions per frame
     int scan_kmin;                                    // a warp takes at least this many rounds of a stage at once (they share the node fetches)
+    int scan_chunked;                                 // the work items are (row band, tile) pairs: first = row | tile << 16 (calls with few frames; see k_scan)
     int tile_min;                                     // hand a tile's survivors to the per-warp evaluator once fewer than this remain
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
     int16_t* stage_map;                               // frame 0 only, padded layout; may be null
@@ -113,8 +114,9 @@ struct DevBufs {
 
 // Builds the in-tile node table for stages [0, dense_stages) and uploads it with the tile geometry
 // to __constant__ (call before launching k_scan with a new cascade).
-ScanGeom make_scan_geom(int win_w, int win_h, bool tilted, bool short_tiles = false);   // short_tiles: 16-row tiles everywhere (calls with few frames)
-void build_scan_work(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk);   // block -> (level, first grid row)
+ScanGeom make_scan_geom(int win_w, int win_h, bool tilted);
+void build_scan_work(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk);
+void build_scan_work_chunked(const ScanGeom& g, const std::vector<LevelInfo>& levels, std::vector<WorkItem>& wk);   // block -> (level, first grid row | tile << 16)   // block -> (level, first grid row)
 bool scan_tma_box(const ScanGeom& g, int si, uint32_t (&box)[3], uint32_t (&estride)[3]);   // the TMA box of a tile, false if it has none
 int32_t scan_tile_off(const ScanGeom& g, int si, int x, int y);   // byte offset of S(x, y) from a window's origin in the tile
 int32_t scan_plane_bytes(const ScanGeom& g, int si);              // bytes from the S tile to the tilted-integral tile
@@ -194,7 +196,7 @@ void launch_integral_bands(const DevBufs& b, const WorkItem* wk, int nblocks, cu
 void launch_tilted(const DevBufs& b, int max_level_w, cudaStream_t st);
 cudaError_t init_tilted_attributes(int device, int max_w);
 void launch_scan(const DevBufs& b, const WorkItem* wk, int nblocks, int nblocks_step2, cudaStream_t st, cudaStream_t side = nullptr,
-                 cudaEvent_t ev_fork = nullptr, cudaEvent_t ev_join = nullptr, bool short_tiles = false);
+                 cudaEvent_t ev_fork = nullptr, cudaEvent_t ev_join = nullptr);
 void launch_group(const DevBufs& b, cudaStream_t st);
 void launch_pack_lists(const uint8_t* recv, size_t msg_bytes, int world, int slot_frames, int cap, int skip_rank, int* packed,
                        size_t rect_off_bytes, cudaStream_t st);
