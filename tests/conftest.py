@@ -70,6 +70,23 @@ def truncate_cascade(path, nstages, out_path):
     return str(out_path)
 
 
+def long_failure_runs_cascade(out_path, win=(20, 20), thr=0.002):
+    """A two-stage stump cascade whose stage 0 looks at one 2x2 spot against its 4x4 surround: on textured frames it fails in
+    long runs (and passes in others), which drives the x-skip rule -- evaluate, skip, evaluate ... along a run of failures --
+    across many tile boundaries.  Stage 1 accepts what is left."""
+    with open(out_path, "w") as fh:
+        fh.write('<?xml version="1.0"?>\n<opencv_storage><c type_id="opencv-haar-classifier">'
+                 f"<size>{win[0]} {win[1]}</size><stages>"
+                 "<_><trees><_><_><feature><rects><_>8 8 4 4 -1.</_><_>9 9 2 2 4.</_></rects><tilted>0</tilted></feature>"
+                 f"<threshold>{thr}</threshold><left_val>0.</left_val><right_val>1.</right_val></_></_></trees>"
+                 "<stage_threshold>0.5</stage_threshold><parent>-1</parent><next>-1</next></_>"
+                 "<_><trees><_><_><feature><rects><_>1 1 4 4 -1.</_><_>2 2 2 2 2.</_></rects><tilted>0</tilted></feature>"
+                 "<threshold>0.1</threshold><left_val>1.</left_val><right_val>1.</right_val></_></_></trees>"
+                 "<stage_threshold>0.5</stage_threshold><parent>0</parent><next>-1</next></_>"
+                 "</stages></c></opencv_storage>")
+    return str(out_path)
+
+
 def pass_everything_cascade(out_path, win=(20, 20)):
     """a one-stump cascade whose two leaves both clear the stage threshold, so it accepts every
     window that is evaluated and passes the variance test -- it enumerates the oracle's window grid."""

@@ -6,7 +6,7 @@ truncated output lists)."""
 import numpy as np
 import pytest
 
-from conftest import inexact_cascade, rectset
+from conftest import inexact_cascade, long_failure_runs_cascade, rectset
 
 pytestmark = pytest.mark.gpu
 
@@ -181,6 +181,35 @@ def test_stage_map_720p_in_a_batch(ug, orc, cv2ref, synth, name):
     for f in range(44):
         assert rectset(lists[f]) == rectset(single)
     assert len(single) > 0
+    det.close()
+
+
+@pytest.mark.parametrize("thr", [0.002, 1e6], ids=["runs-of-dozens", "every-window-fails"])
+def test_x_skip_across_tile_boundaries(ug, orc, synth, tmp_path, thr):
+    """The x-skip rule carries the parity of a run of stage-0 failures along the row -- in a register when a block walks the row,
+    through a backward pass over stage 0 when a block owns one tile (small calls).  A crafted cascade whose stage 0 fails in runs
+    of dozens of windows (or at every window: the backward pass then walks to the start of the row) against the oracle's stage
+    map, for a one-frame call (one block per tile) and for frame 0 of a group of 44 (row-walking blocks), at 1280x720."""
+    p = long_failure_runs_cascade(tmp_path / "runs.xml", thr=thr)
+    casc = ug.Cascade(p)
+    oc = orc.OracleCascade.load(p)
+    g = synth.gray_frame(1280, 720, 8, 31)
+    oraw, osums, octr, omap = orc.detect_raw(oc, g, want_map=True, cap=1 << 21)
+    assert (omap == -2).mean() > 0.25                                                   # a third of the grid is x-skipped
+    det = ug.Detector(casc, ug.default_params(max_raw_per_frame=64), max_size=(1280, 720), max_batch=44)
+    det.set_stage_map(True)
+    for batch in (1, 44):
+        try:
+            if batch == 1:
+                det.detect_gray(g)
+            else:
+                det.detect_batch(np.stack([g] * batch))
+            assert len(oraw) <= 64
+        except ug.UgdError as e:                                                        # hundreds of thousands of accepted windows:
+            assert e.code == ug.ERR_CAPACITY and len(oraw) > 64                         # the candidate list overflows, the map is complete
+        assert np.array_equal(det.stage_map(), omap), batch
+        ctr = det.counters()
+        assert ctr["windows_evaluated"] == octr["windows_evaluated"] * batch
     det.close()
 
 
