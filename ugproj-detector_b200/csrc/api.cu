@@ -643,7 +643,11 @@ int run_group(ugd_detector* d, DevPlan* dp, const uint8_t* dev_frames, size_t fr
         // frames 3.92 / 4.10 ms, 64 frames 640x360 2.10 / 2.35 ms; 64 frames 1280x720 (9216 blocks) 7.08 / 7.06, 1080p and 4K
         // groups 3 to 6 % slower chunked (the backward pass and the extra tile staging are not free).
         static const int chunk_below = getenv("UGD_CHUNK_BELOW") ? atoi(getenv("UGD_CHUNK_BELOW")) : 6000;
-        const bool chunked = !dp->host_wk_scan_chunk.empty() && (long long)nframes * (long long)p.wk_scan.size() < chunk_below;
+        // (two-node-tree cascades -- frontalface_alt2 -- are faster chunked at every size measured: 720p groups 6.68 k -> 6.89 k frames/s,
+        //  1080p 2.94 k -> 3.07 k: their tiles take longer, and the tail of a launch of row-walking blocks with them)
+        static const bool chunk_env = getenv("UGD_CHUNK_BELOW") != nullptr;
+        const bool chunked = !dp->host_wk_scan_chunk.empty() &&
+                             ((!chunk_env && b.fast_scan == 2) || (long long)nframes * (long long)p.wk_scan.size() < chunk_below);
         const std::vector<WorkItem>& wk = chunked ? dp->host_wk_scan_chunk : p.wk_scan;
         int n2 = 0;                                   // scan blocks of the grid-step-2 levels (they lead the table)
         while (n2 < (int)wk.size() && p.levels[wk[n2].level].step == 2) ++n2;
