@@ -713,8 +713,10 @@ k_scan(DevBufs b, const WorkItem* __restrict__ wk, int dbl) {
     __shared__ int s_pop;
     __shared__ unsigned int s_ctr[5];                  // evaluated, lowvar, near, weak, queued
 
-    const WorkItem it = wk[blockIdx.x];
-    const int frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+    // grid = (frames, work items): consecutive blocks are the SAME row band of different frames, so the long blocks (the wide
+    // levels lead the table) of every frame start first and the launch ends on short ones (UGD_SCAN_FRAME_MAJOR: the old order)
+    const WorkItem it = wk[b.scan_frame_major ? blockIdx.x : blockIdx.y];
+    const int frame = b.scan_frame_major ? blockIdx.y : blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);     // warp index, provably warp-uniform
     const LevelInfo& Lg = b.levels[it.level];
     const int sw = Lg.sw, sh = Lg.sh, P = Lg.P, step = Lg.step, nxg = Lg.nxg, nyg = Lg.nyg, nxg_pad = Lg.nxg_pad;
@@ -1269,7 +1271,9 @@ void launch_scan(const DevBufs& b0, const WorkItem* wk, int nblocks, int nblocks
         int dbl = 0;
         const size_t smem = scan_smem_bytes(g, half ? 0 : 1, b.T != nullptr, &dbl);
         b.tmaps = half || b0.deint2 ? b0.tmaps : nullptr;     // the grid-step-2 launch has TMA boxes only over de-interleaved rows
-        const dim3 grid(n, b.nframes);
+        static const bool frame_major = getenv("UGD_SCAN_FRAME_MAJOR") != nullptr || false;
+        b.scan_frame_major = (frame_major || n > 65535) ? 1 : 0;
+        const dim3 grid = b.scan_frame_major ? dim3(n, b.nframes) : dim3(b.nframes, n);
         const bool wide = g.cols[half ? 0 : 1] == 2 * kTileCols;          // only ever with byte offsets (one plane, small window)
         const bool tall = g.rows[half ? 0 : 1] == 2 * kTileRows;          // only ever with wide tiles
         const int variant = tall ? 9 + b.fast_scan : wide ? 6 + b.fast_scan : b.fast_scan * 2 + (b.word_off ? 1 : 0);

@@ -99,6 +99,7 @@ struct DevBufs {
     // window scan
     size_t pos_stride;                                // padded grid positions per frame
     int scan_kmin;                                    // a warp takes at least this many rounds of a stage at once (they share the node fetches)
+    int scan_frame_major;                             // k_scan grid is (work items, frames) instead of (frames, work items)
     int scan_chunked;                                 // the work items are (row band, tile) pairs: first = row | tile << 16 (calls with few frames; see k_scan)
     int tile_min;                                     // hand a tile's survivors to the per-warp evaluator once fewer than this remain
     ugd_rect* raw; double* rawsum; int rawcap; int* rawcount;
