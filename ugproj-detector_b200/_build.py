@@ -24,6 +24,27 @@ def _nvcc() -> str:
     return "nvcc"
 
 
+def _compile_all(objdir: str, defines: list[str]):
+    """Compiles every source to objdir (the translation units in parallel: k_cascade.cu alone takes a minute)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    def one(s):
+        o = os.path.join(objdir, s + ".o")
+        cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-c", os.path.join(CSRC, s), "-o", o]
+        return s, o, subprocess.run(cmd, capture_output=True, text=True)
+
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as ex:
+        results = list(ex.map(one, SOURCES))
+    objs, log = [], []
+    for s, o, r in results:
+        log.append(r.stderr)
+        if r.returncode:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError(f"nvcc failed on {s}")
+        objs.append(o)
+    return objs, log
+
+
 def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
@@ -35,19 +56,9 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
-    objs = []
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    log = []
-    for s in SOURCES:
-        o = os.path.join(objdir, s + ".o")
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, s), "-o", o]
-        r = subprocess.run(cmd, capture_output=True, text=True)
-        log.append(r.stderr)
-        if r.returncode:
-            sys.stderr.write(r.stdout + r.stderr)
-            raise RuntimeError(f"nvcc failed on {s}")
-        objs.append(o)
+    objs, log = _compile_all(objdir, [])
     cmd = [_nvcc(), "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode:
@@ -66,15 +77,7 @@ def build_variant(name: str, defines: list[str]) -> str:
     objdir = os.path.join(HERE, "build", name)
     os.makedirs(objdir, exist_ok=True)
     out = os.path.join(HERE, "build", f"libugdet_{name}.so")
-    objs = []
-    for s in SOURCES:
-        o = os.path.join(objdir, s + ".o")
-        cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-c", os.path.join(CSRC, s), "-o", o]
-        r = subprocess.run(cmd, capture_output=True, text=True)
-        if r.returncode:
-            sys.stderr.write(r.stdout + r.stderr)
-            raise RuntimeError(f"nvcc failed on {s}")
-        objs.append(o)
+    objs, _ = _compile_all(objdir, defines)
     r = subprocess.run([_nvcc(), "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a"], capture_output=True, text=True)
     if r.returncode:
         sys.stderr.write(r.stdout + r.stderr)
