@@ -543,6 +543,18 @@ def main():
                                               "produced by the fused resize kernel)", "ms": int_ms,
                                       "algorithmic_bytes": (level_px + 8 * int_entries) * GROUP_, "achieved": g2, "peak": hbm_peak,
                                       "unit": "GB/s", "frac": g2 / hbm_peak, "traffic": tb, "traffic_source": tsrc}
+        if scan:
+            # the BGR front end of the tracker's workload as ONE unit: INTER_AREA decimation + gray / skin mask / histogram +
+            # equalisation (algorithmic bytes: the full-size BGR frame read once; gray, mask and the equalised image written once)
+            fe_ms = sum(kern[k]["ms_per_launch"] for k in ("k_area", "k_preprocess", "k_equalize") if k in kern)
+            fe_bytes = (3 * w * h + 3 * scan[0] * scan[1]) * GROUP_
+            if fe_ms:
+                g3 = fe_bytes / (fe_ms * 1e-3) / 1e9
+                tbf, tsf = traffic_record("bgr_front_end", f"{args.cascade} {w}x{h} -> {scan[0]}x{scan[1]} group {GROUP_}")
+                stage["bgr_front_end"] = {"what": "INTER_AREA decimation + BGR->gray / skin mask / histogram + equalizeHist of one launch group"
+                                                  + (" (the 2x2 decimation runs inside k_preprocess)" if "k_area" not in kern else ""),
+                                          "ms": fe_ms, "algorithmic_bytes": fe_bytes, "achieved": g3, "peak": hbm_peak, "unit": "GB/s",
+                                          "frac": g3 / hbm_peak, "traffic": tbf, "traffic_source": tsf}
         casc_ms = kern["k_scan"]["ms_per_launch"] if "k_scan" in kern else 0.0   # both scan launches of a group
         l1_nominal = 148 * 128 * sm_max * 1e6 / 1e9            # GB/s: 148 SMs x 128 B/clk x max SM clock
         try:
